@@ -1,0 +1,116 @@
+"""Library baseline trainer: the same RetinaNet in PyTorch eager with cuDNN/cuBLAS kernels,
+``torchvision`` focal loss and NCCL (DistributedDataParallel) gradient allreduce.
+
+This is "the baseline, not the product" (SURVEY.md 6.2): the strongest
+honest proxy for the reference's Horovod-NCCL + cuDNN stack on a B200, since the reference
+itself (``/root/reference/train.py``: TF1/Keras 2.1/Horovod) cannot be installed offline.
+It also runs on CPU (gloo) and is the oracle for the native engine's end-to-end tests.
+"""
+
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from ..models.retinanet import RetinaNet
+from ..ops import anchors as anchor_ops
+from ..ops import losses as loss_ops
+
+CAFFE_MEAN_BGR = (103.939, 116.779, 123.68)
+
+
+def assign_targets_batched(anchors: torch.Tensor, gt: torch.Tensor, gt_count: torch.Tensor, img_hw: torch.Tensor,
+                           neg_thr: float = 0.4, pos_thr: float = 0.5):
+    """Vectorised torch version of ops.anchors.assign_targets for a padded batch.
+
+    anchors (A,4); gt (B,G,5); gt_count (B,); img_hw (B,2) -> state (B,A) int8, cls (B,A) int64,
+    reg_target (B,A,4) fp32.
+    """
+    B, G, _ = gt.shape
+    A = anchors.shape[0]
+    a = anchors.view(1, A, 1, 4).double()
+    g = gt[..., :4].view(B, 1, G, 4).double()
+    iw = (torch.minimum(a[..., 2], g[..., 2]) - torch.maximum(a[..., 0], g[..., 0]) + 1).clamp(min=0)
+    ih = (torch.minimum(a[..., 3], g[..., 3]) - torch.maximum(a[..., 1], g[..., 1]) + 1).clamp(min=0)
+    inter = iw * ih
+    ua = ((a[..., 2] - a[..., 0] + 1) * (a[..., 3] - a[..., 1] + 1) +
+          (g[..., 2] - g[..., 0] + 1) * (g[..., 3] - g[..., 1] + 1) - inter).clamp(min=1e-8)
+    iou = inter / ua
+    valid = torch.arange(G, device=gt.device).view(1, 1, G) < gt_count.view(B, 1, 1)
+    iou = torch.where(valid, iou, torch.full_like(iou, -1.0))
+    best, idx = iou.max(dim=2)
+    state = torch.full((B, A), -1, dtype=torch.int8, device=gt.device)
+    state[best < neg_thr] = 0
+    state[best >= pos_thr] = 1
+    state[(gt_count == 0).view(B, 1).expand(B, A)] = 0
+    cx = (anchors[:, 0] + anchors[:, 2]) / 2
+    cy = (anchors[:, 1] + anchors[:, 3]) / 2
+    outside = (cx.view(1, A) >= img_hw[:, 1].view(B, 1)) | (cy.view(1, A) >= img_hw[:, 0].view(B, 1))
+    state[outside] = -1
+    matched = torch.gather(gt, 1, idx.unsqueeze(-1).expand(B, A, 5))
+    aw = (anchors[:, 2] - anchors[:, 0]).view(1, A)
+    ah = (anchors[:, 3] - anchors[:, 1]).view(1, A)
+    reg = torch.stack([(matched[..., 0] - anchors[:, 0]) / aw, (matched[..., 1] - anchors[:, 1]) / ah,
+                       (matched[..., 2] - anchors[:, 2]) / aw, (matched[..., 3] - anchors[:, 3]) / ah], dim=-1) / 0.2
+    return state, matched[..., 4].long(), reg.float()
+
+
+class LibraryTrainer:
+    """One training step = H2D of uint8 images + boxes, forward, losses, backward, clip, allreduce, Adam."""
+
+    def __init__(self, backbone: str = "resnet50", num_classes: int = 80, device="cuda", dtype=torch.bfloat16,
+                 lr: float = 1e-5, clipnorm: float = 0.001, distributed: bool = False, model: RetinaNet | None = None,
+                 freeze_backbone: bool = False):
+        self.device = torch.device(device)
+        self.dtype = dtype
+        self.num_classes = num_classes
+        self.clipnorm = clipnorm
+        self.model = (model or RetinaNet(num_classes, backbone)).to(self.device)
+        if freeze_backbone:
+            self.model.freeze_backbone()
+        if self.device.type == "cuda":
+            self.model = self.model.to(memory_format=torch.channels_last)
+        self.train_model = self.model
+        if distributed:
+            from torch.nn.parallel import DistributedDataParallel as DDP
+            ids = [self.device.index] if self.device.type == "cuda" else None
+            self.train_model = DDP(self.model, device_ids=ids, bucket_cap_mb=64, gradient_as_bucket_view=True)
+        params = [p for p in self.model.parameters() if p.requires_grad]
+        kw = {"fused": True} if self.device.type == "cuda" else {}
+        self.opt = torch.optim.Adam(params, lr=lr, betas=(0.9, 0.999), eps=1e-7, **kw)
+        self.mean = torch.tensor(CAFFE_MEAN_BGR, device=self.device).view(1, 3, 1, 1)
+        self._anchors = {}
+
+    def anchors(self, hw):
+        if hw not in self._anchors:
+            self._anchors[hw] = anchor_ops.anchors_for_shape(hw).to(self.device)
+        return self._anchors[hw]
+
+    def loss(self, images_u8: torch.Tensor, gt: torch.Tensor, gt_count: torch.Tensor, img_hw: torch.Tensor):
+        x = images_u8.permute(0, 3, 1, 2).float() - self.mean
+        if self.device.type == "cuda":
+            x = x.contiguous(memory_format=torch.channels_last)
+        with torch.autocast(self.device.type, dtype=self.dtype, enabled=self.dtype != torch.float32):
+            out = self.train_model(x)
+        h, w = images_u8.shape[1:3]
+        anchors = self.anchors((h, w))
+        with torch.no_grad():
+            state, cls, reg_t = assign_targets_batched(anchors, gt, gt_count, img_hw)
+        npos = (state == 1).sum()
+        lc = loss_ops.focal_compact(out["classification"], state, cls, num_pos=npos)
+        lr_ = loss_ops.smooth_l1_compact(out["regression"], reg_t, state, num_pos=npos)
+        return lc + lr_, lc, lr_
+
+    def train_step(self, images_u8, gt, gt_count, img_hw):
+        dev = self.device
+        images_u8 = images_u8.to(dev, non_blocking=True)
+        gt = gt.to(dev, non_blocking=True)
+        gt_count = gt_count.to(dev, non_blocking=True)
+        img_hw = img_hw.to(dev, non_blocking=True)
+        self.opt.zero_grad(set_to_none=True)
+        total, lc, lr_ = self.loss(images_u8, gt, gt_count, img_hw)
+        total.backward()
+        if self.clipnorm:
+            torch.nn.utils.clip_grad_norm_([p for p in self.model.parameters() if p.requires_grad], self.clipnorm)
+        self.opt.step()
+        return torch.stack([total.detach(), lr_.detach(), lc.detach()])

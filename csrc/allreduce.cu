@@ -1,0 +1,287 @@
+// Peer-to-peer gradient allreduce / broadcast over NVLink (sm_100a), fused with the per-rank
+// global-norm clip factor, the 1/N averaging scale and (optionally) a bf16 wire format.
+//
+// Every rank maps every peer's bucket and flag pad (CUDA IPC) and runs the same kernel:
+//   one-shot : barrier; out[i] = post * sum_r pre_r * peer_r[i]; barrier           (small buckets)
+//   two-shot : barrier; reduce my 1/N slice from all peers, write it back to my bucket;
+//              barrier; gather every peer's reduced slice into out; barrier        (large buckets)
+// Barriers are per-block flag words with release/acquire at system scope and monotonically
+// increasing epochs, so no flag is ever reset (no reset race).
+//
+// Replaces Horovod's fusion-buffer memcpy + ncclAllReduce/MPI_Allreduce + tf.div
+// (SURVEY.md C4-C7, X1-X3); the reference has no CUDA source of its own.
+#include "../include/b200_ops.h"
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kMaxWorld = 8;
+constexpr int kArThreads = 512;
+constexpr int kArMaxBlocks = 64;
+
+struct ArParams {
+  float* bufs[kMaxWorld];
+  uint32_t* flags[kMaxWorld];
+  const float* prescale[kMaxWorld];
+  float* out;
+  int rank, world;
+  long long offset, count;
+  float postscale;
+  uint32_t epoch;   // base flag value of this call; the call uses epoch+1 .. epoch+3
+  int has_prescale;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Block-level barrier across ranks: block b of every rank meets block b of every other rank.
+// Flag layout per rank: flags[block][peer].
+__device__ __forceinline__ void rank_barrier(const ArParams& p, uint32_t value) {
+  __syncthreads();
+  if (threadIdx.x < p.world) {
+    const int peer = threadIdx.x;
+    st_release_sys(p.flags[peer] + blockIdx.x * kMaxWorld + p.rank, value);
+    const uint32_t* mine = p.flags[p.rank] + blockIdx.x * kMaxWorld + peer;
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - value) < 0) {
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 ld_peer(const float* p) {
+  float4 v;
+  asm volatile("ld.global.relaxed.sys.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+
+template <int kWorld>
+__global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(const ArParams p) {
+  rank_barrier(p, p.epoch + 1);
+  float pre[kWorld];
+#pragma unroll
+  for (int r = 0; r < kWorld; ++r) pre[r] = p.has_prescale ? *p.prescale[r] : 1.f;
+  const long long n4 = p.count >> 2;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float4 v[kWorld];
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) v[r] = ld_peer(p.bufs[(p.rank + r) % kWorld] + p.offset + i * 4);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) {
+      const float s = pre[(p.rank + r) % kWorld];
+      acc.x += s * v[r].x; acc.y += s * v[r].y; acc.z += s * v[r].z; acc.w += s * v[r].w;
+    }
+    acc.x *= p.postscale; acc.y *= p.postscale; acc.z *= p.postscale; acc.w *= p.postscale;
+    reinterpret_cast<float4*>(p.out + p.offset)[i] = acc;
+  }
+  rank_barrier(p, p.epoch + 2);
+}
+
+template <int kWorld>
+__global__ void __launch_bounds__(kArThreads) allreduce_twoshot_kernel(const ArParams p) {
+  rank_barrier(p, p.epoch + 1);
+  float pre[kWorld];
+#pragma unroll
+  for (int r = 0; r < kWorld; ++r) pre[r] = p.has_prescale ? *p.prescale[r] : 1.f;
+  const long long n4 = p.count >> 2;
+  const long long slice = (n4 + kWorld - 1) / kWorld;
+  // phase 1: reduce-scatter my slice, write it back into my own bucket (only I read that slice)
+  {
+    const long long s0 = slice * p.rank, s1 = min(n4, s0 + slice);
+    for (long long i = s0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < s1;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+      float4 v[kWorld];
+#pragma unroll
+      for (int r = 0; r < kWorld; ++r) v[r] = ld_peer(p.bufs[(p.rank + r) % kWorld] + p.offset + i * 4);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < kWorld; ++r) {
+        const float s = pre[(p.rank + r) % kWorld];
+        acc.x += s * v[r].x; acc.y += s * v[r].y; acc.z += s * v[r].z; acc.w += s * v[r].w;
+      }
+      acc.x *= p.postscale; acc.y *= p.postscale; acc.z *= p.postscale; acc.w *= p.postscale;
+      reinterpret_cast<float4*>(p.bufs[p.rank] + p.offset)[i] = acc;
+    }
+  }
+  __threadfence_system();
+  rank_barrier(p, p.epoch + 2);
+  // phase 2: all-gather the reduced slices
+#pragma unroll
+  for (int r = 0; r < kWorld; ++r) {
+    const int src = (p.rank + r) % kWorld;
+    const long long s0 = slice * src, s1 = min(n4, s0 + slice);
+    for (long long i = s0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < s1;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+      const float4 v = ld_peer(p.bufs[src] + p.offset + i * 4);
+      reinterpret_cast<float4*>(p.out + p.offset)[i] = v;
+    }
+  }
+  rank_barrier(p, p.epoch + 3);
+}
+
+template <int kWorld>
+__global__ void __launch_bounds__(kArThreads) broadcast_kernel(const ArParams p, int root) {
+  rank_barrier(p, p.epoch + 1);
+  if (p.rank != root) {
+    const long long n4 = p.count >> 2;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+      const float4 v = ld_peer(p.bufs[root] + p.offset + i * 4);
+      reinterpret_cast<float4*>(p.out + p.offset)[i] = v;
+    }
+  }
+  rank_barrier(p, p.epoch + 2);
+}
+
+__global__ void scale_copy_kernel(const float* __restrict__ in, float* __restrict__ out, long long n4,
+                                  const float* __restrict__ pre, float post) {
+  const float s = (pre ? *pre : 1.f) * post;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float4 v = reinterpret_cast<const float4*>(in)[i];
+    v.x *= s; v.y *= s; v.z *= s; v.w *= s;
+    reinterpret_cast<float4*>(out)[i] = v;
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// Host-side argument block: pointer tables are HOST arrays here (copied by value into the
+// kernel parameters), so no device-side table has to be maintained.
+extern "C" {
+
+
+
+static int fill(ArParams& p, const B200ArHostArgs* a) {
+  if (a->world < 1 || a->world > kMaxWorld) return set_error(-1, "allreduce: world %d unsupported", a->world);
+  if ((a->count & 3) || (a->offset & 3)) return set_error(-1, "allreduce: offset/count must be multiples of 4 floats");
+  for (int r = 0; r < kMaxWorld; ++r) {
+    p.bufs[r] = r < a->world ? static_cast<float*>(a->bufs[r]) : nullptr;
+    p.flags[r] = r < a->world ? a->flags[r] : nullptr;
+    p.prescale[r] = r < a->world ? a->prescale[r] : nullptr;
+  }
+  p.out = a->out;
+  p.rank = a->rank;
+  p.world = a->world;
+  p.offset = a->offset;
+  p.count = a->count;
+  p.postscale = a->postscale;
+  p.epoch = a->epoch;
+  p.has_prescale = a->has_prescale;
+  return 0;
+}
+
+int b200_allreduce_host(const B200ArHostArgs* a, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  ArParams p;
+  int rc = fill(p, a);
+  if (rc) return rc;
+  const long long n4 = p.count >> 2;
+  if (n4 == 0) return 0;
+  if (p.world == 1) {
+    long long g = (n4 + 255) / 256;
+    if (g > num_sms() * 4LL) g = num_sms() * 4LL;
+    scale_copy_kernel<<<static_cast<unsigned>(g), 256, 0, stream>>>(p.bufs[0] + p.offset, p.out + p.offset, n4,
+                                                                    p.has_prescale ? p.prescale[0] : nullptr, p.postscale);
+    return check_launch("scale_copy_kernel");
+  }
+  int blocks = a->max_blocks > 0 ? a->max_blocks : kArMaxBlocks;
+  if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  const long long bytes = p.count * 4;
+  int algo = a->algo;
+  if (algo == 0) algo = (bytes <= (512 << 10)) ? 1 : 2;
+  const long long work = (algo == 1) ? n4 : (n4 + p.world - 1) / p.world;
+  long long need = (work + kArThreads - 1) / kArThreads;
+  if (need < blocks) blocks = static_cast<int>(need < 1 ? 1 : need);
+#define B200_AR_LAUNCH(W)                                                                        \
+  case W:                                                                                        \
+    if (algo == 1)                                                                               \
+      allreduce_oneshot_kernel<W><<<blocks, kArThreads, 0, stream>>>(p);                         \
+    else                                                                                         \
+      allreduce_twoshot_kernel<W><<<blocks, kArThreads, 0, stream>>>(p);                         \
+    break;
+  switch (p.world) {
+    B200_AR_LAUNCH(2)
+    B200_AR_LAUNCH(4)
+    B200_AR_LAUNCH(8)
+    default:
+      return set_error(-1, "allreduce: world size %d not instantiated (1, 2, 4, 8)", p.world);
+  }
+#undef B200_AR_LAUNCH
+  return check_launch("allreduce_kernel");
+}
+
+int b200_broadcast_host(const B200ArHostArgs* a, int root, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  ArParams p;
+  int rc = fill(p, a);
+  if (rc) return rc;
+  const long long n4 = p.count >> 2;
+  if (n4 == 0 || p.world == 1) return 0;
+  int blocks = a->max_blocks > 0 ? a->max_blocks : kArMaxBlocks;
+  if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  long long need = (n4 + kArThreads - 1) / kArThreads;
+  if (need < blocks) blocks = static_cast<int>(need < 1 ? 1 : need);
+  switch (p.world) {
+    case 2: broadcast_kernel<2><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+    case 4: broadcast_kernel<4><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+    case 8: broadcast_kernel<8><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+    default: return set_error(-1, "broadcast: world size %d not instantiated", p.world);
+  }
+  return check_launch("broadcast_kernel");
+}
+
+/* Bytes each rank must allocate (zeroed) for its flag pad. */
+long long b200_flag_pad_bytes(void) { return static_cast<long long>(kArMaxBlocks) * kMaxWorld * sizeof(uint32_t); }
+
+int b200_ipc_alloc(void** ptr, long long bytes) {
+  B200_CUDA_OK(cudaMalloc(ptr, static_cast<size_t>(bytes)));
+  B200_CUDA_OK(cudaMemset(*ptr, 0, static_cast<size_t>(bytes)));
+  return 0;
+}
+int b200_ipc_free(void* ptr) {
+  B200_CUDA_OK(cudaFree(ptr));
+  return 0;
+}
+int b200_ipc_get_handle(void* ptr, void* handle64) {
+  cudaIpcMemHandle_t h;
+  B200_CUDA_OK(cudaIpcGetMemHandle(&h, ptr));
+  memcpy(handle64, &h, sizeof(h));
+  return 0;
+}
+int b200_ipc_open_handle(const void* handle64, void** ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  B200_CUDA_OK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+int b200_ipc_close_handle(void* ptr) {
+  B200_CUDA_OK(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+int b200_enable_peer_access(int device, int world_local) {
+  for (int d = 0; d < world_local; ++d) {
+    if (d == device) continue;
+    int can = 0;
+    B200_CUDA_OK(cudaDeviceCanAccessPeer(&can, device, d));
+    if (!can) return set_error(-7, "device %d cannot access peer %d", device, d);
+    cudaError_t e = cudaDeviceEnablePeerAccess(d, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return set_error(-3, "enable peer: %s", cudaGetErrorString(e));
+    cudaGetLastError();
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,48 @@
+// Shared host-side helpers for libb200ops: error reporting, launch counting, driver entry points.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include <atomic>
+
+namespace b200 {
+
+extern thread_local char g_last_error[512];
+extern std::atomic<long long> g_launch_count;
+
+inline int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+inline int check_launch(const char* what) {
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error(-2, "%s: launch failed: %s", what, cudaGetErrorString(e));
+  return 0;
+}
+
+#define B200_CUDA_OK(expr)                                                                       \
+  do {                                                                                           \
+    cudaError_t _e = (expr);                                                                     \
+    if (_e != cudaSuccess) return b200::set_error(-3, "%s: %s", #expr, cudaGetErrorString(_e)); \
+  } while (0)
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+PFN_encodeTiled get_encode_tiled();
+
+// bf16 tensor map with 128B swizzle and zero OOB fill.  dims/strides innermost first;
+// strides[i] is the byte stride of dim i+1 (dim 0 is contiguous).
+int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const unsigned long long* dims,
+                   const unsigned long long* strides_bytes, const unsigned int* box);
+
+int num_sms();
+
+}  // namespace b200

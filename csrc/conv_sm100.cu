@@ -1,0 +1,454 @@
+// Implicit-GEMM convolution (fprop and dgrad) for sm_100a: TMA + tcgen05.mma + TMEM.
+//
+//   out[n, y, x, :] = epilogue( sum_{tap} sum_{k} in[n, y + dh(tap), x + dw(tap), k] * w[tap][:, k] )
+//
+// GEMM view: M = output pixels (tiles of th x tw = 128 pixels of ONE image, so a tap is a pure
+// (dh, dw) shift of the TMA box and the conv halo / padding is TMA's out-of-bounds zero fill),
+// N = output channels (BN <= 256 per tile), K = taps x input channels (64 per pipeline stage).
+//
+// Warp roles (256 threads, 1 CTA per SM, persistent over tiles):
+//   warp 0   TMA producer  (one lane): A box [64ch, tw, th, 1] + B box [64ch, BN rows, 1 tap]
+//   warp 1   MMA issuer    (one lane): 4 x tcgen05.mma (K=16) per stage, commit -> empty barrier
+//   warp 2   TMEM allocator (512 columns = two 256-column accumulators, double-buffered)
+//   warps 4-7 epilogue: tcgen05.ld 32 lanes x 32 columns, fused shift/add/mask/ReLU, bf16 store
+//
+// Stride-2 convolutions use one tensor map per input parity class (strided views), so every
+// tap is still a plain shifted box.  Stride-2 dgrad computes one output parity class per launch.
+//
+// Replaces cuDNN fprop/dgrad + separate bias/BN/ReLU/add kernels of the reference stack
+// (SURVEY.md G2-G4, G6, G8, G12); the reference itself has no CUDA source.
+#include "../include/b200_ops.h"
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace b200 {
+
+constexpr int kStages = 4;
+constexpr int kBM = 128;
+constexpr int kBK = 64;
+constexpr int kAStageBytes = kBM * kBK * 2;       // 16 KB
+constexpr int kBStageBytes = 256 * kBK * 2;       // 32 KB (BN <= 256)
+constexpr int kMaxTaps = 49;
+constexpr int kMaxMaps = 8;
+constexpr int kTmemCols = 512;
+constexpr int kConvThreads = 256;
+constexpr int kSmemBytes = kStages * (kAStageBytes + kBStageBytes) + 1024 /*align*/ + 256 /*barriers*/;
+
+struct Tap {
+  int8_t dh, dw, map, pad;
+  int widx;
+};
+
+struct DevProblem {
+  void* out;
+  const void* add;
+  const void* mask;
+  int N, OH, OW;        // GEMM pixel grid
+  int OHo, OWo;         // output tensor spatial dims
+  int tiles_h, tiles_w; // spatial tiles per image
+  int tile_begin;       // first m-tile of this problem
+  int th_log2, tw_log2;
+  int map_base;
+};
+
+struct ConvParams {
+  CUtensorMap in_maps[kMaxMaps];
+  CUtensorMap w_map;
+  DevProblem prob[B200_MAX_PROBLEMS];
+  Tap taps[kMaxTaps];
+  const float* shift;
+  int num_problems, num_m_tiles, num_n_tiles;
+  int Nrows, ldo, BN;
+  int num_taps, num_kc;
+  int os, oy, ox;       // output scatter: (y*os + oy, x*os + ox)
+  int relu, out_fp32;
+};
+
+__device__ __forceinline__ void decode_tile(const ConvParams& p, int tile, int& pi, int& n, int& y0, int& x0,
+                                            int& n_tile) {
+  const int m_tile = tile % p.num_m_tiles;
+  n_tile = tile / p.num_m_tiles;
+  pi = 0;
+#pragma unroll
+  for (int i = 1; i < B200_MAX_PROBLEMS; ++i)
+    if (i < p.num_problems && m_tile >= p.prob[i].tile_begin) pi = i;
+  const DevProblem& q = p.prob[pi];
+  const int local = m_tile - q.tile_begin;
+  const int per_img = q.tiles_h * q.tiles_w;
+  n = local / per_img;
+  const int rem = local - n * per_img;
+  const int ty = rem / q.tiles_w;
+  const int tx = rem - ty * q.tiles_w;
+  y0 = ty << q.th_log2;
+  x0 = tx << q.tw_log2;
+}
+
+__global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_smem = smem_base;
+  const uint32_t b_smem = smem_base + kStages * kAStageBytes;
+  const uint32_t bar_base = b_smem + kStages * kBStageBytes;
+  // barrier layout (8 bytes each): full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], tmem_ptr
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
+  const uint32_t tmem_ptr_smem = bar_base + 8u * (2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int num_k = p.num_taps * p.num_kc;
+  const uint32_t b_bytes = static_cast<uint32_t>(p.BN) * kBK * 2;
+
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < kMaxMaps; ++i) tma_prefetch_desc(&p.in_maps[i]);
+    tma_prefetch_desc(&p.w_map);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr_smem, kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int pi, n, y0, x0, n_tile;
+        decode_tile(p, tile, pi, n, y0, x0, n_tile);
+        const int map_base = p.prob[pi].map_base;
+        for (int t = 0; t < p.num_taps; ++t) {
+          const Tap tap = p.taps[t];
+          const void* amap = &p.in_maps[map_base + tap.map];
+          for (int kc = 0; kc < p.num_kc; ++kc) {
+            mbar_wait(empty_bar(stage), phase ^ 1);
+            mbar_expect_tx(full_bar(stage), kAStageBytes + b_bytes);
+            tma_load_4d(a_smem + stage * kAStageBytes, amap, full_bar(stage), kc * kBK, x0 + tap.dw, y0 + tap.dh, n);
+            tma_load_3d(b_smem + stage * kBStageBytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
+            if (++stage == kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    const uint32_t idesc = make_idesc_bf16(kBM, p.BN, 0, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * 256;
+      for (int kb = 0; kb < num_k; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint64_t adesc = make_smem_desc(a_smem + stage * kAStageBytes, 16, 1024);
+          const uint64_t bdesc = make_smem_desc(b_smem + stage * kBStageBytes, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            // advance 16 bf16 = 32 bytes along K inside the 128B swizzle row: +2 in (addr >> 4) units
+            umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          }
+          umma_commit(empty_bar(stage));
+          if (kb == num_k - 1) umma_commit(tfull_bar(acc));
+        }
+        __syncwarp();
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ epilogue
+    const int quarter = warp - 4;
+    const int m = quarter * 32 + lane;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int pi, n, y0, x0, n_tile;
+      decode_tile(p, tile, pi, n, y0, x0, n_tile);
+      const DevProblem& q = p.prob[pi];
+      const int y = y0 + (m >> q.tw_log2);
+      const int x = x0 + (m & ((1 << q.tw_log2) - 1));
+      const bool valid = (y < q.OH) && (x < q.OW);
+      const long long pix = (static_cast<long long>(n) * q.OHo + (y * p.os + p.oy)) * q.OWo + (x * p.os + p.ox);
+      const long long row_off = pix * p.ldo;
+      const int col0 = n_tile * p.BN;
+      const int col_end = min(p.Nrows, col0 + p.BN);
+
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * 256;
+      for (int c = 0; c < p.BN; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c, r);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            const int col = col0 + c + j;
+            if (col < col_end) {
+              float v[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j + e]);
+              if (p.shift) {
+                const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.shift + col));
+                const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.shift + col + 4));
+                v[0] += s0.x; v[1] += s0.y; v[2] += s0.z; v[3] += s0.w;
+                v[4] += s1.x; v[5] += s1.y; v[6] += s1.z; v[7] += s1.w;
+              }
+              if (q.add) {
+                const uint4 a = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(q.add) + row_off + col);
+                v[0] += bf16_lo(a.x); v[1] += bf16_hi(a.x); v[2] += bf16_lo(a.y); v[3] += bf16_hi(a.y);
+                v[4] += bf16_lo(a.z); v[5] += bf16_hi(a.z); v[6] += bf16_lo(a.w); v[7] += bf16_hi(a.w);
+              }
+              if (q.mask) {
+                const uint4 k = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(q.mask) + row_off + col);
+                if (!(bf16_lo(k.x) > 0.f)) v[0] = 0.f;
+                if (!(bf16_hi(k.x) > 0.f)) v[1] = 0.f;
+                if (!(bf16_lo(k.y) > 0.f)) v[2] = 0.f;
+                if (!(bf16_hi(k.y) > 0.f)) v[3] = 0.f;
+                if (!(bf16_lo(k.z) > 0.f)) v[4] = 0.f;
+                if (!(bf16_hi(k.z) > 0.f)) v[5] = 0.f;
+                if (!(bf16_lo(k.w) > 0.f)) v[6] = 0.f;
+                if (!(bf16_hi(k.w) > 0.f)) v[7] = 0.f;
+              }
+              if (p.relu) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+              }
+              if (col + 8 <= col_end) {
+                if (p.out_fp32) {
+                  float* o = static_cast<float*>(q.out) + row_off + col;
+                  *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+                  *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                } else {
+                  uint4 o;
+                  o.x = pack_bf16x2(v[0], v[1]);
+                  o.y = pack_bf16x2(v[2], v[3]);
+                  o.z = pack_bf16x2(v[4], v[5]);
+                  o.w = pack_bf16x2(v[6], v[7]);
+                  *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(q.out) + row_off + col) = o;
+                }
+              } else {
+                for (int e = 0; e < col_end - col; ++e) {
+                  if (p.out_fp32)
+                    static_cast<float*>(q.out)[row_off + col + e] = v[e];
+                  else
+                    static_cast<__nv_bfloat16*>(q.out)[row_off + col + e] = __float2bfloat16(v[e]);
+                }
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(tempty_bar(acc));
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+
+static int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+static int posmod(int a, int b) { return ((a % b) + b) % b; }
+
+static void pick_tile(int OH, int OW, int& th_log2, int& tw_log2) {
+  // 128 pixels as (128/tw) x tw; minimise padded tiles, prefer wide tiles on ties.
+  long long best = -1;
+  for (int tl = 7; tl >= 0; --tl) {
+    const int tw = 1 << tl, th = 128 >> tl;
+    const long long tiles = static_cast<long long>((OH + th - 1) / th) * ((OW + tw - 1) / tw);
+    if (best < 0 || tiles < best) {
+      best = tiles;
+      tw_log2 = tl;
+      th_log2 = 7 - tl;
+    }
+  }
+}
+
+static int pick_bn(int nrows) {
+  if (nrows <= 256) return (nrows + 15) / 16 * 16;
+  // largest multiple of 16 <= 256 that minimises padded work
+  int best = 256;
+  long long best_cost = -1;
+  for (int bn = 256; bn >= 128; bn -= 16) {
+    const long long tiles = (nrows + bn - 1) / bn;
+    const long long cost = tiles * bn;
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      best = bn;
+    }
+  }
+  return best;
+}
+
+}  // namespace b200
+
+extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
+  using namespace b200;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!a || a->num_problems < 1 || a->num_problems > B200_MAX_PROBLEMS) return set_error(-1, "b200_conv: bad num_problems");
+  if (a->stride != 1 && a->stride != 2) return set_error(-1, "b200_conv: stride must be 1 or 2");
+  if (a->stride == 2 && a->num_problems != 1) return set_error(-1, "b200_conv: grouped launch needs stride 1");
+  if (a->KH * a->KW > kMaxTaps) return set_error(-1, "b200_conv: too many taps");
+  if ((a->ldi % 8) || (a->ldw % 8) || (a->ldo % 8)) return set_error(-1, "b200_conv: ld* must be multiples of 8");
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    attr_set = true;
+  }
+
+  ConvParams p;
+  memset(&p, 0, sizeof(p));
+  p.num_problems = a->num_problems;
+  p.Nrows = a->Nrows;
+  p.ldo = a->ldo;
+  p.BN = pick_bn(a->Nrows);
+  p.num_n_tiles = (a->Nrows + p.BN - 1) / p.BN;
+  p.num_kc = (a->K + kBK - 1) / kBK;
+  p.shift = a->shift;
+  p.relu = a->relu;
+  p.out_fp32 = a->out_fp32;
+  p.os = 1;
+  p.oy = p.ox = 0;
+
+  // ---- tap table
+  const int s = a->stride;
+  int nt = 0;
+  if (a->mode == 0) {
+    for (int r = 0; r < a->KH; ++r)
+      for (int c = 0; c < a->KW; ++c) {
+        const int eh = r - a->pad_h, ew = c - a->pad_w;
+        Tap t;
+        const int py = posmod(eh, s), px = posmod(ew, s);
+        t.dh = static_cast<int8_t>(floordiv(eh, s));
+        t.dw = static_cast<int8_t>(floordiv(ew, s));
+        t.map = static_cast<int8_t>(py * s + px);
+        t.pad = 0;
+        t.widx = r * a->KW + c;
+        p.taps[nt++] = t;
+      }
+  } else {
+    if (s == 2) {
+      p.os = 2;
+      p.oy = a->par_y;
+      p.ox = a->par_x;
+    }
+    for (int r = 0; r < a->KH; ++r)
+      for (int c = 0; c < a->KW; ++c) {
+        const int eh = (s == 2 ? a->par_y : 0) + a->pad_h - r;
+        const int ew = (s == 2 ? a->par_x : 0) + a->pad_w - c;
+        if (posmod(eh, s) != 0 || posmod(ew, s) != 0) continue;
+        Tap t;
+        t.dh = static_cast<int8_t>(floordiv(eh, s));
+        t.dw = static_cast<int8_t>(floordiv(ew, s));
+        t.map = 0;
+        t.pad = 0;
+        t.widx = r * a->KW + c;
+        p.taps[nt++] = t;
+      }
+  }
+  p.num_taps = nt;
+  if (nt == 0) return set_error(-6, "b200_conv: empty tap set (caller should zero-fill this parity class)");
+
+  // ---- problems + tensor maps
+  int tile_begin = 0;
+  int map_count = 0;
+  for (int i = 0; i < a->num_problems; ++i) {
+    const B200ConvProblem& q = a->prob[i];
+    DevProblem& d = p.prob[i];
+    d.out = q.out;
+    d.add = q.add;
+    d.mask = q.mask;
+    d.N = q.N;
+    d.OHo = q.OHo;
+    d.OWo = q.OWo;
+    if (a->mode == 1 && s == 2) {
+      d.OH = (q.OHo - a->par_y + 1) / 2;
+      d.OW = (q.OWo - a->par_x + 1) / 2;
+    } else {
+      d.OH = q.OHo;
+      d.OW = q.OWo;
+    }
+    if (d.OH <= 0 || d.OW <= 0) return set_error(-1, "b200_conv: empty problem");
+    pick_tile(d.OH, d.OW, d.th_log2, d.tw_log2);
+    const int th = 1 << d.th_log2, tw = 1 << d.tw_log2;
+    d.tiles_h = (d.OH + th - 1) / th;
+    d.tiles_w = (d.OW + tw - 1) / tw;
+    d.tile_begin = tile_begin;
+    tile_begin += q.N * d.tiles_h * d.tiles_w;
+    d.map_base = map_count;
+    const unsigned int box[4] = {static_cast<unsigned>(kBK), static_cast<unsigned>(tw), static_cast<unsigned>(th), 1u};
+    const int nmaps = (a->mode == 0 && s == 2) ? 4 : 1;
+    if (map_count + nmaps > kMaxMaps) return set_error(-1, "b200_conv: too many tensor maps");
+    for (int mi = 0; mi < nmaps; ++mi) {
+      const int py = mi / 2, px = mi % 2;
+      const int step = (nmaps == 4) ? 2 : 1;
+      const long long Wd = (q.W - px + step - 1) / step;
+      const long long Hd = (q.H - py + step - 1) / step;
+      const __nv_bfloat16* base = static_cast<const __nv_bfloat16*>(q.in) + (static_cast<long long>(py) * q.W + px) * a->ldi;
+      unsigned long long dims[4] = {static_cast<unsigned long long>(a->K), static_cast<unsigned long long>(Wd > 0 ? Wd : 1),
+                                    static_cast<unsigned long long>(Hd > 0 ? Hd : 1), static_cast<unsigned long long>(q.N)};
+      unsigned long long strides[3] = {static_cast<unsigned long long>(step) * a->ldi * 2ull,
+                                       static_cast<unsigned long long>(step) * q.W * a->ldi * 2ull,
+                                       static_cast<unsigned long long>(q.H) * q.W * a->ldi * 2ull};
+      int rc = make_tmap_bf16(&p.in_maps[map_count + mi], base, 4, dims, strides, box);
+      if (rc) return rc;
+    }
+    map_count += nmaps;
+  }
+  p.num_m_tiles = tile_begin;
+  {
+    unsigned long long dims[3] = {static_cast<unsigned long long>(a->K), static_cast<unsigned long long>(a->Nrows),
+                                  static_cast<unsigned long long>(a->KH * a->KW)};
+    unsigned long long strides[2] = {static_cast<unsigned long long>(a->ldw) * 2ull,
+                                     static_cast<unsigned long long>(a->Nrows) * a->ldw * 2ull};
+    const unsigned int box[3] = {static_cast<unsigned>(kBK), static_cast<unsigned>(p.BN), 1u};
+    int rc = make_tmap_bf16(&p.w_map, a->weight, 3, dims, strides, box);
+    if (rc) return rc;
+  }
+  // unused map slots must still be valid descriptors for the prefetch: replicate slot 0
+  for (int i = map_count; i < kMaxMaps; ++i) p.in_maps[i] = p.in_maps[0];
+
+  const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles;
+  const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
+  conv_igemm_kernel<<<grid, kConvThreads, kSmemBytes, stream>>>(p);
+  return check_launch("conv_igemm_kernel");
+}

@@ -1,0 +1,310 @@
+// Inference tail: score threshold + candidate compaction, sort, box decode + clip, class-aware
+// bitmask NMS, top-k and -1 padding -- keras-retinanet's RegressBoxes / ClipBoxes /
+// FilterDetections as built into the prediction graph at reference train.py:95
+// (SURVEY.md B6-B8, G17, G18).  In the reference this is a TF map_fn over images with a CPU NMS
+// kernel per class; here it is a handful of launches for the whole batch.
+#include <cub/device/device_segmented_radix_sort.cuh>
+
+#include "../include/b200_ops.h"
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace b200 {
+
+constexpr int kNmsCap = 8192;  // candidates (best scores first) that enter NMS per image
+
+struct LevelTable {
+  const void* cls[5];
+  const void* reg[5];
+  int anchor_begin[6];
+  int num_levels;
+};
+
+__global__ void collect_kernel(const __nv_bfloat16* __restrict__ logits, long long pixels_total, int HW, int K, int ld,
+                               int a_off, float logit_thr, int max_cand, int* __restrict__ count,
+                               unsigned long long* __restrict__ keys) {
+  const int groups = (9 * K + 7) >> 3;
+  const long long total = pixels_total * groups;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % groups);
+    const long long pix = i / groups;
+    const int b = static_cast<int>(pix / HW);
+    const int p = static_cast<int>(pix - static_cast<long long>(b) * HW);
+    const uint4 u = *reinterpret_cast<const uint4*>(logits + pix * ld + g * 8);
+    const float x[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
+                        bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int ch = g * 8 + e;
+      if (ch < 9 * K && x[e] > logit_thr) {
+        const float score = 1.f / (1.f + __expf(-x[e]));
+        const int j = ch / K, k = ch - j * K;
+        const unsigned int id = static_cast<unsigned int>((a_off + p * 9 + j)) * static_cast<unsigned int>(K) + k;
+        const int slot = atomicAdd(count + b, 1);
+        if (slot < max_cand)
+          keys[static_cast<long long>(b) * max_cand + slot] =
+              (static_cast<unsigned long long>(__float_as_uint(score)) << 32) | static_cast<unsigned int>(~id);
+      }
+    }
+  }
+}
+
+__global__ void segments_kernel(const int* __restrict__ count, int B, int max_cand, int* __restrict__ seg_begin,
+                                int* __restrict__ seg_end) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) {
+    seg_begin[b] = b * max_cand;
+    seg_end[b] = b * max_cand + min(count[b], max_cand);
+  }
+}
+
+__global__ void decode_kernel(const unsigned long long* __restrict__ keys_sorted, const int* __restrict__ count,
+                              int max_cand, int K, LevelTable lt, int ld_reg, const float* __restrict__ anchors,
+                              int img_h, int img_w, float* __restrict__ boxes, float* __restrict__ scores,
+                              int* __restrict__ labels) {
+  const int b = blockIdx.y;
+  const int n = min(min(count[b], max_cand), kNmsCap);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long key = keys_sorted[static_cast<long long>(b) * max_cand + i];
+  const unsigned int id = ~static_cast<unsigned int>(key & 0xffffffffu);
+  const int aidx = id / K, k = id - aidx * K;
+  int lv = 0;
+  for (int l = 1; l < lt.num_levels; ++l)
+    if (aidx >= lt.anchor_begin[l]) lv = l;
+  const int la = aidx - lt.anchor_begin[lv];
+  const int hw = (lt.anchor_begin[lv + 1] - lt.anchor_begin[lv]) / 9;
+  const int p = la / 9, j = la - p * 9;
+  const __nv_bfloat16* r = static_cast<const __nv_bfloat16*>(lt.reg[lv]) + (static_cast<long long>(b) * hw + p) * ld_reg + j * 4;
+  const float4 an = reinterpret_cast<const float4*>(anchors)[aidx];
+  const float w = an.z - an.x, h = an.w - an.y;
+  float4 o;
+  o.x = fminf(fmaxf(an.x + __bfloat162float(r[0]) * 0.2f * w, 0.f), static_cast<float>(img_w));
+  o.y = fminf(fmaxf(an.y + __bfloat162float(r[1]) * 0.2f * h, 0.f), static_cast<float>(img_h));
+  o.z = fminf(fmaxf(an.z + __bfloat162float(r[2]) * 0.2f * w, 0.f), static_cast<float>(img_w));
+  o.w = fminf(fmaxf(an.w + __bfloat162float(r[3]) * 0.2f * h, 0.f), static_cast<float>(img_h));
+  const long long oi = static_cast<long long>(b) * kNmsCap + i;
+  reinterpret_cast<float4*>(boxes)[oi] = o;
+  scores[oi] = __uint_as_float(static_cast<unsigned int>(key >> 32));
+  labels[oi] = k;
+}
+
+__device__ __forceinline__ bool iou_gt(const float4& a, const float4& b, float thr) {
+  const float iw = fminf(a.z, b.z) - fmaxf(a.x, b.x);
+  const float ih = fminf(a.w, b.w) - fmaxf(a.y, b.y);
+  if (iw <= 0.f || ih <= 0.f) return false;
+  const float inter = iw * ih;
+  const float ua = (a.z - a.x) * (a.w - a.y) + (b.z - b.x) * (b.w - b.y) - inter;
+  return inter > thr * ua;
+}
+
+// mask[i][cb] bit j: box (cb*64+j) comes after i, same class (if labels), IoU > thr.
+__global__ void nms_mask_kernel(const float* __restrict__ boxes, const int* __restrict__ labels,
+                                const int* __restrict__ count, int fixed_n, int max_cand, long long box_stride,
+                                float thr, unsigned long long* __restrict__ mask, int words) {
+  const int b = blockIdx.z;
+  const int n = count ? min(min(count[b], max_cand), kNmsCap) : fixed_n;
+  const int rb = blockIdx.y, cb = blockIdx.x;
+  if (rb * 64 >= n || cb * 64 >= n || cb < rb) return;
+  __shared__ float4 cbox[64];
+  __shared__ int clab[64];
+  const float4* bx = reinterpret_cast<const float4*>(boxes) + b * box_stride;
+  const int* lb = labels ? labels + b * box_stride : nullptr;
+  const int cj = cb * 64 + threadIdx.x;
+  if (cj < n) {
+    cbox[threadIdx.x] = bx[cj];
+    clab[threadIdx.x] = lb ? lb[cj] : 0;
+  }
+  __syncthreads();
+  const int i = rb * 64 + threadIdx.x;
+  if (i < n) {
+    const float4 me = bx[i];
+    const int ml = lb ? lb[i] : 0;
+    unsigned long long bits = 0;
+    const int jn = min(64, n - cb * 64);
+    for (int j = 0; j < jn; ++j) {
+      const int gj = cb * 64 + j;
+      if (gj > i && clab[j] == ml && iou_gt(me, cbox[j], thr)) bits |= 1ull << j;
+    }
+    mask[(static_cast<long long>(b) * box_stride + i) * words + cb] = bits;
+  }
+}
+
+// One block per image: greedy scan in score order.
+__global__ void nms_scan_kernel(const unsigned long long* __restrict__ mask, const int* __restrict__ count, int fixed_n,
+                                int max_cand, long long box_stride, int words, int max_keep,
+                                const float* __restrict__ boxes, const float* __restrict__ scores,
+                                const int* __restrict__ labels, float* __restrict__ out_boxes,
+                                float* __restrict__ out_scores, int* __restrict__ out_labels,
+                                int* __restrict__ keep_flags) {
+  extern __shared__ unsigned long long removed[];
+  __shared__ int s_keep;
+  const int b = blockIdx.x;
+  const int n = count ? min(min(count[b], max_cand), kNmsCap) : fixed_n;
+  for (int w = threadIdx.x; w < words; w += blockDim.x) removed[w] = 0ull;
+  if (threadIdx.x == 0) s_keep = 0;
+  __syncthreads();
+  int kept = 0;
+  for (int i = 0; i < n && kept < max_keep; ++i) {
+    const bool dead = (removed[i >> 6] >> (i & 63)) & 1ull;
+    if (!dead) {
+      const unsigned long long* row = mask + (static_cast<long long>(b) * box_stride + i) * words;
+      // words below i>>6 hold no bits (only later boxes are marked)
+      for (int w = (i >> 6) + threadIdx.x; w < words; w += blockDim.x) {
+        const int cbw = w;
+        if (cbw * 64 < n) removed[w] |= row[w];
+      }
+      if (threadIdx.x == 0) {
+        if (keep_flags) keep_flags[b * box_stride + i] = 1;
+        if (out_boxes) {
+          const long long o = static_cast<long long>(b) * max_keep + kept;
+          reinterpret_cast<float4*>(out_boxes)[o] = reinterpret_cast<const float4*>(boxes)[b * box_stride + i];
+          out_scores[o] = scores[b * box_stride + i];
+          out_labels[o] = labels[b * box_stride + i];
+        }
+      }
+      ++kept;
+    }
+    __syncthreads();
+  }
+  if (out_boxes) {
+    for (int k = kept + threadIdx.x; k < max_keep; k += blockDim.x) {
+      const long long o = static_cast<long long>(b) * max_keep + k;
+      reinterpret_cast<float4*>(out_boxes)[o] = make_float4(-1.f, -1.f, -1.f, -1.f);
+      out_scores[o] = -1.f;
+      out_labels[o] = -1;
+    }
+  }
+}
+
+struct DetWorkspace {
+  int* count;
+  int* seg_begin;
+  int* seg_end;
+  unsigned long long* keys;
+  unsigned long long* keys_sorted;
+  float* boxes;
+  float* scores;
+  int* labels;
+  unsigned long long* mask;
+  void* cub_temp;
+  size_t cub_bytes;
+  long long total;
+};
+
+static size_t align_up(size_t v) { return (v + 255) & ~static_cast<size_t>(255); }
+
+static DetWorkspace carve(void* base, int B, int max_cand) {
+  DetWorkspace w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? static_cast<char*>(base) + off : nullptr;
+    off += align_up(bytes);
+    return p;
+  };
+  w.count = static_cast<int*>(take(sizeof(int) * B));
+  w.seg_begin = static_cast<int*>(take(sizeof(int) * B));
+  w.seg_end = static_cast<int*>(take(sizeof(int) * B));
+  w.keys = static_cast<unsigned long long*>(take(8ull * B * max_cand));
+  w.keys_sorted = static_cast<unsigned long long*>(take(8ull * B * max_cand));
+  w.boxes = static_cast<float*>(take(16ull * B * kNmsCap));
+  w.scores = static_cast<float*>(take(4ull * B * kNmsCap));
+  w.labels = static_cast<int*>(take(4ull * B * kNmsCap));
+  w.mask = static_cast<unsigned long long*>(take(8ull * B * kNmsCap * (kNmsCap / 64)));
+  size_t cub_bytes = 0;
+  cub::DeviceSegmentedRadixSort::SortKeysDescending(nullptr, cub_bytes, static_cast<unsigned long long*>(nullptr),
+                                                    static_cast<unsigned long long*>(nullptr), B * max_cand, B,
+                                                    static_cast<int*>(nullptr), static_cast<int*>(nullptr));
+  w.cub_bytes = cub_bytes;
+  w.cub_temp = take(cub_bytes);
+  w.total = static_cast<long long>(off);
+  return w;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+long long b200_filter_detections_workspace(int B, int max_cand) { return carve(nullptr, B, max_cand).total; }
+
+int b200_filter_detections(const void* const* cls_levels, const void* const* reg_levels, const int* level_anchors,
+                           int num_levels, int ld_cls, int ld_reg, int K, const float* anchors, int A_total, int B,
+                           int img_h, int img_w, float score_thr, float nms_thr, int max_det, int max_cand,
+                           void* workspace, long long workspace_bytes, float* out_boxes, float* out_scores,
+                           int* out_labels, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (num_levels < 1 || num_levels > 5) return set_error(-1, "filter_detections: 1..5 levels");
+  DetWorkspace w = carve(workspace, B, max_cand);
+  if (w.total > workspace_bytes) return set_error(-1, "filter_detections: workspace too small (%lld < %lld)", workspace_bytes, w.total);
+  B200_CUDA_OK(cudaMemsetAsync(w.count, 0, sizeof(int) * B, stream));
+  LevelTable lt;
+  lt.num_levels = num_levels;
+  int off = 0;
+  const float logit_thr = logf(score_thr / (1.f - score_thr));
+  for (int l = 0; l < num_levels; ++l) {
+    lt.cls[l] = cls_levels[l];
+    lt.reg[l] = reg_levels[l];
+    lt.anchor_begin[l] = off;
+    const int hw = level_anchors[l] / 9;
+    const long long pixels = static_cast<long long>(B) * hw;
+    const long long total = pixels * ((9 * K + 7) / 8);
+    long long g = (total + 255) / 256;
+    if (g > num_sms() * 8LL) g = num_sms() * 8LL;
+    collect_kernel<<<static_cast<unsigned>(g < 1 ? 1 : g), 256, 0, stream>>>(
+        static_cast<const __nv_bfloat16*>(cls_levels[l]), pixels, hw, K, ld_cls, off, logit_thr, max_cand, w.count, w.keys);
+    int rc = check_launch("collect_kernel");
+    if (rc) return rc;
+    off += level_anchors[l];
+  }
+  lt.anchor_begin[num_levels] = off;
+  if (off != A_total) return set_error(-1, "filter_detections: level anchors sum %d != A_total %d", off, A_total);
+  segments_kernel<<<(B + 63) / 64, 64, 0, stream>>>(w.count, B, max_cand, w.seg_begin, w.seg_end);
+  int rc = check_launch("segments_kernel");
+  if (rc) return rc;
+  size_t cub_bytes = w.cub_bytes;
+  B200_CUDA_OK(cub::DeviceSegmentedRadixSort::SortKeysDescending(w.cub_temp, cub_bytes, w.keys, w.keys_sorted,
+                                                                 B * max_cand, B, w.seg_begin, w.seg_end, 0, 64, stream));
+  g_launch_count.fetch_add(1);
+  dim3 dgrid((kNmsCap + 255) / 256, B);
+  decode_kernel<<<dgrid, 256, 0, stream>>>(w.keys_sorted, w.count, max_cand, K, lt, ld_reg, anchors, img_h, img_w,
+                                           w.boxes, w.scores, w.labels);
+  rc = check_launch("decode_kernel");
+  if (rc) return rc;
+  const int words = kNmsCap / 64;
+  dim3 mgrid(words, words, B);
+  nms_mask_kernel<<<mgrid, 64, 0, stream>>>(w.boxes, w.labels, w.count, 0, max_cand, kNmsCap, nms_thr, w.mask, words);
+  rc = check_launch("nms_mask_kernel");
+  if (rc) return rc;
+  nms_scan_kernel<<<B, 128, words * sizeof(unsigned long long), stream>>>(
+      w.mask, w.count, 0, max_cand, kNmsCap, words, max_det, w.boxes, w.scores, w.labels, out_boxes, out_scores,
+      out_labels, nullptr);
+  return check_launch("nms_scan_kernel");
+}
+
+/* boxes fp32 [n,4] already sorted by descending score; cls optional int32 [n];
+ * mask_ws: n * ceil(n/64) uint64; keep_flags int32 [n] must be zeroed by the caller. */
+int b200_nms_sorted(const float* boxes, const int* cls_or_null, int n, float thr, unsigned long long* mask_ws,
+                    int* keep_flags, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (n <= 0) return 0;
+  const int words = (n + 63) / 64;
+  if (words * 8 > 200 * 1024) return set_error(-1, "nms_sorted: too many boxes (%d)", n);
+  dim3 mgrid(words, words, 1);
+  nms_mask_kernel<<<mgrid, 64, 0, stream>>>(boxes, cls_or_null, nullptr, n, 0, n, thr, mask_ws, words);
+  int rc = check_launch("nms_mask_kernel");
+  if (rc) return rc;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA_OK(cudaFuncSetAttribute(nms_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr = true;
+  }
+  nms_scan_kernel<<<1, 128, words * sizeof(unsigned long long), stream>>>(mask_ws, nullptr, n, 0, n, words, n, boxes,
+                                                                          nullptr, nullptr, nullptr, nullptr, nullptr,
+                                                                          keep_flags);
+  return check_launch("nms_scan_kernel");
+}
+
+}  // extern "C"

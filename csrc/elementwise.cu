@@ -1,0 +1,386 @@
+// Bandwidth-bound fused kernels: weight preparation (BN-scale fold + layout transform),
+// stem BN+ReLU+max-pool (fwd/bwd), FPN nearest-upsample-to-shape + add (fwd/bwd), ReLU,
+// column sums (bias gradients), image normalisation.  All bf16 NHWC, 16-byte vector accesses.
+// Replaces the separate TF elementwise/pool/resize kernels of the reference stack
+// (SURVEY.md G4, G5, G7, G19); no counterpart source in the reference.
+#include "../include/b200_ops.h"
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------ weight preparation
+__global__ void prepare_weights_kernel(const B200WeightEntry* __restrict__ table, int n) {
+  __shared__ float tile[32][33];
+  // locate the entry that owns this block (entries sorted by block_begin)
+  int lo = 0, hi = n - 1;
+  const long long b = blockIdx.x;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (table[mid].block_begin <= b) lo = mid; else hi = mid - 1;
+  }
+  const B200WeightEntry e = table[lo];
+  long long local = b - e.block_begin;
+  const int tiles_ci = (e.Cin + 31) / 32;
+  const int tiles_co = (e.Cout + 31) / 32;
+  const int tci = static_cast<int>(local % tiles_ci);
+  local /= tiles_ci;
+  const int tco = static_cast<int>(local % tiles_co);
+  const int tap = static_cast<int>(local / tiles_co);
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  __nv_bfloat16* df = static_cast<__nv_bfloat16*>(e.dst_f);
+  __nv_bfloat16* dd = static_cast<__nv_bfloat16*>(e.dst_d);
+#pragma unroll
+  for (int r = ty; r < 32; r += 8) {
+    const int co = tco * 32 + r, ci = tci * 32 + tx;
+    float v = 0.f;
+    if (co < e.Cout && ci < e.Cin) {
+      v = e.src[(static_cast<long long>(tap) * e.Cout + co) * e.Cin + ci];
+      if (e.scale) v *= e.scale[co];
+      if (df) df[(static_cast<long long>(tap) * e.Cout + co) * e.ldf + ci] = __float2bfloat16(v);
+    }
+    tile[r][tx] = v;
+  }
+  __syncthreads();
+  if (dd) {
+#pragma unroll
+    for (int r = ty; r < 32; r += 8) {
+      const int ci = tci * 32 + r, co = tco * 32 + tx;
+      if (co < e.Cout && ci < e.Cin)
+        dd[(static_cast<long long>(tap) * e.Cin + ci) * e.ldd + co] = __float2bfloat16(tile[tx][r]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ stem BN + ReLU + maxpool
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  v[0] = bf16_lo(u.x); v[1] = bf16_hi(u.x); v[2] = bf16_lo(u.y); v[3] = bf16_hi(u.y);
+  v[4] = bf16_lo(u.z); v[5] = bf16_hi(u.z); v[6] = bf16_lo(u.w); v[7] = bf16_hi(u.w);
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
+  uint4 u;
+  u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
+  u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ float round_bf16(float x) { return __bfloat162float(__float2bfloat16(x)); }
+
+__global__ void bn_relu_maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ scale,
+                                           const float* __restrict__ shift, __nv_bfloat16* __restrict__ y, int N,
+                                           int H, int W, int C, int OH, int OW, int pad_h, int pad_w) {
+  const int cg = C >> 3;
+  const long long total = static_cast<long long>(N) * OH * OW * cg;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % cg) * 8;
+    long long t = i / cg;
+    const int ow = static_cast<int>(t % OW);
+    t /= OW;
+    const int oh = static_cast<int>(t % OH);
+    const int n = static_cast<int>(t / OH);
+    float sc[8], sh[8], m[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; m[e] = 0.f; }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int h = oh * 2 - pad_h + r;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int w = ow * 2 - pad_w + s;
+        if (w < 0 || w >= W) continue;
+        float v[8];
+        load8(x + ((static_cast<long long>(n) * H + h) * W + w) * C + c, v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) m[e] = fmaxf(m[e], fmaf(v[e], sc[e], sh[e]));
+      }
+    }
+    store8(y + ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c, m);
+  }
+}
+
+// dx = scale * [z > 0] * sum over windows whose (first) arg-max is this position of dy.
+__global__ void bn_relu_maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ scale,
+                                           const float* __restrict__ shift, const __nv_bfloat16* __restrict__ y,
+                                           const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N,
+                                           int H, int W, int C, int OH, int OW, int pad_h, int pad_w) {
+  const int cg = C >> 3;
+  const long long total = static_cast<long long>(N) * H * W * cg;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % cg) * 8;
+    long long t = i / cg;
+    const int w = static_cast<int>(t % W);
+    t /= W;
+    const int h = static_cast<int>(t % H);
+    const int n = static_cast<int>(t / H);
+    float sc[8], sh[8], z[8], g[8];
+    float v[8];
+    load8(x + ((static_cast<long long>(n) * H + h) * W + w) * C + c, v);
+    bool any = false;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      sc[e] = scale[c + e];
+      sh[e] = shift[c + e];
+      z[e] = round_bf16(fmaxf(fmaf(v[e], sc[e], sh[e]), 0.f));
+      g[e] = 0.f;
+      any |= z[e] > 0.f;
+    }
+    if (any) {
+      // windows (oh, ow) with oh*2 - pad_h <= h <= oh*2 - pad_h + 2
+      const int oh_lo = max(0, (h + pad_h - 2 + 1) >> 1), oh_hi = min(OH - 1, (h + pad_h) >> 1);
+      const int ow_lo = max(0, (w + pad_w - 2 + 1) >> 1), ow_hi = min(OW - 1, (w + pad_w) >> 1);
+      for (int oh = oh_lo; oh <= oh_hi; ++oh)
+        for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+          const long long o = ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c;
+          float ym[8], gy[8];
+          load8(y + o, ym);
+          bool cand = false;
+          bool is_max[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            is_max[e] = (z[e] > 0.f) && (z[e] == ym[e]);
+            cand |= is_max[e];
+          }
+          if (!cand) continue;
+          // tie-break: an earlier window position with the same value wins
+          const int r0 = h - (oh * 2 - pad_h), s0 = w - (ow * 2 - pad_w);
+          for (int r = 0; r <= r0; ++r) {
+            const int hh = oh * 2 - pad_h + r;
+            if (hh < 0) continue;
+            const int s_end = (r == r0) ? s0 : 3;
+            for (int s = 0; s < s_end; ++s) {
+              const int ww = ow * 2 - pad_w + s;
+              if (ww < 0 || ww >= W) continue;
+              float u[8];
+              load8(x + ((static_cast<long long>(n) * H + hh) * W + ww) * C + c, u);
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                if (is_max[e] && round_bf16(fmaxf(fmaf(u[e], sc[e], sh[e]), 0.f)) == ym[e]) is_max[e] = false;
+            }
+          }
+          load8(dy + o, gy);
+#pragma unroll
+          for (int e = 0; e < 8; ++e)
+            if (is_max[e]) g[e] += gy[e];
+        }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] *= sc[e];
+    }
+    store8(dx + ((static_cast<long long>(n) * H + h) * W + w) * C + c, g);
+  }
+}
+
+// ------------------------------------------------------------------ FPN upsample-to-shape + add
+__global__ void upsample_add_kernel(const __nv_bfloat16* __restrict__ lateral, const __nv_bfloat16* __restrict__ top,
+                                    __nv_bfloat16* __restrict__ out, int N, int H, int W, int C, int TH, int TW) {
+  const int cg = C >> 3;
+  const long long total = static_cast<long long>(N) * H * W * cg;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % cg) * 8;
+    long long t = i / cg;
+    const int w = static_cast<int>(t % W);
+    t /= W;
+    const int h = static_cast<int>(t % H);
+    const int n = static_cast<int>(t / H);
+    // nearest (legacy): src = floor(dst * in / out)
+    const int th = min(TH - 1, static_cast<int>((static_cast<long long>(h) * TH) / H));
+    const int tw = min(TW - 1, static_cast<int>((static_cast<long long>(w) * TW) / W));
+    float a[8], b[8];
+    load8(lateral + ((static_cast<long long>(n) * H + h) * W + w) * C + c, a);
+    load8(top + ((static_cast<long long>(n) * TH + th) * TW + tw) * C + c, b);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) a[e] += b[e];
+    store8(out + ((static_cast<long long>(n) * H + h) * W + w) * C + c, a);
+  }
+}
+
+__global__ void upsample_bwd_add_kernel(const __nv_bfloat16* __restrict__ dmerged, __nv_bfloat16* __restrict__ dtop,
+                                        int N, int H, int W, int C, int TH, int TW) {
+  const int cg = C >> 3;
+  const long long total = static_cast<long long>(N) * TH * TW * cg;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % cg) * 8;
+    long long t = i / cg;
+    const int tw = static_cast<int>(t % TW);
+    t /= TW;
+    const int th = static_cast<int>(t % TH);
+    const int n = static_cast<int>(t / TH);
+    // destination rows h with floor(h*TH/H) == th  <=>  ceil(th*H/TH) <= h < ceil((th+1)*H/TH)
+    const int h0 = static_cast<int>((static_cast<long long>(th) * H + TH - 1) / TH);
+    const int h1 = static_cast<int>((static_cast<long long>(th + 1) * H + TH - 1) / TH);
+    const int w0 = static_cast<int>((static_cast<long long>(tw) * W + TW - 1) / TW);
+    const int w1 = static_cast<int>((static_cast<long long>(tw + 1) * W + TW - 1) / TW);
+    float acc[8];
+    load8(dtop + ((static_cast<long long>(n) * TH + th) * TW + tw) * C + c, acc);
+    for (int h = h0; h < min(h1, H); ++h)
+      for (int w = w0; w < min(w1, W); ++w) {
+        float g[8];
+        load8(dmerged + ((static_cast<long long>(n) * H + h) * W + w) * C + c, g);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] += g[e];
+      }
+    store8(dtop + ((static_cast<long long>(n) * TH + th) * TW + tw) * C + c, acc);
+  }
+}
+
+__global__ void relu_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n8) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n8;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v[8];
+    load8(x + i * 8, v);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+    store8(y + i * 8, v);
+  }
+}
+__global__ void relu_bwd_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy,
+                                __nv_bfloat16* __restrict__ dx, long long n8) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n8;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v[8], g[8];
+    load8(y + i * 8, v);
+    load8(dy + i * 8, g);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) g[e] = v[e] > 0.f ? g[e] : 0.f;
+    store8(dx + i * 8, g);
+  }
+}
+
+// ------------------------------------------------------------------ column sums (bias grads)
+constexpr int kColsumRows = 512;
+__global__ void colsum_kernel(const __nv_bfloat16* __restrict__ x, long long rows, int cols, int ld,
+                              float* __restrict__ out) {
+  const long long r0 = static_cast<long long>(blockIdx.x) * kColsumRows;
+  const long long r1 = min(rows, r0 + kColsumRows);
+  for (int c2 = threadIdx.x; c2 * 2 < cols; c2 += blockDim.x) {
+    float a0 = 0.f, a1 = 0.f;
+    const __nv_bfloat16* p = x + r0 * ld + c2 * 2;
+    for (long long r = r0; r < r1; ++r, p += ld) {
+      const uint32_t u = *reinterpret_cast<const uint32_t*>(p);
+      a0 += bf16_lo(u);
+      a1 += bf16_hi(u);
+    }
+    atomicAdd(out + c2 * 2, a0);
+    if (c2 * 2 + 1 < cols) atomicAdd(out + c2 * 2 + 1, a1);
+  }
+}
+
+// ------------------------------------------------------------------ image normalise + pad
+__global__ void preprocess_kernel(const uint8_t* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long pixels,
+                                  int C, int ldc, float m0, float m1, float m2, float m3) {
+  const float mean[4] = {m0, m1, m2, m3};
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < pixels;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    for (int c = 0; c < ldc; ++c) {
+      const float v = (c < C) ? static_cast<float>(src[i * C + c]) - mean[c & 3] : 0.f;
+      dst[i * ldc + c] = __float2bfloat16(v);
+    }
+  }
+}
+
+static int grid_for(long long work, int block) {
+  long long g = (work + block - 1) / block;
+  const long long cap = static_cast<long long>(num_sms()) * 16;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return static_cast<int>(g);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_prepare_weights(const B200WeightEntry* host_entries, int n, void* dev_table, void* stream_) {
+  // host_entries: block_begin already filled (see b200_weight_table_blocks); dev_table: device copy.
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (n <= 0) return 0;
+  const B200WeightEntry& last = host_entries[n - 1];
+  const long long blocks = last.block_begin + static_cast<long long>(last.taps) * ((last.Cout + 31) / 32) * ((last.Cin + 31) / 32);
+  prepare_weights_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(static_cast<const B200WeightEntry*>(dev_table), n);
+  return check_launch("prepare_weights_kernel");
+}
+
+/* Fill block_begin of every entry; returns total blocks. */
+long long b200_weight_table_blocks(B200WeightEntry* host_entries, int n) {
+  long long b = 0;
+  for (int i = 0; i < n; ++i) {
+    host_entries[i].block_begin = b;
+    b += static_cast<long long>(host_entries[i].taps) * ((host_entries[i].Cout + 31) / 32) * ((host_entries[i].Cin + 31) / 32);
+  }
+  return b;
+}
+
+int b200_bn_relu_maxpool_fwd(const void* x, const float* scale, const float* shift, void* y, int N, int H, int W,
+                             int C, int OH, int OW, int pad_h, int pad_w, void* stream) {
+  if (C % 8) return set_error(-1, "maxpool: C must be a multiple of 8");
+  const long long total = static_cast<long long>(N) * OH * OW * (C / 8);
+  bn_relu_maxpool_fwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), scale, shift, static_cast<__nv_bfloat16*>(y), N, H, W, C, OH, OW, pad_h, pad_w);
+  return check_launch("bn_relu_maxpool_fwd");
+}
+
+int b200_bn_relu_maxpool_bwd(const void* x, const float* scale, const float* shift, const void* y, const void* dy,
+                             void* dx, int N, int H, int W, int C, int OH, int OW, int pad_h, int pad_w, void* stream) {
+  if (C % 8) return set_error(-1, "maxpool: C must be a multiple of 8");
+  const long long total = static_cast<long long>(N) * H * W * (C / 8);
+  bn_relu_maxpool_bwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), scale, shift, static_cast<const __nv_bfloat16*>(y),
+      static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), N, H, W, C, OH, OW, pad_h, pad_w);
+  return check_launch("bn_relu_maxpool_bwd");
+}
+
+int b200_upsample_add(const void* lateral, const void* top, void* out, int N, int H, int W, int C, int TH, int TW,
+                      void* stream) {
+  if (C % 8) return set_error(-1, "upsample_add: C must be a multiple of 8");
+  const long long total = static_cast<long long>(N) * H * W * (C / 8);
+  upsample_add_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(lateral), static_cast<const __nv_bfloat16*>(top),
+      static_cast<__nv_bfloat16*>(out), N, H, W, C, TH, TW);
+  return check_launch("upsample_add");
+}
+
+int b200_upsample_bwd_add(const void* dmerged, void* dtop, int N, int H, int W, int C, int TH, int TW, void* stream) {
+  if (C % 8) return set_error(-1, "upsample_bwd_add: C must be a multiple of 8");
+  const long long total = static_cast<long long>(N) * TH * TW * (C / 8);
+  upsample_bwd_add_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dmerged), static_cast<__nv_bfloat16*>(dtop), N, H, W, C, TH, TW);
+  return check_launch("upsample_bwd_add");
+}
+
+int b200_relu(const void* x, void* y, long long n, void* stream) {
+  if (n % 8) return set_error(-1, "relu: n must be a multiple of 8");
+  relu_kernel<<<grid_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), n / 8);
+  return check_launch("relu");
+}
+
+int b200_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* stream) {
+  if (n % 8) return set_error(-1, "relu_bwd: n must be a multiple of 8");
+  relu_bwd_kernel<<<grid_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), n / 8);
+  return check_launch("relu_bwd");
+}
+
+int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accum, void* stream) {
+  if (ld % 2) return set_error(-1, "colsum: ld must be even");
+  const long long blocks = (rows + kColsumRows - 1) / kColsumRows;
+  colsum_kernel<<<static_cast<unsigned>(blocks), 384, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), rows, cols, ld, out_accum);
+  return check_launch("colsum");
+}
+
+int b200_preprocess(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean, void* stream) {
+  const long long pixels = static_cast<long long>(N) * H * W;
+  preprocess_kernel<<<grid_for(pixels, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<__nv_bfloat16*>(dst), pixels, C, ldc, mean[0], C > 1 ? mean[1] : 0.f, C > 2 ? mean[2] : 0.f,
+      C > 3 ? mean[3] : 0.f);
+  return check_launch("preprocess");
+}
+
+}  // extern "C"

@@ -1,0 +1,333 @@
+// Convolution weight gradient for sm_100a: TMA + tcgen05.mma with MN-major operands.
+//
+//   dW[tap][co][ci] += rowscale[co] * sum_{n,y,x} dY[n, y, x, co] * X[n, y*s + dh(tap), x*s + dw(tap), ci]
+//
+// GEMM view: M = co (128 per CTA), N = ci (<= 256 per CTA), K = output pixels.  Both operands
+// come straight out of NHWC activation tensors: a TMA box [64 ch, tw, th, 1] lands in smem as
+// 64 pixel rows of 128 bytes (64 channels), which is exactly UMMA's MN-major SWIZZLE_128B
+// layout (channels contiguous, rows step along K).  So no transposes are ever materialised.
+//
+// Work split: (tap, co-tile, ci-tile) output tiles x a split of the pixel range; partial sums
+// are added with vectorised fp32 reductions (red.global.add.v4.f32) directly into the gradient
+// bucket, which is what the allreduce kernel later reads.  Shared heads accumulate their five
+// pyramid levels in the same launch.
+//
+// Replaces cuDNN backward-filter; no counterpart source in the reference.
+#include "../include/b200_ops.h"
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace b200 {
+
+constexpr int kWStages = 4;
+constexpr int kKT = 64;                           // pixels per pipeline stage
+constexpr int kChunkBytes = kKT * 128;            // one [64 px][64 ch] chunk = 8 KB
+constexpr int kWAStage = 2 * kChunkBytes;         // M = 128 -> 2 chunks
+constexpr int kWBStage = 4 * kChunkBytes;         // N <= 256 -> 4 chunks
+constexpr int kWThreads = 256;
+constexpr int kWSmemBytes = kWStages * (kWAStage + kWBStage) + 1024 + 256;
+constexpr int kWMaxTaps = 49;
+constexpr int kWMaxMaps = 4 * B200_MAX_PROBLEMS;  // stride-2 parity maps only with 1 problem
+
+struct WTap {
+  int8_t dh, dw, map, pad;
+};
+
+struct WProblem {
+  int N, OH, OW;
+  int tiles_h, tiles_w;
+  int tile_begin;  // first pixel tile of this problem
+  int th_log2, tw_log2;
+  int xmap_base;
+};
+
+struct WgradParams {
+  CUtensorMap x_maps[8];
+  CUtensorMap dy_maps[B200_MAX_PROBLEMS];
+  WProblem prob[B200_MAX_PROBLEMS];
+  WTap taps[kWMaxTaps];
+  float* dw;
+  const float* rowscale;
+  int num_problems, num_pixel_tiles;
+  int num_taps, num_m_tiles, num_n_tiles, ksplit, chunk;
+  int Cin, Cout, BN;
+};
+
+__device__ __forceinline__ void w_decode(const WgradParams& p, int pt, int& pi, int& n, int& y0, int& x0) {
+  pi = 0;
+#pragma unroll
+  for (int i = 1; i < B200_MAX_PROBLEMS; ++i)
+    if (i < p.num_problems && pt >= p.prob[i].tile_begin) pi = i;
+  const WProblem& q = p.prob[pi];
+  const int local = pt - q.tile_begin;
+  const int per_img = q.tiles_h * q.tiles_w;
+  n = local / per_img;
+  const int rem = local - n * per_img;
+  const int ty = rem / q.tiles_w;
+  const int tx = rem - ty * q.tiles_w;
+  y0 = ty << q.th_log2;
+  x0 = tx << q.tw_log2;
+}
+
+__global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_constant__ WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_smem = smem_base;
+  const uint32_t b_smem = smem_base + kWStages * kWAStage;
+  const uint32_t bar_base = b_smem + kWStages * kWBStage;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kWStages + s); };
+  const uint32_t tfull_bar = bar_base + 8u * (2 * kWStages);
+  const uint32_t tmem_ptr_smem = bar_base + 8u * (2 * kWStages + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // unit decode: blockIdx.x = ((tap * num_m + m_tile) * num_n + n_tile) * ksplit + split
+  int u = blockIdx.x;
+  const int split = u % p.ksplit;
+  u /= p.ksplit;
+  const int n_tile = u % p.num_n_tiles;
+  u /= p.num_n_tiles;
+  const int m_tile = u % p.num_m_tiles;
+  const int tap_i = u / p.num_m_tiles;
+  const int pt_begin = split * p.chunk;
+  const int pt_end = min(p.num_pixel_tiles, pt_begin + p.chunk);
+  const int n_chunks = p.BN >> 6;
+  const uint32_t stage_bytes = (2 + n_chunks) * kChunkBytes;
+
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < 8; ++i) tma_prefetch_desc(&p.x_maps[i]);
+    for (int i = 0; i < B200_MAX_PROBLEMS; ++i) tma_prefetch_desc(&p.dy_maps[i]);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kWStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr_smem, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
+
+  if (pt_begin < pt_end) {
+    if (warp == 0) {
+      if (lane == 0) {
+        const WTap tap = p.taps[tap_i];
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int pt = pt_begin; pt < pt_end; ++pt) {
+          int pi, n, y0, x0;
+          w_decode(p, pt, pi, n, y0, x0);
+          const void* xmap = &p.x_maps[p.prob[pi].xmap_base + tap.map];
+          const void* dymap = &p.dy_maps[pi];
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          mbar_expect_tx(full_bar(stage), stage_bytes);
+          const uint32_t a_dst = a_smem + stage * kWAStage;
+          const uint32_t b_dst = b_smem + stage * kWBStage;
+          tma_load_4d(a_dst, dymap, full_bar(stage), m_tile * 128, x0, y0, n);
+          tma_load_4d(a_dst + kChunkBytes, dymap, full_bar(stage), m_tile * 128 + 64, x0, y0, n);
+          for (int c = 0; c < n_chunks; ++c)
+            tma_load_4d(b_dst + c * kChunkBytes, xmap, full_bar(stage), n_tile * p.BN + c * 64, x0 + tap.dw,
+                        y0 + tap.dh, n);
+          if (++stage == kWStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    } else if (warp == 1) {
+      const uint32_t idesc = make_idesc_bf16(128, p.BN, 1, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int pt = pt_begin; pt < pt_end; ++pt) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        if (lane == 0) {
+          // MN-major: LBO = distance between 64-channel chunks, SBO = 8 pixel rows = 1024 B
+          const uint64_t adesc = make_smem_desc(a_smem + stage * kWAStage, kChunkBytes, 1024);
+          const uint64_t bdesc = make_smem_desc(b_smem + stage * kWBStage, kChunkBytes, 1024);
+#pragma unroll
+          for (int k = 0; k < kKT / 16; ++k) {
+            // 16 pixel rows = 2048 bytes -> +128 in (addr >> 4) units
+            umma_bf16(tmem_base, adesc + 128 * k, bdesc + 128 * k, idesc, (pt != pt_begin) || (k != 0));
+          }
+          umma_commit(empty_bar(stage));
+          if (pt == pt_end - 1) umma_commit(tfull_bar);
+        }
+        __syncwarp();
+        if (++stage == kWStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    } else if (warp >= 4) {
+      const int quarter = warp - 4;
+      const int co = m_tile * 128 + quarter * 32 + lane;
+      const bool valid = co < p.Cout;
+      const float rs = (valid && p.rowscale) ? __ldg(p.rowscale + co) : 1.f;
+      float* row = p.dw + (static_cast<long long>(tap_i) * p.Cout + (valid ? co : 0)) * p.Cin + n_tile * p.BN;
+      mbar_wait(tfull_bar, 0);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+      for (int c = 0; c < p.BN; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c, r);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            if (n_tile * p.BN + c + j < p.Cin) {
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(row + c + j),
+                           "f"(__uint_as_float(r[j]) * rs), "f"(__uint_as_float(r[j + 1]) * rs),
+                           "f"(__uint_as_float(r[j + 2]) * rs), "f"(__uint_as_float(r[j + 3]) * rs)
+                           : "memory");
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 256);
+}
+
+static int floordiv_w(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+static int posmod_w(int a, int b) { return ((a % b) + b) % b; }
+
+static void pick_tile64(int OH, int OW, int& th_log2, int& tw_log2) {
+  long long best = -1;
+  for (int tl = 6; tl >= 0; --tl) {
+    const int tw = 1 << tl, th = 64 >> tl;
+    const long long tiles = static_cast<long long>((OH + th - 1) / th) * ((OW + tw - 1) / tw);
+    if (best < 0 || tiles < best) {
+      best = tiles;
+      tw_log2 = tl;
+      th_log2 = 6 - tl;
+    }
+  }
+}
+
+}  // namespace b200
+
+extern "C" int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accum, void* stream);
+
+extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
+  using namespace b200;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!a || a->num_problems < 1 || a->num_problems > B200_MAX_PROBLEMS) return set_error(-1, "b200_wgrad: bad num_problems");
+  if (a->stride != 1 && a->stride != 2) return set_error(-1, "b200_wgrad: stride must be 1 or 2");
+  if (a->stride == 2 && a->num_problems > 2) return set_error(-1, "b200_wgrad: at most 2 problems with stride 2");
+  if (a->KH * a->KW > kWMaxTaps) return set_error(-1, "b200_wgrad: too many taps");
+  if ((a->ldx % 8) || (a->ldy % 8)) return set_error(-1, "b200_wgrad: ld* must be multiples of 8");
+  if (a->Cin % 64) return set_error(-1, "b200_wgrad: Cin must be a multiple of 64");
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA_OK(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmemBytes));
+    attr_set = true;
+  }
+
+  WgradParams p;
+  memset(&p, 0, sizeof(p));
+  p.dw = a->dw;
+  p.rowscale = a->rowscale;
+  p.num_problems = a->num_problems;
+  p.Cin = a->Cin;
+  p.Cout = a->Cout;
+  p.BN = a->Cin >= 256 ? 256 : a->Cin;
+  p.num_n_tiles = (a->Cin + p.BN - 1) / p.BN;
+  p.num_m_tiles = (a->Cout + 127) / 128;
+  const int s = a->stride;
+  int nt = 0;
+  for (int r = 0; r < a->KH; ++r)
+    for (int c = 0; c < a->KW; ++c) {
+      const int eh = r - a->pad_h, ew = c - a->pad_w;
+      WTap t;
+      t.dh = static_cast<int8_t>(floordiv_w(eh, s));
+      t.dw = static_cast<int8_t>(floordiv_w(ew, s));
+      t.map = static_cast<int8_t>(posmod_w(eh, s) * s + posmod_w(ew, s));
+      t.pad = 0;
+      p.taps[nt++] = t;
+    }
+  p.num_taps = nt;
+
+  int tile_begin = 0, map_count = 0;
+  for (int i = 0; i < a->num_problems; ++i) {
+    const B200WgradProblem& q = a->prob[i];
+    WProblem& d = p.prob[i];
+    d.N = q.N;
+    d.OH = q.OH;
+    d.OW = q.OW;
+    pick_tile64(q.OH, q.OW, d.th_log2, d.tw_log2);
+    const int th = 1 << d.th_log2, tw = 1 << d.tw_log2;
+    d.tiles_h = (q.OH + th - 1) / th;
+    d.tiles_w = (q.OW + tw - 1) / tw;
+    d.tile_begin = tile_begin;
+    tile_begin += q.N * d.tiles_h * d.tiles_w;
+    d.xmap_base = map_count;
+    const unsigned int box[4] = {64u, static_cast<unsigned>(tw), static_cast<unsigned>(th), 1u};
+    const int nmaps = (s == 2) ? 4 : 1;
+    if (map_count + nmaps > 8) return set_error(-1, "b200_wgrad: too many tensor maps");
+    for (int mi = 0; mi < nmaps; ++mi) {
+      const int py = mi / 2, px = mi % 2;
+      const int step = (nmaps == 4) ? 2 : 1;
+      const long long Wd = (q.W - px + step - 1) / step;
+      const long long Hd = (q.H - py + step - 1) / step;
+      const __nv_bfloat16* base = static_cast<const __nv_bfloat16*>(q.x) + (static_cast<long long>(py) * q.W + px) * a->ldx;
+      unsigned long long dims[4] = {static_cast<unsigned long long>(a->Cin), static_cast<unsigned long long>(Wd > 0 ? Wd : 1),
+                                    static_cast<unsigned long long>(Hd > 0 ? Hd : 1), static_cast<unsigned long long>(q.N)};
+      unsigned long long strides[3] = {static_cast<unsigned long long>(step) * a->ldx * 2ull,
+                                       static_cast<unsigned long long>(step) * q.W * a->ldx * 2ull,
+                                       static_cast<unsigned long long>(q.H) * q.W * a->ldx * 2ull};
+      int rc = make_tmap_bf16(&p.x_maps[map_count + mi], base, 4, dims, strides, box);
+      if (rc) return rc;
+    }
+    map_count += nmaps;
+    {
+      unsigned long long dims[4] = {static_cast<unsigned long long>(a->Cout), static_cast<unsigned long long>(q.OW),
+                                    static_cast<unsigned long long>(q.OH), static_cast<unsigned long long>(q.N)};
+      unsigned long long strides[3] = {static_cast<unsigned long long>(a->ldy) * 2ull,
+                                       static_cast<unsigned long long>(q.OW) * a->ldy * 2ull,
+                                       static_cast<unsigned long long>(q.OH) * q.OW * a->ldy * 2ull};
+      int rc = make_tmap_bf16(&p.dy_maps[i], q.dy, 4, dims, strides, box);
+      if (rc) return rc;
+    }
+  }
+  for (int i = map_count; i < 8; ++i) p.x_maps[i] = p.x_maps[0];
+  for (int i = a->num_problems; i < B200_MAX_PROBLEMS; ++i) p.dy_maps[i] = p.dy_maps[0];
+  p.num_pixel_tiles = tile_begin;
+
+  const long long units = static_cast<long long>(p.num_taps) * p.num_m_tiles * p.num_n_tiles;
+  // ~3 waves of CTAs, but at least 8 pixel tiles (512 pixels) per CTA to amortise the epilogue
+  long long ks = (3LL * num_sms() + units - 1) / units;
+  const long long max_ks = (p.num_pixel_tiles + 7) / 8;
+  if (ks > max_ks) ks = max_ks;
+  if (ks < 1) ks = 1;
+  p.chunk = static_cast<int>((p.num_pixel_tiles + ks - 1) / ks);
+  p.ksplit = (p.num_pixel_tiles + p.chunk - 1) / p.chunk;
+  const long long grid = units * p.ksplit;
+  if (grid > 0x7fffffffLL) return set_error(-1, "b200_wgrad: grid too large");
+
+  wgrad_kernel<<<static_cast<unsigned>(grid), kWThreads, kWSmemBytes, stream>>>(p);
+  int rc = check_launch("wgrad_kernel");
+  if (rc) return rc;
+  if (a->dbias) {
+    for (int i = 0; i < a->num_problems; ++i) {
+      const B200WgradProblem& q = a->prob[i];
+      rc = b200_colsum(q.dy, static_cast<long long>(q.N) * q.OH * q.OW, a->Cout, a->ldy, a->dbias, stream_);
+      if (rc) return rc;
+    }
+  }
+  return 0;
+}

@@ -1,0 +1,200 @@
+/* C ABI of libb200ops.so -- hand-written sm_100a kernels for the RetinaNet hot path.
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on (as void*),
+ * returns 0 on success and a negative code on failure (b200_last_error() has the text).
+ * None of them synchronises the stream.  Tensors are NHWC ("channels last"); `ld*` arguments
+ * are per-pixel channel strides in elements.
+ *
+ * The "Replaces" notes cite the reference stack's op (SURVEY.md section 2F ids) so parity can
+ * be checked; the reference itself ships no CUDA code (its train.py delegates to TF/cuDNN).
+ */
+#ifndef B200_OPS_H_
+#define B200_OPS_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* b200_last_error(void);
+int b200_ops_abi_version(void);
+/* Number of kernel launches issued by this library in this process (bench.py gpu_launches). */
+long long b200_launch_count(void);
+void b200_reset_launch_count(void);
+
+/* ------------------------------------------------------------------ convolution (tcgen05)
+ * Implicit-GEMM convolution on the 5th-gen tensor cores: TMA tiled loads (zero-filled halos)
+ * -> 128B-swizzled smem ring -> tcgen05.mma (M=128, N<=256, K=16, bf16 in / fp32 acc in TMEM)
+ * -> tcgen05.ld epilogue fusing: + shift[c] (bias or frozen-BN shift; the BN scale is folded
+ * into the bf16 working weights), + add (residual / gradient accumulation), * (mask > 0)
+ * (ReLU backward), ReLU, bf16 or fp32 store.  Persistent, warp-specialised (TMA / MMA / TMEM
+ * alloc / 4 epilogue warps), double-buffered accumulators.  Up to 5 same-weight problems
+ * (the FPN levels of a shared head) are scheduled in one launch.
+ * Replaces: cuDNN fprop + bias-add + fused-BN + ReLU + add (G2-G4, G6, G8) and dgrad (G12). */
+#define B200_MAX_PROBLEMS 5
+
+typedef struct {
+  const void* in;   /* bf16 [N, H, W, ldi] */
+  void* out;        /* bf16/fp32 [N, OHo, OWo, ldo] */
+  const void* add;  /* optional bf16, geometry of out */
+  const void* mask; /* optional bf16, geometry of out */
+  int N, H, W;      /* dims of `in` */
+  int OHo, OWo;     /* spatial dims of `out` */
+} B200ConvProblem;
+
+typedef struct {
+  int mode;         /* 0 fprop: out = conv(in, w); 1 dgrad: out = conv_transpose(in = dY, w) */
+  int num_problems;
+  B200ConvProblem prob[B200_MAX_PROBLEMS];
+  const void* weight; /* bf16 [KH*KW][Nrows][ldw]; fprop: rows = Cout, K = Cin; dgrad: rows = Cin, K = Cout */
+  int K;            /* reduction channels (channels of `in`) */
+  int ldi;          /* channel stride of `in` */
+  int Nrows;        /* output channels of this GEMM */
+  int ldw;          /* row stride of weight, elements */
+  int ldo;          /* channel stride of out / add / mask */
+  int KH, KW, stride, pad_h, pad_w; /* pad_* = padding before (TF 'same' may be asymmetric) */
+  int par_y, par_x; /* dgrad with stride 2: output parity class computed by this launch */
+  const float* shift; /* optional fp32 [Nrows] */
+  int relu;
+  int out_fp32;
+} B200ConvArgs;
+
+int b200_conv(const B200ConvArgs* args, void* stream);
+
+/* Weight gradient: dW[t][co][ci] += rowscale[co] * sum_pixels dY[p, co] * X[p + tap, ci]
+ * (fp32 atomics; split over pixels).  Both operands are MN-major UMMA operands straight from
+ * NHWC tiles.  Up to 5 problems accumulate into the same dW (shared heads).
+ * Replaces: cuDNN backward-filter (G12). */
+typedef struct {
+  const void* x;    /* bf16 [N, H, W, ldx] forward input */
+  const void* dy;   /* bf16 [N, OH, OW, ldy] gradient of conv output */
+  int N, H, W, OH, OW;
+} B200WgradProblem;
+
+typedef struct {
+  int num_problems;
+  B200WgradProblem prob[B200_MAX_PROBLEMS];
+  float* dw;        /* fp32 [KH*KW][Cout][Cin], accumulated into */
+  int Cin, ldx, Cout, ldy;
+  int KH, KW, stride, pad_h, pad_w;
+  const float* rowscale; /* optional fp32 [Cout] (frozen-BN scale) */
+  float* dbias;     /* optional fp32 [Cout]: += sum_pixels dY (computed by the tap-0 CTAs) */
+} B200WgradArgs;
+
+int b200_wgrad(const B200WgradArgs* args, void* stream);
+
+/* ------------------------------------------------------------------ bandwidth-bound fused ops */
+
+/* Frozen-BN scale fold + layout transform of master weights into the bf16 working copies
+ * consumed by b200_conv (table-driven, one launch for every conv of the model).
+ * entry: src fp32 [KH*KW][Cout][Cin] (engine master layout), scale fp32 [Cout] or null,
+ * dst_f bf16 [KH*KW][Cout][ldf] (fprop), dst_d bf16 [KH*KW][Cin][ldd] (dgrad, transposed). */
+typedef struct {
+  const float* src;
+  const float* scale;
+  void* dst_f;
+  void* dst_d;
+  int taps, Cout, Cin, ldf, ldd;
+  long long block_begin; /* filled by the library */
+} B200WeightEntry;
+long long b200_weight_table_blocks(B200WeightEntry* host_entries, int n); /* fills block_begin */
+int b200_prepare_weights(const B200WeightEntry* host_entries, int n, void* dev_table, void* stream);
+
+/* 3x3/2 'same' max-pool fused with the stem's frozen-BN affine + ReLU (G4+G5), and backward. */
+int b200_bn_relu_maxpool_fwd(const void* x, const float* scale, const float* shift, void* y, int N, int H, int W,
+                             int C, int OH, int OW, int pad_h, int pad_w, void* stream);
+int b200_bn_relu_maxpool_bwd(const void* x, const float* scale, const float* shift, const void* y, const void* dy,
+                             void* dx, int N, int H, int W, int C, int OH, int OW, int pad_h, int pad_w,
+                             void* stream);
+/* Nearest upsample-to-shape + add (FPN top-down merge, G7) and its backward (gather-sum). */
+int b200_upsample_add(const void* lateral, const void* top, void* out, int N, int H, int W, int C, int TH, int TW,
+                      void* stream);
+int b200_upsample_bwd_add(const void* dmerged, void* dtop_inout, int N, int H, int W, int C, int TH, int TW,
+                          void* stream);
+/* y = relu(x) and dx = dy * (y > 0) on bf16 buffers (P7's input; generic). */
+int b200_relu(const void* x, void* y, long long n, void* stream);
+int b200_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* stream);
+/* Column sums of a bf16 [rows, ld] matrix into fp32 (bias gradients). */
+int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accum, void* stream);
+
+/* Image normalise + pad (G19): uint8 HWC (BGR) -> bf16 NHWC with Caffe mean subtraction. */
+int b200_preprocess(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean,
+                    void* stream);
+
+/* Anchor generation (G15): 9 anchors per location, level l, written at anchors[offset..]. */
+int b200_generate_anchors(float* anchors, int H, int W, int stride, float size, void* stream);
+
+/* IoU + arg-max + assignment + target encoding (G16; replaces the Cython compute_overlap path).
+ * gt: fp32 [B, Gmax, 5] (x1,y1,x2,y2,label), gt_count int32 [B], img_hw int32 [B,2] un-padded sizes.
+ * Outputs: state int8 [B,A], cls int16 [B,A], reg_target fp32 [B,A,4], num_pos int32[1] (+=). */
+int b200_assign_targets(const float* anchors, int A, const float* gt, const int* gt_count, const int* img_hw, int B,
+                        int Gmax, float neg_thr, float pos_thr, int8_t* state, int16_t* cls, float* reg_target,
+                        int* num_pos, void* stream);
+
+/* Sigmoid focal loss fwd+bwd in one pass over the logits (G9+G10).  logits bf16 [B, A_l, ld]
+ * (A_l = anchors of this level, K classes used of ld), targets indexed at [b*A_total + a_off + a].
+ * loss_accum += sum(loss)/max(1,num_pos); dlogits = dloss/dlogit * loss_scale / max(1,num_pos). */
+int b200_focal_loss(const void* logits, void* dlogits, int B, int A_l, int K, int ld, const int8_t* state,
+                    const int16_t* cls, int A_total, int a_off, const int* num_pos, float alpha, float gamma,
+                    float loss_scale, float* loss_accum, void* stream);
+/* Smooth-L1 fwd+bwd on positives only (G11).  pred bf16 [B, A_l, ld] (4 used). */
+int b200_smooth_l1(const void* pred, void* dpred, int B, int A_l, int ld, const int8_t* state,
+                   const float* reg_target, int A_total, int a_off, const int* num_pos, float sigma,
+                   float loss_scale, float* loss_accum, void* stream);
+
+/* Sum of squares of a flat fp32 buffer (G13), accumulated into out[0]. */
+int b200_sumsq(const float* x, long long n, float* out, void* stream);
+/* Keras-semantics Adam on flat fp32 buffers (G14): grads are first multiplied by
+ * grad_scale[0] (device scalar: the global-norm clip factor), then
+ * m,v update; p -= lr_t * m / (sqrt(v) + eps) with lr_t = lr*sqrt(1-b2^t)/(1-b1^t). */
+int b200_adam(float* p, const float* g, float* m, float* v, long long n, const float* grad_scale, float lr_t,
+              float beta1, float beta2, float eps, void* stream);
+/* clip factor: scale[0] = (norm >= clip) ? clip / norm : 1 with norm = sqrt(sumsq[0]). */
+int b200_clip_scale(const float* sumsq, float clipnorm, float* scale, void* stream);
+
+/* Box decode + clip + score threshold + candidate compaction (G17), then class-aware
+ * bitmask NMS + top-k + pad (G18). */
+int b200_filter_detections(const void* const* cls_levels, const void* const* reg_levels, const int* level_anchors,
+                           int num_levels, int ld_cls, int ld_reg, int K, const float* anchors, int A_total, int B,
+                           int img_h, int img_w, float score_thr, float nms_thr, int max_det, int max_cand,
+                           void* workspace, long long workspace_bytes, float* out_boxes, float* out_scores,
+                           int* out_labels, void* stream);
+long long b200_filter_detections_workspace(int B, int max_cand);
+/* Stand-alone greedy NMS on fp32 boxes sorted by the caller (descending score); keep mask out. */
+int b200_nms_sorted(const float* boxes, const int* cls_or_null, int n, float thr, unsigned long long* mask_ws,
+                    int* keep_flags, void* stream);
+
+/* ------------------------------------------------------------------ peer-to-peer collectives
+ * Allreduce over NVLink peer mappings: every rank passes the table of all ranks' bucket
+ * pointers (mapped with CUDA IPC) and flag pads (host arrays, copied into kernel params).  Fused: per-rank pre-scale (global-norm clip
+ * factor read from each peer), 1/N averaging, optional bf16 wire format.
+ * Replaces: ncclAllReduce / MPI_Allreduce + tf.div + fusion-buffer memcpys (X1-X3). */
+typedef struct {
+  void* bufs[8];            /* every rank's fp32 bucket base (peer-mapped device pointers) */
+  uint32_t* flags[8];       /* every rank's flag pad (b200_flag_pad_bytes(), zero-initialised) */
+  const float* prescale[8]; /* every rank's device scalar (its clip factor), if has_prescale */
+  float* out;               /* LOCAL result buffer (same offsets as the bucket) */
+  int rank, world;          /* world in {1, 2, 4, 8} */
+  long long offset, count;  /* element range of the bucket, multiples of 4 */
+  float postscale;          /* e.g. 1/world */
+  uint32_t epoch;           /* flag base; advance by 4 per call, same on every rank */
+  int algo;                 /* 0 auto, 1 one-shot, 2 two-shot */
+  int max_blocks;           /* <= 64; 0 = default */
+  int has_prescale;
+} B200ArHostArgs;
+int b200_allreduce_host(const B200ArHostArgs* args, void* stream);
+int b200_broadcast_host(const B200ArHostArgs* args, int root, void* stream);
+long long b200_flag_pad_bytes(void);
+/* IPC helpers (cudaIpc*): 64-byte handles exchanged by the Python layer. */
+int b200_ipc_alloc(void** ptr, long long bytes);
+int b200_ipc_free(void* ptr);
+int b200_ipc_get_handle(void* ptr, void* handle64);
+int b200_ipc_open_handle(const void* handle64, void** ptr);
+int b200_ipc_close_handle(void* ptr);
+int b200_enable_peer_access(int device, int world_local);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_OPS_H_ */

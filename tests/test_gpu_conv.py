@@ -1,0 +1,193 @@
+"""tcgen05 convolution kernels vs a plain PyTorch fp32 reference of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from batchai_retinanet_horovod_coco_b200.ops import conv as cv
+from batchai_retinanet_horovod_coco_b200.ops import native
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk(n, h, w, c, ld=None, scale=1.0, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    ld = ld or cv.round8(c)
+    x = torch.zeros(n, h, w, ld, device="cuda", dtype=torch.bfloat16)
+    x[..., :c] = (torch.randn(n, h, w, c, device="cuda", generator=g) * scale).to(torch.bfloat16)
+    return x
+
+
+def _ref_conv(x_nhwc, c, w_oihw, stride, pads):
+    """pads = (top, bottom, left, right)"""
+    x = x_nhwc[..., :c].float().permute(0, 3, 1, 2)
+    x = F.pad(x, (pads[2], pads[3], pads[0], pads[1]))
+    return F.conv2d(x, w_oihw.to(torch.bfloat16).float(), stride=stride)
+
+
+def _close(a, b, tol=2e-2):
+    err = (a.float() - b.float()).abs().max().item()
+    ref = b.float().abs().max().item() + 1e-6
+    assert err <= tol * ref, f"max err {err} vs ref max {ref}"
+    return err / ref
+
+
+CASES = [
+    # n, h, w, cin, cout, k, stride
+    (2, 16, 16, 64, 64, 1, 1),
+    (2, 13, 21, 256, 512, 1, 1),
+    (1, 25, 42, 256, 256, 3, 1),
+    (2, 7, 11, 256, 720, 3, 1),
+    (2, 9, 10, 256, 36, 3, 1),
+    (2, 26, 42, 256, 128, 1, 2),
+    (1, 25, 42, 128, 256, 3, 2),
+    (1, 32, 32, 2048, 256, 3, 2),
+]
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride", CASES)
+def test_fprop(n, h, w, cin, cout, k, stride):
+    torch.manual_seed(1)
+    x = _mk(n, h, w, cin)
+    wt = torch.randn(cout, cin, k, k, device="cuda") * (1.0 / (cin * k * k) ** 0.5)
+    if stride == 1:
+        pb = (k // 2, k // 2)
+        pads = (k // 2, k // 2, k // 2, k // 2)
+        ptot = (2 * pb[0], 2 * pb[1])
+    else:
+        from batchai_retinanet_horovod_coco_b200.models.resnet import tf_same_pad
+        ph, pw = tf_same_pad(h, k, 2), tf_same_pad(w, k, 2)
+        pb, pads, ptot = (ph[0], pw[0]), (ph[0], ph[1], pw[0], pw[1]), (sum(ph), sum(pw))
+    wf, _ = cv.pack_working(cv.pack_master(wt))
+    y = cv.fprop(x, wf, cin, cout, k, k, stride, pad=pb, pad_total=ptot)
+    torch.cuda.synchronize()
+    ref = _ref_conv(x, cin, wt, stride, pads).permute(0, 2, 3, 1)
+    assert y.shape[:3] == ref.shape[:3]
+    _close(y[..., :cout], ref)
+
+
+def test_fprop_epilogue():
+    n, h, w, cin, cout = 2, 20, 30, 128, 256
+    x = _mk(n, h, w, cin)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda") * 0.03
+    shift = torch.randn(cout, device="cuda")
+    res = _mk(n, h, w, cout, seed=3)
+    wf, _ = cv.pack_working(cv.pack_master(wt))
+    y = cv.fprop(x, wf, cin, cout, 3, 3, 1, pad=(1, 1), shift=shift, relu=True, add=res)
+    ref = _ref_conv(x, cin, wt, 1, (1, 1, 1, 1)).permute(0, 2, 3, 1) + shift + res.float()
+    _close(y, ref.clamp(min=0))
+    y32 = cv.fprop(x, wf, cin, cout, 3, 3, 1, pad=(1, 1), shift=shift, out_fp32=True)
+    _close(y32, _ref_conv(x, cin, wt, 1, (1, 1, 1, 1)).permute(0, 2, 3, 1) + shift, tol=5e-3)
+
+
+def test_fprop_group():
+    shapes = [(2, 25, 42), (2, 13, 21), (2, 7, 11), (2, 4, 6), (2, 2, 3)]
+    xs = [_mk(n, h, w, 256, seed=i) for i, (n, h, w) in enumerate(shapes)]
+    wt = torch.randn(256, 256, 3, 3, device="cuda") * 0.02
+    b = torch.randn(256, device="cuda")
+    wf, _ = cv.pack_working(cv.pack_master(wt))
+    ys = cv.fprop_group(xs, wf, 256, 256, 3, 3, shift=b, relu=True)
+    for x, y in zip(xs, ys):
+        ref = (_ref_conv(x, 256, wt, 1, (1, 1, 1, 1)).permute(0, 2, 3, 1) + b).clamp(min=0)
+        _close(y, ref)
+
+
+def _ref_dgrad(dy_nhwc, cout, w_oihw, stride, pads, in_hw):
+    n = dy_nhwc.shape[0]
+    cin = w_oihw.shape[1]
+    x = torch.zeros(n, cin, in_hw[0], in_hw[1], device="cuda", requires_grad=True)
+    xp = F.pad(x, (pads[2], pads[3], pads[0], pads[1]))
+    y = F.conv2d(xp, w_oihw.to(torch.bfloat16).float(), stride=stride)
+    y.backward(dy_nhwc[..., :cout].float().permute(0, 3, 1, 2))
+    return x.grad.permute(0, 2, 3, 1)
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride", [
+    (2, 16, 16, 64, 256, 1, 1), (1, 25, 42, 256, 256, 3, 1), (2, 9, 10, 256, 36, 3, 1), (2, 7, 11, 256, 720, 3, 1),
+    (2, 26, 42, 256, 128, 1, 2), (1, 25, 42, 128, 256, 3, 2), (1, 13, 21, 256, 256, 3, 2)])
+def test_dgrad(n, h, w, cin, cout, k, stride):
+    from batchai_retinanet_horovod_coco_b200.models.resnet import tf_same_pad
+    wt = torch.randn(cout, cin, k, k, device="cuda") * (1.0 / (cout * k * k) ** 0.5)
+    if stride == 1:
+        pb, pads = (k // 2, k // 2), (k // 2,) * 4
+        oh, ow = h, w
+    else:
+        ph, pw = tf_same_pad(h, k, 2), tf_same_pad(w, k, 2)
+        pb, pads = (ph[0], pw[0]), (ph[0], ph[1], pw[0], pw[1])
+        oh, ow = -(-h // 2), -(-w // 2)
+    dy = _mk(n, oh, ow, cout)
+    _, wd = cv.pack_working(cv.pack_master(wt))
+    dx = cv.dgrad(dy, wd, cin, cout, k, k, (h, w), stride, pad=pb)
+    ref = _ref_dgrad(dy, cout, wt, stride, pads, (h, w))
+    _close(dx[..., :cin], ref)
+
+
+def test_dgrad_mask_add():
+    n, h, w, cin, cout = 2, 20, 30, 128, 64
+    wt = torch.randn(cout, cin, 3, 3, device="cuda") * 0.05
+    dy = _mk(n, h, w, cout)
+    mask = _mk(n, h, w, cin, seed=5)
+    add = _mk(n, h, w, cin, seed=6)
+    _, wd = cv.pack_working(cv.pack_master(wt))
+    dx = cv.dgrad(dy, wd, cin, cout, 3, 3, (h, w), 1, pad=(1, 1), mask=mask, add=add)
+    ref = (_ref_dgrad(dy, cout, wt, 1, (1, 1, 1, 1), (h, w)) + add.float()) * (mask.float() > 0)
+    _close(dx, ref)
+
+
+def _ref_wgrad(x_nhwc, cin, dy_nhwc, cout, k, stride, pads):
+    w = torch.zeros(cout, cin, k, k, device="cuda", requires_grad=True)
+    x = F.pad(x_nhwc[..., :cin].float().permute(0, 3, 1, 2), (pads[2], pads[3], pads[0], pads[1]))
+    y = F.conv2d(x, w, stride=stride)
+    y.backward(dy_nhwc[..., :cout].float().permute(0, 3, 1, 2))
+    return cv.pack_master(w.grad)
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride", [
+    (2, 16, 16, 64, 64, 1, 1), (1, 25, 42, 256, 256, 3, 1), (2, 9, 10, 256, 36, 3, 1), (2, 7, 11, 256, 720, 3, 1),
+    (2, 26, 42, 256, 128, 1, 2), (1, 25, 42, 128, 256, 3, 2), (2, 40, 56, 512, 128, 1, 1)])
+def test_wgrad(n, h, w, cin, cout, k, stride):
+    from batchai_retinanet_horovod_coco_b200.models.resnet import tf_same_pad
+    x = _mk(n, h, w, cin)
+    if stride == 1:
+        pb, pads = (k // 2, k // 2), (k // 2,) * 4
+        oh, ow = h, w
+    else:
+        ph, pw = tf_same_pad(h, k, 2), tf_same_pad(w, k, 2)
+        pb, pads = (ph[0], pw[0]), (ph[0], ph[1], pw[0], pw[1])
+        oh, ow = -(-h // 2), -(-w // 2)
+    dy = _mk(n, oh, ow, cout, seed=2)
+    rs = torch.rand(cout, device="cuda") + 0.5
+    dw = torch.zeros(k * k, cout, cin, device="cuda")
+    db = torch.zeros(cout, device="cuda")
+    cv.wgrad(x, dy, dw, cin, cout, k, k, stride, pad=pb, rowscale=rs, dbias=db)
+    ref = _ref_wgrad(x, cin, dy, cout, k, stride, pads) * rs.view(1, -1, 1)
+    _close(dw, ref)
+    _close(db, dy[..., :cout].float().sum(dim=(0, 1, 2)), tol=1e-3)
+
+
+def test_wgrad_group():
+    shapes = [(2, 25, 42), (2, 13, 21), (2, 7, 11), (2, 4, 6), (2, 2, 3)]
+    xs = [_mk(n, h, w, 256, seed=i) for i, (n, h, w) in enumerate(shapes)]
+    dys = [_mk(n, h, w, 256, seed=10 + i) for i, (n, h, w) in enumerate(shapes)]
+    dw = torch.zeros(9, 256, 256, device="cuda")
+    cv.wgrad_group(xs, dys, dw, 256, 256, 3, 3)
+    ref = sum(_ref_wgrad(x, 256, dy, 256, 3, 1, (1, 1, 1, 1)) for x, dy in zip(xs, dys))
+    _close(dw, ref)
+
+
+def test_prepare_weights_kernel():
+    m1 = torch.randn(9, 256, 64, device="cuda")
+    m2 = torch.randn(1, 36, 256, device="cuda")
+    s1 = torch.rand(256, device="cuda") + 0.5
+    e = []
+    outs = []
+    for m, s in ((m1, s1), (m2, None)):
+        t, co, ci = m.shape
+        wf = torch.zeros(t, co, cv.round8(ci), device="cuda", dtype=torch.bfloat16)
+        wd = torch.zeros(t, ci, cv.round8(co), device="cuda", dtype=torch.bfloat16)
+        e.append(dict(src=m, scale=s, dst_f=wf, dst_d=wd, taps=t, Cout=co, Cin=ci))
+        outs.append((wf, wd))
+    tab = native.WeightTable(e)
+    tab.run()
+    for (m, s), (wf, wd) in zip(((m1, s1), (m2, None)), outs):
+        rf, rd = cv.pack_working(m, s)
+        assert torch.equal(wf, rf) and torch.equal(wd, rd)

@@ -1,0 +1,236 @@
+"""Bandwidth-bound CUDA kernels vs their plain-PyTorch fp32 spec implementations."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from batchai_retinanet_horovod_coco_b200.ops import anchors as A
+from batchai_retinanet_horovod_coco_b200.ops import losses as L
+from batchai_retinanet_horovod_coco_b200.ops import native
+from batchai_retinanet_horovod_coco_b200.ops.filter_detections import nms_reference, filter_detections_single
+from batchai_retinanet_horovod_coco_b200.ops.boxes import bbox_transform_inv, clip_boxes
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def test_anchors_match_spec():
+    shapes = A.guess_shapes((200, 333))
+    got = native.anchors_for_shape_gpu(shapes, DEV)
+    ref = A.anchors_for_shape((200, 333)).to(DEV)
+    assert got.shape == ref.shape
+    assert (got - ref).abs().max().item() < 1e-3
+
+
+def _targets(B=3, H=256, W=320, G=7, K=80, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    anchors = A.anchors_for_shape((H, W))
+    gts = []
+    for b in range(B):
+        n = G if b != 1 else 0
+        xy = torch.rand(n, 2, generator=g) * torch.tensor([W * 0.6, H * 0.6])
+        wh = torch.rand(n, 2, generator=g) * torch.tensor([W * 0.4, H * 0.4]) + 16
+        lab = torch.randint(0, K, (n, 1), generator=g).float()
+        gts.append(torch.cat([xy, xy + wh, lab], dim=1))
+    return anchors, gts
+
+
+def _assign_gpu(anchors, gts, hw):
+    B, Gmax = len(gts), max(1, max(g.shape[0] for g in gts))
+    gt = torch.zeros(B, Gmax, 5)
+    cnt = torch.zeros(B, dtype=torch.int32)
+    for b, g in enumerate(gts):
+        gt[b, :g.shape[0]] = g
+        cnt[b] = g.shape[0]
+    An = anchors.shape[0]
+    state = torch.empty(B, An, dtype=torch.int8, device=DEV)
+    cls = torch.empty(B, An, dtype=torch.int16, device=DEV)
+    reg = torch.empty(B, An, 4, device=DEV)
+    npos = torch.zeros(1, dtype=torch.int32, device=DEV)
+    img_hw = torch.tensor(hw, dtype=torch.int32, device=DEV)
+    native.assign_targets(anchors.to(DEV), gt.to(DEV), cnt.to(DEV), img_hw, state, cls, reg, npos)
+    return state, cls, reg, npos
+
+
+def test_assign_targets():
+    anchors, gts = _targets()
+    hw = [(256, 320), (200, 320), (256, 250)]
+    state, cls, reg, npos = _assign_gpu(anchors, gts, hw)
+    tot = 0
+    for b, g in enumerate(gts):
+        s, m, _ = A.assign_targets(anchors, g, hw[b])
+        assert torch.equal(state[b].cpu(), s), f"image {b}: {(state[b].cpu() != s).sum()} state mismatches"
+        tot += int((s == 1).sum())
+        if g.shape[0]:
+            pos = s == 1
+            assert torch.equal(cls[b].cpu()[pos].long(), g[m][pos, 4].long())
+            ref = A.bbox_transform(anchors, g[m][:, :4])
+            assert (reg[b].cpu()[pos] - ref[pos]).abs().max() < 1e-3
+    assert int(npos.item()) == tot
+
+
+def test_focal_and_smooth_l1():
+    K = 80
+    anchors, gts = _targets(B=2, H=128, W=160)
+    hw = [(128, 160), (128, 150)]
+    state, cls, reg, npos = _assign_gpu(anchors, gts, hw)
+    shapes = A.guess_shapes((128, 160))
+    A_total = anchors.shape[0]
+    torch.manual_seed(0)
+    loss_c = torch.zeros(1, device=DEV)
+    loss_r = torch.zeros(1, device=DEV)
+    logit_l, reg_l, dlog_l, dreg_l = [], [], [], []
+    off = 0
+    for (h, w) in shapes:
+        lg = (torch.randn(2, h, w, 9 * K, device=DEV) * 2 - 3).to(torch.bfloat16)
+        rg = torch.zeros(2, h, w, 40, device=DEV, dtype=torch.bfloat16)
+        rg[..., :36] = torch.randn(2, h, w, 36, device=DEV).to(torch.bfloat16)
+        dl, dr = torch.empty_like(lg), torch.zeros_like(rg)
+        native.focal_loss(lg, dl, K, state, cls, A_total, off, npos, loss_c)
+        native.smooth_l1(rg, dr, state, reg, A_total, off, npos, loss_r)
+        logit_l.append(lg); reg_l.append(rg); dlog_l.append(dl); dreg_l.append(dr)
+        off += h * w * 9
+    logits = torch.cat([t.float().reshape(2, -1, K) for t in logit_l], dim=1).requires_grad_(True)
+    preds = torch.cat([t[..., :36].float().reshape(2, -1, 4) for t in reg_l], dim=1).requires_grad_(True)
+    ref_c = L.focal_compact(logits, state, cls)
+    ref_r = L.smooth_l1_compact(preds, reg, state)
+    (ref_c + ref_r).backward()
+    assert abs(loss_c.item() - ref_c.item()) <= 2e-3 * abs(ref_c.item()) + 1e-5
+    assert abs(loss_r.item() - ref_r.item()) <= 2e-3 * abs(ref_r.item()) + 1e-5
+    got_dc = torch.cat([t.float().reshape(2, -1, K) for t in dlog_l], dim=1)
+    got_dr = torch.cat([t[..., :36].float().reshape(2, -1, 4) for t in dreg_l], dim=1)
+    assert (got_dc - logits.grad).abs().max() <= 1e-2 * logits.grad.abs().max() + 1e-8
+    assert (got_dr - preds.grad).abs().max() <= 1e-2 * preds.grad.abs().max() + 1e-8
+
+
+def test_sumsq_clip_adam():
+    n = 1_000_003
+    torch.manual_seed(0)
+    p = torch.randn(n + 1, device=DEV)[:n]
+    g = torch.randn(n, device=DEV) * 1e-2
+    m = torch.zeros(n, device=DEV)
+    v = torch.zeros(n, device=DEV)
+    ss = torch.zeros(1, device=DEV)
+    sc = torch.zeros(1, device=DEV)
+    native.sumsq(g, ss)
+    assert abs(ss.item() - (g.double() ** 2).sum().item()) < 1e-3 * ss.item()
+    native.clip_scale(ss, 0.001, sc)
+    norm = ss.sqrt().item()
+    assert abs(sc.item() - 0.001 / norm) < 1e-6
+    p0 = p.clone()
+    lr, b1, b2, eps, t = 1e-5, 0.9, 0.999, 1e-7, 1
+    lr_t = lr * (1 - b2 ** t) ** 0.5 / (1 - b1 ** t)
+    native.adam(p, g, m, v, sc, lr_t, b1, b2, eps)
+    gs = g * sc
+    m_ref = (1 - b1) * gs
+    v_ref = (1 - b2) * gs * gs
+    p_ref = p0 - lr_t * m_ref / (v_ref.sqrt() + eps)
+    assert (m - m_ref).abs().max() < 1e-9
+    assert (p - p_ref).abs().max() < 1e-6
+
+
+def test_maxpool_fused():
+    from batchai_retinanet_horovod_coco_b200.models.resnet import tf_same_pad, max_pool_same
+    for (n, h, w, c) in [(2, 40, 66, 64), (1, 41, 67, 64)]:
+        x = torch.randn(n, h, w, c, device=DEV).to(torch.bfloat16)
+        scale = torch.rand(c, device=DEV) + 0.5
+        shift = torch.randn(c, device=DEV) * 0.3
+        ph, pw = tf_same_pad(h, 3, 2), tf_same_pad(w, 3, 2)
+        oh, ow = -(-h // 2), -(-w // 2)
+        y = torch.empty(n, oh, ow, c, device=DEV, dtype=torch.bfloat16)
+        native.bn_relu_maxpool_fwd(x, scale, shift, y, ph[0], pw[0])
+        xr = x.float().requires_grad_(True)
+        z = F.relu(xr * scale + shift).to(torch.bfloat16).float()  # value seen by the pool (rounded)
+        zz = F.relu(xr * scale + shift)
+        ref = max_pool_same(zz.permute(0, 3, 1, 2)).permute(0, 2, 3, 1)
+        assert (y.float() - ref).abs().max() <= 1e-2 * ref.abs().max()
+        dy = torch.randn(n, oh, ow, c, device=DEV).to(torch.bfloat16)
+        dx = torch.empty_like(x)
+        native.bn_relu_maxpool_bwd(x, scale, shift, y, dy, dx, ph[0], pw[0])
+        ref.backward(dy.float())
+        # ties after bf16 rounding may route gradient to a different (equal-valued) element: compare sums
+        assert abs(dx.float().sum().item() - xr.grad.sum().item()) <= 2e-2 * xr.grad.abs().sum().item()
+        frac = ((dx.float() - xr.grad).abs() > 1e-2 * xr.grad.abs().max()).float().mean().item()
+        assert frac < 5e-3, f"mismatching fraction {frac}"
+
+
+def test_upsample_add_and_relu_colsum():
+    n, c = 2, 256
+    for (h, w, th, tw) in [(50, 84, 25, 42), (100, 167, 50, 84), (13, 21, 7, 11)]:
+        lat = torch.randn(n, h, w, c, device=DEV).to(torch.bfloat16)
+        top = torch.randn(n, th, tw, c, device=DEV).to(torch.bfloat16)
+        out = torch.empty_like(lat)
+        native.upsample_add(lat, top, out)
+        tr = top.float().permute(0, 3, 1, 2).requires_grad_(True)
+        up = F.interpolate(tr, size=(h, w), mode="nearest")
+        ref = lat.float() + up.permute(0, 2, 3, 1)
+        assert (out.float() - ref).abs().max() <= 2e-2 * ref.abs().max()
+        dm = torch.randn(n, h, w, c, device=DEV).to(torch.bfloat16)
+        dtop = torch.randn(n, th, tw, c, device=DEV).to(torch.bfloat16)
+        d0 = dtop.float().clone()
+        native.upsample_bwd_add(dm, dtop)
+        up.backward(dm.float().permute(0, 3, 1, 2))
+        ref_d = d0 + tr.grad.permute(0, 2, 3, 1)
+        assert (dtop.float() - ref_d).abs().max() <= 2e-2 * ref_d.abs().max()
+    x = torch.randn(4, 8, 8, 720, device=DEV).to(torch.bfloat16)
+    y = torch.empty_like(x)
+    native.relu(x, y)
+    assert torch.equal(y, F.relu(x))
+    dy = torch.randn_like(x)
+    dx = torch.empty_like(x)
+    native.relu_bwd(y, dy, dx)
+    assert torch.equal(dx, dy * (y > 0))
+    acc = torch.zeros(720, device=DEV)
+    native.colsum(x, 720, acc)
+    assert (acc - x.float().sum(dim=(0, 1, 2))).abs().max() < 1e-2
+
+
+def test_preprocess():
+    src = torch.randint(0, 256, (2, 17, 23, 3), dtype=torch.uint8, device=DEV)
+    dst = torch.empty(2, 17, 23, 8, device=DEV, dtype=torch.bfloat16)
+    mean = [103.939, 116.779, 123.68]
+    native.preprocess(src, dst, mean)
+    ref = (src.float() - torch.tensor(mean, device=DEV)).to(torch.bfloat16)
+    assert torch.equal(dst[..., :3], ref)
+    assert (dst[..., 3:] == 0).all()
+
+
+def test_nms_matches_reference():
+    torch.manual_seed(0)
+    n = 3000
+    xy = torch.rand(n, 2, device=DEV) * 500
+    wh = torch.rand(n, 2, device=DEV) * 80 + 5
+    boxes = torch.cat([xy, xy + wh], dim=1)
+    scores = torch.rand(n, device=DEV)
+    got = native.nms(boxes, scores, 0.5)
+    ref = nms_reference(boxes.cpu(), scores.cpu(), 0.5)
+    assert torch.equal(got.cpu(), ref)
+    import torchvision
+    tv = torchvision.ops.nms(boxes, scores, 0.5)
+    assert torch.equal(got, tv)
+
+
+def test_filter_detections_levels():
+    K = 80
+    H, W = 128, 160
+    shapes = A.guess_shapes((H, W))
+    anchors = A.anchors_for_shape((H, W)).to(DEV)
+    torch.manual_seed(0)
+    B = 2
+    cls_l, reg_l = [], []
+    for (h, w) in shapes:
+        lg = (torch.randn(B, h, w, 9 * K, device=DEV) * 1.5 - 5.0).to(torch.bfloat16)
+        rg = torch.zeros(B, h, w, 40, device=DEV, dtype=torch.bfloat16)
+        rg[..., :36] = (torch.randn(B, h, w, 36, device=DEV) * 0.5).to(torch.bfloat16)
+        cls_l.append(lg); reg_l.append(rg)
+    boxes, scores, labels = native.filter_detections_levels(cls_l, reg_l, K, anchors, (H, W))
+    logits = torch.cat([t.float().reshape(B, -1, K) for t in cls_l], dim=1)
+    regs = torch.cat([t[..., :36].float().reshape(B, -1, 4) for t in reg_l], dim=1)
+    dec = clip_boxes(bbox_transform_inv(anchors.unsqueeze(0), regs), (H, W))
+    probs = torch.sigmoid(logits)
+    for b in range(B):
+        rb, rs, rl = filter_detections_single(dec[b].cpu(), probs[b].cpu())
+        k = int((rl >= 0).sum())
+        assert int((labels[b] >= 0).sum()) == k
+        assert (scores[b, :k].cpu() - rs[:k]).abs().max() < 1e-3
+        assert torch.equal(labels[b, :k].cpu(), rl[:k])
+        assert (boxes[b, :k].cpu() - rb[:k]).abs().max() < 1e-2
