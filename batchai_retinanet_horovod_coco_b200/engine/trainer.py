@@ -1,0 +1,606 @@
+"""Native B200 training/inference engine for RetinaNet (the hot path of this framework).
+
+A static, hand-scheduled executor instead of autograd: the RetinaNet graph is small and fixed,
+so forward, losses, backward and the optimizer are an explicit list of launches of the
+sm_100a kernels in ``csrc/`` over preallocated NHWC bf16 activations.
+
+Memory plan (all persistent, sized once per (batch, H, W)):
+
+* ``P``  fp32 flat master parameters.  Conv weights are stored ``[KH*KW, Cout, Cin]`` (the layout
+  wgrad writes and the working-weight transform reads); biases follow their weights.
+* ``G``  fp32 flat gradients, same offsets as ``P``.  wgrad accumulates straight into it
+  (``red.global.add.v4.f32``), shared heads sum their five levels there, and it IS the allreduce
+  bucket (peer-mapped with CUDA IPC when distributed): no fusion-buffer copies.
+* ``M``, ``V`` fp32 Adam slots; ``Wf``/``Wd`` bf16 working weights (BN scale folded) rebuilt by one
+  table-driven kernel after each optimizer step.
+
+Step order (reference ``train.py:98-105`` + Horovod ``DistributedOptimizer`` semantics,
+SURVEY.md 3.3): forward -> focal + smooth-L1 (fused fwd+bwd) -> backward -> sum g^2 ->
+local global-norm clip factor -> allreduce with the per-rank clip factor and 1/N folded into
+the peer reads -> Keras-Adam -> working weights.
+
+The PyTorch ``RetinaNet`` module (``models/retinanet.py``) stays the source of truth for
+checkpoints: ``load_from_model`` / ``store_to_model`` convert between the two parameter layouts.
+"""
+
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn.functional as F
+
+from ..models.resnet import BLOCKS, tf_same_pad
+from ..models.retinanet import RetinaNet
+from ..ops import anchors as anchor_ops
+from ..ops import native
+from ..ops.conv import round8
+
+CAFFE_MEAN_BGR = (103.939, 116.779, 123.68)
+BF16 = torch.bfloat16
+
+
+def _align4(n: int) -> int:
+    return (n + 3) // 4 * 4
+
+
+class Conv:
+    """One convolution of the model: geometry, flat-buffer offsets, working weights."""
+
+    def __init__(self, name, module, bn=None, stride=1, same=False):
+        w = module.weight
+        self.name = name
+        self.module = module
+        self.bn = bn
+        self.cout, self.cin, self.kh, self.kw = w.shape
+        self.stride = stride
+        self.same = same  # TensorFlow 'same' padding (stride-2 3x3)
+        self.has_bias = module.bias is not None
+        self.taps = self.kh * self.kw
+        self.w_off = self.b_off = -1
+        self.trainable = w.requires_grad
+        self.ldo = round8(self.cout)
+
+    def pads(self, h, w):
+        """(pad_before_h, pad_before_w, out_h, out_w)."""
+        if self.kh == 1:
+            return 0, 0, -(-h // self.stride), -(-w // self.stride)
+        if self.stride == 1:
+            return self.kh // 2, self.kw // 2, h, w
+        ph, pw = tf_same_pad(h, self.kh, self.stride), tf_same_pad(w, self.kw, self.stride)
+        return ph[0], pw[0], -(-h // self.stride), -(-w // self.stride)
+
+    # views into the flat buffers ------------------------------------------------------------
+    def wview(self, flat):
+        return flat[self.w_off:self.w_off + self.taps * self.cout * self.cin].view(self.taps, self.cout, self.cin)
+
+    def bview(self, flat):
+        return flat[self.b_off:self.b_off + self.cout]
+
+
+class NativeTrainer:
+    def __init__(self, backbone: str = "resnet50", num_classes: int = 80, device="cuda", batch: int = 8,
+                 image_hw=(800, 1333), lr: float = 1e-5, clipnorm: float = 0.001, distributed: bool = False,
+                 model: RetinaNet | None = None, freeze_backbone: bool = False, comm=None):
+        native.require()
+        self.device = torch.device(device)
+        self.num_classes = num_classes
+        self.lr = lr
+        self.clipnorm = clipnorm
+        self.beta1, self.beta2, self.eps = 0.9, 0.999, 1e-7
+        self.iterations = 0
+        self.freeze_backbone = freeze_backbone
+        self.model = model if model is not None else RetinaNet(num_classes, backbone)
+        if freeze_backbone:
+            self.model.freeze_backbone()
+        self.backbone_name = self.model.backbone_name
+        self.comm = comm
+        self.distributed = distributed
+        self._build_layers()
+        self._alloc_params()
+        self.load_from_model(self.model)
+        self._plans = {}
+        self._prof = None  # list of (name, cuda event) when profiling
+        self.mean_t = torch.tensor(CAFFE_MEAN_BGR, device=self.device)
+        if distributed and comm is None:
+            from ..parallel.p2p import P2PComm
+            self.comm = P2PComm.from_torch_distributed(self.device)
+        if self.comm is not None and self.comm.world > 1:
+            self._attach_comm()
+
+    # ------------------------------------------------------------------ structure
+    def _build_layers(self):
+        m = self.model
+        bb = m.backbone
+        self.stem = Conv("conv1", bb.conv1, bb.bn_conv1, stride=2)
+        self.blocks = []  # list of stages, each a list of dicts
+        for stage in bb.stages:
+            st = []
+            for blk in stage:
+                d = {"a": Conv(f"res{blk.name}_branch2a", blk.branch2a, blk.bn2a, stride=blk.stride),
+                     "b": Conv(f"res{blk.name}_branch2b", blk.branch2b, blk.bn2b),
+                     "c": Conv(f"res{blk.name}_branch2c", blk.branch2c, blk.bn2c),
+                     "s": Conv(f"res{blk.name}_branch1", blk.branch1, blk.bn1, stride=blk.stride) if blk.project else None,
+                     "stride": blk.stride}
+                st.append(d)
+            self.blocks.append(st)
+        f = m.fpn
+        self.fpn = {n: Conv(n, getattr(f, n), stride=(2 if n in ("P6", "P7") else 1), same=n in ("P6", "P7"))
+                    for n in f.LAYER_ORDER}
+        self.reg_tower = [Conv(f"pyramid_regression_{i}", c) for i, c in enumerate(m.regression_submodel.tower)]
+        self.reg_out = Conv("pyramid_regression", m.regression_submodel.out)
+        self.cls_tower = [Conv(f"pyramid_classification_{i}", c) for i, c in enumerate(m.classification_submodel.tower)]
+        self.cls_out = Conv("pyramid_classification", m.classification_submodel.out)
+        # backward-completion order: heads, FPN, backbone stages 5..2, stem
+        order = [self.cls_out] + self.cls_tower[::-1] + [self.reg_out] + self.reg_tower[::-1]
+        order += [self.fpn[n] for n in ("P7", "P6", "P3", "C3_reduced", "P4", "C4_reduced", "P5", "C5_reduced")]
+        for st in self.blocks[::-1]:
+            for d in st[::-1]:
+                order += [d["c"], d["b"], d["a"]] + ([d["s"]] if d["s"] is not None else [])
+        order.append(self.stem)
+        self.convs = order
+
+    def _alloc_params(self):
+        dev = self.device
+        off = 0
+        for c in self.convs:  # trainable first so that [0, n_train) is the allreduce range
+            if not c.trainable:
+                continue
+            c.w_off = off
+            off = _align4(off + c.taps * c.cout * c.cin)
+            if c.has_bias:
+                c.b_off = off
+                off = _align4(off + c.cout)
+        self.n_train = off
+        for c in self.convs:
+            if c.trainable:
+                continue
+            c.w_off = off
+            off = _align4(off + c.taps * c.cout * c.cin)
+            if c.has_bias:
+                c.b_off = off
+                off = _align4(off + c.cout)
+        self.n_params = off
+        pad = 64
+        self.P = torch.zeros(off + pad, device=dev)
+        self.M = torch.zeros(self.n_train + pad, device=dev)
+        self.V = torch.zeros(self.n_train + pad, device=dev)
+        self.G = torch.zeros(self.n_train + pad, device=dev)
+        self.Gavg = self.G
+        # frozen BN affine per conv
+        nbn = sum(round8(c.cout) for c in self.convs if c.bn is not None)
+        self.bn_scale = torch.ones(nbn, device=dev)
+        self.bn_shift = torch.zeros(nbn, device=dev)
+        o = 0
+        for c in self.convs:
+            if c.bn is not None:
+                c.scale = self.bn_scale[o:o + c.cout]
+                c.shift = self.bn_shift[o:o + c.cout]
+                o += round8(c.cout)
+            else:
+                c.scale = None
+                c.shift = None
+        # bf16 working weights
+        entries = []
+        for c in self.convs:
+            if c is self.stem:
+                continue
+            c.wf = torch.zeros(c.taps, c.cout, round8(c.cin), device=dev, dtype=BF16)
+            need_d = not (self.freeze_backbone and not c.trainable)
+            c.wd = torch.zeros(c.taps, c.cin, round8(c.cout), device=dev, dtype=BF16) if need_d else None
+            entries.append(dict(src=c.wview(self.P), scale=c.scale, dst_f=c.wf, dst_d=c.wd, taps=c.taps, Cout=c.cout,
+                                Cin=c.cin))
+        self.wtable = native.WeightTable(entries)
+        # small device scalars
+        self.scal = torch.zeros(8, device=dev)           # [0] sumsq  [1] clip scale  [2] reg loss  [3] cls loss
+        self.npos = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    # ------------------------------------------------------------------ parameter import / export
+    @torch.no_grad()
+    def load_from_model(self, model: RetinaNet | None = None):
+        for c in self.convs:
+            w = c.module.weight.detach().to(self.device, torch.float32)
+            c.wview(self.P).copy_(w.permute(2, 3, 0, 1).reshape(c.taps, c.cout, c.cin))
+            if c.has_bias:
+                c.bview(self.P).copy_(c.module.bias.detach().to(self.device, torch.float32))
+            if c.bn is not None:
+                s, t = c.bn.scale_shift()
+                c.scale.copy_(s.to(self.device))
+                c.shift.copy_(t.to(self.device))
+        self._refresh_weights()
+
+    @torch.no_grad()
+    def store_to_model(self, model: RetinaNet | None = None):
+        for c in self.convs:
+            w = c.wview(self.P).view(c.kh, c.kw, c.cout, c.cin).permute(2, 3, 0, 1)
+            c.module.weight.data.copy_(w.to(c.module.weight.device))
+            if c.has_bias:
+                c.module.bias.data.copy_(c.bview(self.P).to(c.module.bias.device))
+        return self.model
+
+    def _refresh_weights(self):
+        self.wtable.run()
+        s = self.stem
+        w = s.wview(self.P).view(s.kh, s.kw, s.cout, s.cin).permute(2, 3, 0, 1)
+        self.stem_w = w.to(BF16).contiguous(memory_format=torch.channels_last)
+
+    def optimizer_state(self):
+        """Adam slots as {keras layer name: {'kernel': (m, v), 'bias': (m, v)}} views + iterations."""
+        return {"iterations": self.iterations, "lr": self.lr, "M": self.M, "V": self.V}
+
+    # ------------------------------------------------------------------ per-shape plan
+    def _plan(self, B, H, W):
+        key = (B, H, W)
+        if key in self._plans:
+            return self._plans[key]
+        dev = self.device
+        p = {}
+
+        def buf(h, w, c, zero=False):
+            return (torch.zeros if zero else torch.empty)(B, h, w, c, device=dev, dtype=BF16)
+
+        p["img"] = torch.empty(B, H, W, 3, device=dev, dtype=BF16)
+        h1, w1 = -(-H // 2), -(-W // 2)
+        p["stem_raw_hw"] = (h1, w1)
+        ph, pw = tf_same_pad(h1, 3, 2), tf_same_pad(w1, 3, 2)
+        p["pool_pad"] = (ph[0], pw[0])
+        h2, w2 = -(-h1 // 2), -(-w1 // 2)
+        p["pool"] = buf(h2, w2, 64)
+        p["pool_idx"] = torch.empty(B, h2, w2, 64, device=dev, dtype=torch.uint8)
+        acts = []
+        hh, ww = h2, w2
+        for st in self.blocks:
+            sacts = []
+            for d in st:
+                s = d["stride"]
+                ho, wo = -(-hh // s), -(-ww // s)
+                f = d["a"].cout
+                sacts.append({"a": buf(ho, wo, f), "b": buf(ho, wo, f), "o": buf(ho, wo, f * 4),
+                              "s": buf(ho, wo, f * 4) if d["s"] is not None else None, "in_hw": (hh, ww),
+                              "hw": (ho, wo)})
+                hh, ww = ho, wo
+            acts.append(sacts)
+        p["acts"] = acts
+        c3hw, c4hw, c5hw = acts[1][-1]["hw"], acts[2][-1]["hw"], acts[3][-1]["hw"]
+        p6hw = (-(-c5hw[0] // 2), -(-c5hw[1] // 2))
+        p7hw = (-(-p6hw[0] // 2), -(-p6hw[1] // 2))
+        lv = [c3hw, c4hw, c5hw, p6hw, p7hw]
+        p["levels"] = lv
+        fp = {"c5r": buf(*c5hw, 256), "m4": buf(*c4hw, 256), "m3": buf(*c3hw, 256), "r6": buf(*p6hw, 256)}
+        fp["P"] = [buf(h, w, 256) for (h, w) in lv]
+        p["fpn"] = fp
+        K = self.num_classes
+        p["cls_t"] = [[buf(h, w, 256) for (h, w) in lv] for _ in range(4)]
+        p["reg_t"] = [[buf(h, w, 256) for (h, w) in lv] for _ in range(4)]
+        p["cls_o"] = [buf(h, w, round8(9 * K), zero=True) for (h, w) in lv]
+        p["reg_o"] = [buf(h, w, 40, zero=True) for (h, w) in lv]
+        # gradient scratch
+        p["dcls_o"] = [buf(h, w, round8(9 * K), zero=True) for (h, w) in lv]
+        p["dreg_o"] = [buf(h, w, 40, zero=True) for (h, w) in lv]
+        p["dt"] = [[buf(h, w, 256) for (h, w) in lv] for _ in range(2)]
+        p["dP"] = [buf(h, w, 256) for (h, w) in lv]
+        p["dfpn"] = {"m3": buf(*c3hw, 256), "m4": buf(*c4hw, 256), "c5r": buf(*c5hw, 256), "p6": buf(*p6hw, 256)}
+        # backbone gradient buffers, sized per stage
+        gb = []
+        for si, st in enumerate(self.blocks):
+            a0 = acts[si][0]
+            f = st[0]["a"].cout
+            ho, wo = a0["hw"]
+            gb.append({"g": buf(ho, wo, f * 4), "ga": buf(ho, wo, f), "gb": buf(ho, wo, f),
+                       "gx": buf(*a0["in_hw"], st[0]["a"].cin), "tmp": buf(*a0["in_hw"], st[0]["a"].cin)})
+        p["gb"] = gb
+        p["dstem"] = torch.empty(B, h1, w1, 64, device=dev, dtype=BF16)
+        # anchors + targets
+        p["anchors"] = native.anchors_for_shape_gpu(lv, dev)
+        A = p["anchors"].shape[0]
+        p["A"] = A
+        p["state"] = torch.empty(B, A, dtype=torch.int8, device=dev)
+        p["cls_id"] = torch.empty(B, A, dtype=torch.int16, device=dev)
+        p["reg_t_tgt"] = torch.empty(B, A, 4, device=dev)
+        p["a_off"] = [0]
+        for (h, w) in lv:
+            p["a_off"].append(p["a_off"][-1] + h * w * 9)
+        self._plans[key] = p
+        return p
+
+    # ------------------------------------------------------------------ kernels wrappers
+    def _fprop(self, c: Conv, x, out, relu=False, add=None):
+        h, w = x.shape[1:3]
+        ph, pw, _, _ = c.pads(h, w)
+        shift = c.shift if c.bn is not None else (c.bview(self.P) if c.has_bias else None)
+        native.conv_raw(0, [(x, out, add, None)], c.wf, c.cin, x.shape[-1], c.cout, out.shape[-1], c.kh, c.kw,
+                        c.stride, ph, pw, shift=shift, relu=relu)
+
+    def _fprop_group(self, c: Conv, xs, outs, relu=False):
+        native.conv_raw(0, [(x, o, None, None) for x, o in zip(xs, outs)], c.wf, c.cin, xs[0].shape[-1], c.cout,
+                        outs[0].shape[-1], c.kh, c.kw, 1, c.kh // 2, c.kw // 2, shift=c.bview(self.P), relu=relu)
+
+    def _dgrad(self, c: Conv, dy, out, mask=None, add=None, add_after_mask=False):
+        """Gradient w.r.t. the conv input.  out [N,H,W,cin]."""
+        h, w = out.shape[1:3]
+        ph, pw, _, _ = c.pads(h, w)
+        if c.stride == 1:
+            native.conv_raw(1, [(dy, out, add, mask)], c.wd, c.cout, dy.shape[-1], c.cin, out.shape[-1], c.kh, c.kw, 1,
+                            ph, pw, add_after_mask=add_after_mask)
+            return
+        for py in range(2):
+            for px in range(2):
+                ok = any((py + ph - r) % 2 == 0 for r in range(c.kh)) and any((px + pw - s) % 2 == 0 for s in range(c.kw))
+                if ok:
+                    native.conv_raw(1, [(dy, out, add, mask)], c.wd, c.cout, dy.shape[-1], c.cin, out.shape[-1], c.kh,
+                                    c.kw, 2, ph, pw, par=(py, px), add_after_mask=add_after_mask)
+
+    def _dgrad_group(self, c: Conv, dys, outs, masks=None, adds=None):
+        probs = [(dy, o, None if adds is None else adds[i], None if masks is None else masks[i])
+                 for i, (dy, o) in enumerate(zip(dys, outs))]
+        native.conv_raw(1, probs, c.wd, c.cout, dys[0].shape[-1], c.cin, outs[0].shape[-1], c.kh, c.kw, 1, c.kh // 2,
+                        c.kw // 2)
+
+    def _wgrad(self, c: Conv, xs, dys):
+        if not c.trainable:
+            return
+        h, w = xs[0].shape[1:3]
+        ph, pw, _, _ = c.pads(h, w)
+        native.wgrad_raw(list(zip(xs, dys)), c.wview(self.G), c.cin, xs[0].shape[-1], c.cout, dys[0].shape[-1], c.kh,
+                         c.kw, c.stride, ph, pw, rowscale=c.scale, dbias=c.bview(self.G) if c.has_bias else None)
+
+    # ------------------------------------------------------------------ forward
+    def _forward(self, p, images_u8):
+        B, H, W, _ = images_u8.shape
+        native.preprocess(images_u8, p["img"], CAFFE_MEAN_BGR)
+        x = p["img"].permute(0, 3, 1, 2)
+        raw = F.conv2d(x, self.stem_w, stride=2, padding=3)  # cuDNN; Cin=3 does not fit a 64-wide K tile
+        p["stem_raw"] = raw.permute(0, 2, 3, 1)
+        if not p["stem_raw"].is_contiguous():
+            p["stem_raw"] = p["stem_raw"].contiguous()
+        native.bn_relu_maxpool_fwd(p["stem_raw"], self.stem.scale, self.stem.shift, p["pool"], p["pool_idx"],
+                                   *p["pool_pad"])
+        self._mark("fwd_stem")
+        x = p["pool"]
+        for si, st in enumerate(self.blocks):
+            for bi, d in enumerate(st):
+                a = p["acts"][si][bi]
+                self._fprop(d["a"], x, a["a"], relu=True)
+                self._fprop(d["b"], a["a"], a["b"], relu=True)
+                if d["s"] is not None:
+                    self._fprop(d["s"], x, a["s"])
+                    self._fprop(d["c"], a["b"], a["o"], relu=True, add=a["s"])
+                else:
+                    self._fprop(d["c"], a["b"], a["o"], relu=True, add=x)
+                a["x"] = x
+                x = a["o"]
+        self._mark("fwd_backbone")
+        c3, c4, c5 = p["acts"][1][-1]["o"], p["acts"][2][-1]["o"], p["acts"][3][-1]["o"]
+        fp, f = p["fpn"], self.fpn
+        P3, P4, P5, P6, P7 = fp["P"]
+        self._fprop(f["C5_reduced"], c5, fp["c5r"])
+        self._fprop(f["P5"], fp["c5r"], P5)
+        self._fprop(f["C4_reduced"], c4, fp["m4"])
+        native.upsample_add(fp["m4"], fp["c5r"], fp["m4"])
+        self._fprop(f["P4"], fp["m4"], P4)
+        self._fprop(f["C3_reduced"], c3, fp["m3"])
+        native.upsample_add(fp["m3"], fp["m4"], fp["m3"])
+        self._fprop(f["P3"], fp["m3"], P3)
+        self._fprop(f["P6"], c5, P6)
+        native.relu(P6, fp["r6"])
+        self._fprop(f["P7"], fp["r6"], P7)
+        self._mark("fwd_fpn")
+        for tower, outc, ts, outs in ((self.cls_tower, self.cls_out, p["cls_t"], p["cls_o"]),
+                                      (self.reg_tower, self.reg_out, p["reg_t"], p["reg_o"])):
+            xs = fp["P"]
+            for i, c in enumerate(tower):
+                self._fprop_group(c, xs, ts[i], relu=True)
+                xs = ts[i]
+            self._fprop_group(outc, xs, outs)
+
+    # ------------------------------------------------------------------ losses (fused fwd+bwd)
+    def _losses(self, p, gt, gt_count, img_hw):
+        self.npos.zero_()
+        self.scal.zero_()
+        native.assign_targets(p["anchors"], gt, gt_count, img_hw, p["state"], p["cls_id"], p["reg_t_tgt"], self.npos)
+        A = p["A"]
+        for l in range(5):
+            native.focal_loss(p["cls_o"][l], p["dcls_o"][l], self.num_classes, p["state"], p["cls_id"], A,
+                              p["a_off"][l], self.npos, self.scal[3:4])
+            native.smooth_l1(p["reg_o"][l], p["dreg_o"][l], p["state"], p["reg_t_tgt"], A, p["a_off"][l], self.npos,
+                             self.scal[2:3])
+
+    # ------------------------------------------------------------------ backward
+    def _backward(self, p):
+        fp, f = p["fpn"], self.fpn
+        feats = fp["P"]
+        dP = p["dP"]
+        first = True
+        for tower, outc, ts, douts in ((self.cls_tower, self.cls_out, p["cls_t"], p["dcls_o"]),
+                                       (self.reg_tower, self.reg_out, p["reg_t"], p["dreg_o"])):
+            self._wgrad(outc, ts[3], douts)
+            cur = p["dt"][0]
+            self._dgrad_group(outc, douts, cur, masks=ts[3])
+            for i in (3, 2, 1):
+                self._wgrad(tower[i], ts[i - 1], cur)
+                nxt = p["dt"][1] if cur is p["dt"][0] else p["dt"][0]
+                self._dgrad_group(tower[i], cur, nxt, masks=ts[i - 1])
+                cur = nxt
+            self._wgrad(tower[0], feats, cur)
+            self._dgrad_group(tower[0], cur, dP, adds=None if first else dP)
+            first = False
+        self._mark("bwd_heads")
+        dP3, dP4, dP5, dP6, dP7 = dP
+        df = p["dfpn"]
+        c3, c4, c5 = p["acts"][1][-1]["o"], p["acts"][2][-1]["o"], p["acts"][3][-1]["o"]
+        P6 = feats[3]
+        # P7 = conv(relu(P6)); P6 also feeds the heads directly
+        self._wgrad(f["P7"], [fp["r6"]], [dP7])
+        self._dgrad(f["P7"], dP7, df["p6"], mask=P6, add=dP6, add_after_mask=True)
+        self._wgrad(f["P6"], [c5], [df["p6"]])
+        # P3 branch
+        self._wgrad(f["P3"], [fp["m3"]], [dP3])
+        self._dgrad(f["P3"], dP3, df["m3"])
+        self._wgrad(f["C3_reduced"], [c3], [df["m3"]])
+        # P4 branch
+        self._wgrad(f["P4"], [fp["m4"]], [dP4])
+        self._dgrad(f["P4"], dP4, df["m4"])
+        native.upsample_bwd_add(df["m3"], df["m4"])
+        self._wgrad(f["C4_reduced"], [c4], [df["m4"]])
+        # P5 branch
+        self._wgrad(f["P5"], [fp["c5r"]], [dP5])
+        self._dgrad(f["P5"], dP5, df["c5r"])
+        native.upsample_bwd_add(df["m4"], df["c5r"])
+        self._wgrad(f["C5_reduced"], [c5], [df["c5r"]])
+        self._mark("bwd_fpn")
+        if self.freeze_backbone:
+            return
+        gb = p["gb"]
+        # gradient w.r.t. C5 / C4 / C3 from the FPN (masked by the ReLU of the block output)
+        g5 = gb[3]["g"]
+        self._dgrad(f["C5_reduced"], df["c5r"], g5)
+        self._dgrad(f["P6"], df["p6"], g5, mask=c5, add=g5)
+        extra = {2: (f["C4_reduced"], df["m4"]), 1: (f["C3_reduced"], df["m3"])}
+        g = g5
+        for si in (3, 2, 1, 0):
+            st = self.blocks[si]
+            acts = p["acts"][si]
+            b = gb[si]
+            for bi in range(len(st) - 1, -1, -1):
+                d, a = st[bi], acts[bi]
+                x = a["x"]
+                self._wgrad(d["c"], [a["b"]], [g])
+                self._dgrad(d["c"], g, b["gb"], mask=a["b"])
+                self._wgrad(d["b"], [a["a"]], [b["gb"]])
+                self._dgrad(d["b"], b["gb"], b["ga"], mask=a["a"])
+                self._wgrad(d["a"], [x], [b["ga"]])
+                if d["s"] is None:
+                    self._dgrad(d["a"], b["ga"], g, mask=x, add=g)  # in place: g <- mask(dgrad + g)
+                else:
+                    self._wgrad(d["s"], [x], [g])
+                    gx = b["gx"]
+                    if d["stride"] == 1:
+                        self._dgrad(d["s"], g, b["tmp"])
+                        self._dgrad(d["a"], b["ga"], gx, mask=x, add=b["tmp"])
+                    else:
+                        gx.zero_()
+                        self._dgrad(d["s"], g, gx)
+                        self._dgrad(d["a"], b["ga"], gx, add=gx)
+                        # + FPN lateral gradient of the previous stage's output, then its ReLU mask
+                        if (si - 1) in extra:
+                            lat, dlat = extra[si - 1]
+                            self._dgrad(lat, dlat, b["tmp"])
+                            native.add_mask(gx, b["tmp"], x, gx)
+                        else:
+                            native.add_mask(gx, None, x, gx)
+                    g_next = gx
+            if si > 0:
+                # gx has the geometry of stage si-1's output: copy into that stage's g buffer
+                gb[si - 1]["g"].copy_(g_next)
+                g = gb[si - 1]["g"]
+            else:
+                g = g_next
+        self._mark("bwd_backbone")
+        # stem: max-pool + ReLU + BN backward, then cuDNN wgrad for the 7x7x3 filter
+        native.bn_relu_maxpool_bwd(p["pool_idx"], self.stem.scale, g, p["dstem"], *p["pool_pad"])
+        if self.stem.trainable:
+            x = p["img"].permute(0, 3, 1, 2)
+            gy = p["dstem"].permute(0, 3, 1, 2)
+            _, dw, _ = torch.ops.aten.convolution_backward(gy, x, self.stem_w, None, [2, 2], [3, 3], [1, 1], False,
+                                                           [0, 0], 1, [False, True, False])
+            s = self.stem
+            s.wview(self.G).add_(dw.float().permute(2, 3, 0, 1).reshape(s.taps, s.cout, s.cin))
+
+    # ------------------------------------------------------------------ optimizer
+    def _attach_comm(self):
+        """Move the gradient bucket into peer-mapped memory and allocate the reduced copy."""
+        self.G = self.comm.symmetric_bucket(self.n_train + 64)
+        self.Gavg = torch.zeros_like(self.G)
+        self.comm.broadcast_(self.P, 0)
+        self._refresh_weights()
+
+    def _optimizer_step(self):
+        n = self.n_train
+        self.iterations += 1
+        t = self.iterations
+        lr_t = self.lr * math.sqrt(1.0 - self.beta2 ** t) / (1.0 - self.beta1 ** t)
+        native.sumsq(self.G[:n], self.scal[0:1])
+        native.clip_scale(self.scal[0:1], self.clipnorm, self.scal[1:2])
+        if self.comm is not None and self.comm.world > 1:
+            self.comm.allreduce_avg(self.G, self.Gavg, n, prescale=self.scal[1:2])
+            native.adam(self.P[:n], self.Gavg[:n], self.M[:n], self.V[:n], None, lr_t, self.beta1, self.beta2, self.eps)
+        else:
+            native.adam(self.P[:n], self.G[:n], self.M[:n], self.V[:n], self.scal[1:2], lr_t, self.beta1, self.beta2,
+                        self.eps)
+        self._refresh_weights()
+
+    def _mark(self, name):
+        if self._prof is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._prof.append((name, ev))
+
+    def profile_step(self, *batch):
+        """Run one step with CUDA events between phases; returns {phase: ms} (device time)."""
+        self._prof = []
+        self._mark("start")
+        self.train_step(*batch)
+        torch.cuda.synchronize()
+        out = {}
+        for (n0, e0), (n1, e1) in zip(self._prof[:-1], self._prof[1:]):
+            out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+        self._prof = None
+        return out
+
+    # ------------------------------------------------------------------ public API
+    def train_step(self, images_u8, gt, gt_count, img_hw):
+        """One optimisation step.  Inputs may live in (pinned) host memory or on the device:
+        images uint8 [B,H,W,3] BGR, gt fp32 [B,G,5] (x1,y1,x2,y2,label), gt_count int32 [B],
+        img_hw int32 [B,2] un-padded sizes.  Returns a device tensor [loss, regression_loss,
+        classification_loss] (the Keras metric names of reference train.py:99-102)."""
+        dev = self.device
+        images_u8 = images_u8.to(dev, non_blocking=True)
+        gt = gt.to(dev, torch.float32, non_blocking=True)
+        gt_count = gt_count.to(dev, torch.int32, non_blocking=True)
+        img_hw = img_hw.to(dev, torch.int32, non_blocking=True)
+        B, H, W, _ = images_u8.shape
+        p = self._plan(B, H, W)
+        self.G.zero_()
+        self._mark("h2d+zero")
+        self._forward(p, images_u8)
+        self._mark("forward")
+        self._losses(p, gt, gt_count, img_hw)
+        self._mark("losses")
+        self._backward(p)
+        self._mark("backward")
+        self._optimizer_step()
+        self._mark("optimizer")
+        return torch.stack([self.scal[2] + self.scal[3], self.scal[2], self.scal[3]])
+
+    @torch.no_grad()
+    def forward_loss(self, images_u8, gt, gt_count, img_hw):
+        """Forward + losses + backward WITHOUT the optimizer (testing / gradient checks)."""
+        dev = self.device
+        images_u8 = images_u8.to(dev)
+        B, H, W, _ = images_u8.shape
+        p = self._plan(B, H, W)
+        self.G.zero_()
+        self._forward(p, images_u8)
+        self._losses(p, gt.to(dev, torch.float32), gt_count.to(dev, torch.int32), img_hw.to(dev, torch.int32))
+        self._backward(p)
+        return torch.stack([self.scal[2] + self.scal[3], self.scal[2], self.scal[3]]), p
+
+    @torch.no_grad()
+    def predict(self, images_u8, score_threshold=0.05, max_detections=300, nms_threshold=0.5):
+        """Prediction graph (reference train.py:95): boxes [B,300,4], scores [B,300], labels [B,300]."""
+        images_u8 = images_u8.to(self.device)
+        B, H, W, _ = images_u8.shape
+        p = self._plan(B, H, W)
+        self._forward(p, images_u8)
+        return native.filter_detections_levels(p["cls_o"], p["reg_o"], self.num_classes, p["anchors"], (H, W),
+                                               score_threshold, nms_threshold, max_detections)
+
+    def gradients_by_layer(self):
+        """{keras layer name: (dW OIHW fp32, db or None)} from the flat gradient buffer (tests)."""
+        out = {}
+        for c in self.convs:
+            if not c.trainable:
+                continue
+            w = c.wview(self.G).view(c.kh, c.kw, c.cout, c.cin).permute(2, 3, 0, 1).contiguous()
+            out[c.name] = (w, c.bview(self.G).clone() if c.has_bias else None)
+        return out

@@ -35,7 +35,7 @@ class ConvArgs(C.Structure):
                 ("weight", C.c_void_p), ("K", C.c_int), ("ldi", C.c_int), ("Nrows", C.c_int), ("ldw", C.c_int),
                 ("ldo", C.c_int), ("KH", C.c_int), ("KW", C.c_int), ("stride", C.c_int), ("pad_h", C.c_int),
                 ("pad_w", C.c_int), ("par_y", C.c_int), ("par_x", C.c_int), ("shift", C.c_void_p),
-                ("relu", C.c_int), ("out_fp32", C.c_int)]
+                ("relu", C.c_int), ("out_fp32", C.c_int), ("add_after_mask", C.c_int)]
 
 
 class WgradProblem(C.Structure):
@@ -127,7 +127,8 @@ def same_pad_before(n: int, k: int, s: int) -> int:
 
 
 def conv_raw(mode: int, problems, weight: torch.Tensor, K: int, ldi: int, Nrows: int, ldo: int, KH: int, KW: int,
-             stride: int, pad_h: int, pad_w: int, shift=None, relu=False, out_fp32=False, par=(0, 0)):
+             stride: int, pad_h: int, pad_w: int, shift=None, relu=False, out_fp32=False, par=(0, 0),
+             add_after_mask=False):
     """problems: list of (inp, out, add, mask) NHWC tensors.  weight: bf16 [taps, Nrows, ldw]."""
     lib = require()
     a = ConvArgs()
@@ -147,6 +148,7 @@ def conv_raw(mode: int, problems, weight: torch.Tensor, K: int, ldi: int, Nrows:
     a.shift = 0 if shift is None else shift.data_ptr()
     a.relu = int(relu)
     a.out_fp32 = int(out_fp32)
+    a.add_after_mask = int(add_after_mask)
     _check(lib.b200_conv(C.byref(a), _stream()), "b200_conv")
 
 
@@ -195,16 +197,16 @@ class WeightTable:
 
 
 # ------------------------------------------------------------------------------ elementwise
-def bn_relu_maxpool_fwd(x, scale, shift, y, pad_h, pad_w):
+def bn_relu_maxpool_fwd(x, scale, shift, y, idx, pad_h, pad_w):
     n, h, w, c = x.shape
-    _check(_load().b200_bn_relu_maxpool_fwd(_ptr(x), _ptr(scale), _ptr(shift), _ptr(y), n, h, w, c, y.shape[1],
-                                            y.shape[2], pad_h, pad_w, _stream()), "bn_relu_maxpool_fwd")
+    _check(_load().b200_bn_relu_maxpool_fwd(_ptr(x), _ptr(scale), _ptr(shift), _ptr(y), _ptr(idx), n, h, w, c,
+                                            y.shape[1], y.shape[2], pad_h, pad_w, _stream()), "bn_relu_maxpool_fwd")
 
 
-def bn_relu_maxpool_bwd(x, scale, shift, y, dy, dx, pad_h, pad_w):
-    n, h, w, c = x.shape
-    _check(_load().b200_bn_relu_maxpool_bwd(_ptr(x), _ptr(scale), _ptr(shift), _ptr(y), _ptr(dy), _ptr(dx), n, h, w,
-                                            c, y.shape[1], y.shape[2], pad_h, pad_w, _stream()), "bn_relu_maxpool_bwd")
+def bn_relu_maxpool_bwd(idx, scale, dy, dx, pad_h, pad_w):
+    n, h, w, c = dx.shape
+    _check(_load().b200_bn_relu_maxpool_bwd(_ptr(idx), _ptr(scale), _ptr(dy), _ptr(dx), n, h, w, c, dy.shape[1],
+                                            dy.shape[2], pad_h, pad_w, _stream()), "bn_relu_maxpool_bwd")
 
 
 def upsample_add(lateral, top, out):
@@ -225,6 +227,10 @@ def relu(x, y):
 
 def relu_bwd(y, dy, dx):
     _check(_load().b200_relu_bwd(_ptr(y), _ptr(dy), _ptr(dx), C.c_longlong(y.numel()), _stream()), "relu_bwd")
+
+
+def add_mask(a, b, mask, out):
+    _check(_load().b200_add_mask(_ptr(a), _ptr(b), _ptr(mask), _ptr(out), C.c_longlong(a.numel()), _stream()), "add_mask")
 
 
 def colsum(x2d, cols, out_accum):

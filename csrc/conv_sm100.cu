@@ -6,11 +6,12 @@
 // (dh, dw) shift of the TMA box and the conv halo / padding is TMA's out-of-bounds zero fill),
 // N = output channels (BN <= 256 per tile), K = taps x input channels (64 per pipeline stage).
 //
-// Warp roles (256 threads, 1 CTA per SM, persistent over tiles):
+// Warp roles (384 threads, 1 CTA per SM, persistent over tiles):
 //   warp 0   TMA producer  (one lane): A box [64ch, tw, th, 1] + B box [64ch, BN rows, 1 tap]
 //   warp 1   MMA issuer    (one lane): 4 x tcgen05.mma (K=16) per stage, commit -> empty barrier
 //   warp 2   TMEM allocator (512 columns = two 256-column accumulators, double-buffered)
-//   warps 4-7 epilogue: tcgen05.ld 32 lanes x 32 columns, fused shift/add/mask/ReLU, bf16 store
+//   warps 4-11 epilogue (2 per TMEM lane quarter): tcgen05.ld 32 lanes x 32 columns, fused
+//            shift/add/mask/ReLU, swizzled smem transpose, coalesced bf16 loads/stores
 //
 // Stride-2 convolutions use one tensor map per input parity class (strided views), so every
 // tap is still a plain shifted box.  Stride-2 dgrad computes one output parity class per launch.
@@ -31,8 +32,10 @@ constexpr int kBStageBytes = 256 * kBK * 2;       // 32 KB (BN <= 256)
 constexpr int kMaxTaps = 49;
 constexpr int kMaxMaps = 8;
 constexpr int kTmemCols = 512;
-constexpr int kConvThreads = 256;
-constexpr int kSmemBytes = kStages * (kAStageBytes + kBStageBytes) + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kEpiWarps = 8;                         // 2 warps per TMEM lane quarter (column halves)
+constexpr int kConvThreads = 128 + 32 * kEpiWarps;
+constexpr int kStagingBytes = kEpiWarps * 4096;      // per epilogue warp: 2 KB add/out + 2 KB mask
+constexpr int kSmemBytes = kStages * (kAStageBytes + kBStageBytes) + kStagingBytes + 1024 /*align*/ + 256 /*barriers*/;
 
 struct Tap {
   int8_t dh, dw, map, pad;
@@ -61,7 +64,7 @@ struct ConvParams {
   int Nrows, ldo, BN;
   int num_taps, num_kc;
   int os, oy, ox;       // output scatter: (y*os + oy, x*os + ox)
-  int relu, out_fp32;
+  int relu, out_fp32, add_after_mask;
 };
 
 __device__ __forceinline__ void decode_tile(const ConvParams& p, int tile, int& pi, int& n, int& y0, int& x0,
@@ -88,7 +91,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t a_smem = smem_base;
   const uint32_t b_smem = smem_base + kStages * kAStageBytes;
-  const uint32_t bar_base = b_smem + kStages * kBStageBytes;
+  const uint32_t stg_base = b_smem + kStages * kBStageBytes;
+  const uint32_t bar_base = stg_base + kStagingBytes;
   // barrier layout (8 bytes each): full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], tmem_ptr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
@@ -113,7 +117,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 128);
+      mbar_init(tempty_bar(a), 32 * kEpiWarps);
     }
     fence_barrier_init();
   }
@@ -188,8 +192,18 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------------ epilogue
-    const int quarter = warp - 4;
+    // Each warp owns 32 accumulator rows (TMEM lanes).  A thread holds one row, but row-per-thread
+    // global accesses would touch 32 lines per instruction with partial sectors, so every 32-column
+    // chunk goes through a warp-private, XOR-swizzled smem transpose: global <-> smem transfers are
+    // 8 rows x 64 B per instruction (sector-complete), smem <-> registers are row-per-thread.
+    const int ew = warp - 4;
+    const int quarter = ew & 3;   // TMEM lanes this warp may read: 32 * (warp_id % 4)
+    const int chalf = ew >> 2;    // which 32-column chunks of the tile this warp handles
     const int m = quarter * 32 + lane;
+    const uint32_t buf_a = stg_base + ew * 4096;  // add in / result out
+    const uint32_t buf_m = buf_a + 2048;               // mask
+    const int crow = lane >> 2, cpiece = lane & 3;
+    const uint32_t own_sw = (lane >> 1) & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -199,76 +213,132 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       const int y = y0 + (m >> q.tw_log2);
       const int x = x0 + (m & ((1 << q.tw_log2) - 1));
       const bool valid = (y < q.OH) && (x < q.OW);
-      const long long pix = (static_cast<long long>(n) * q.OHo + (y * p.os + p.oy)) * q.OWo + (x * p.os + p.ox);
-      const long long row_off = pix * p.ldo;
+      const int pix = (n * q.OHo + (y * p.os + p.oy)) * q.OWo + (x * p.os + p.ox);  // < 2^31 pixels
+      const long long row_off = static_cast<long long>(pix) * p.ldo;
+      const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
+      int pix_r[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) pix_r[i] = __shfl_sync(0xffffffffu, pix, i * 8 + crow);
       const int col0 = n_tile * p.BN;
       const int col_end = min(p.Nrows, col0 + p.BN);
+      const int col_end_pad = (col_end + 7) & ~7;
+      const __nv_bfloat16* addp = static_cast<const __nv_bfloat16*>(q.add);
+      const __nv_bfloat16* maskp = static_cast<const __nv_bfloat16*>(q.mask);
 
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * 256;
-      for (int c = 0; c < p.BN; c += 32) {
+      for (int c = chalf * 32; c < p.BN; c += 64) {
+        const int col = col0 + c;
+        if (col >= col_end) break;
         uint32_t r[32];
         tmem_ld_32x32(t_row + c, r);
-        tmem_ld_wait();
-        if (valid) {
+        if (p.out_fp32) {
+          // rarely used (debug / fp32 head outputs): direct row-per-thread path
+          tmem_ld_wait();
+          if (valid) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            const int col = col0 + c + j;
-            if (col < col_end) {
-              float v[8];
+            for (int j = 0; j < 32; ++j) {
+              if (col + j >= col_end) continue;
+              float v = __uint_as_float(r[j]);
+              if (p.shift) v += __ldg(p.shift + col + j);
+              if (addp && !p.add_after_mask) v += __bfloat162float(addp[row_off + col + j]);
+              if (maskp && !(__bfloat162float(maskp[row_off + col + j]) > 0.f)) v = 0.f;
+              if (addp && p.add_after_mask) v += __bfloat162float(addp[row_off + col + j]);
+              if (p.relu) v = fmaxf(v, 0.f);
+              static_cast<float*>(q.out)[row_off + col + j] = v;
+            }
+          }
+          continue;
+        }
+        // ---- coalesced global -> smem for the epilogue operands
+        if (addp || maskp) {
 #pragma unroll
-              for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j + e]);
-              if (p.shift) {
-                const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.shift + col));
-                const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.shift + col + 4));
-                v[0] += s0.x; v[1] += s0.y; v[2] += s0.z; v[3] += s0.w;
-                v[4] += s1.x; v[5] += s1.y; v[6] += s1.z; v[7] += s1.w;
+          for (int i = 0; i < 4; ++i) {
+            const int rr = i * 8 + crow;
+            const long long roff = static_cast<long long>(pix_r[i]) * p.ldo;
+            const bool ok = ((valid_mask >> rr) & 1u) && (col + cpiece * 8 < col_end_pad);
+            const uint32_t so = rr * 64 + ((cpiece ^ ((rr >> 1) & 3)) << 4);
+            if (ok) {
+              if (addp) {
+                const uint4 t = *reinterpret_cast<const uint4*>(addp + roff + col + cpiece * 8);
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf_a + so), "r"(t.x), "r"(t.y), "r"(t.z), "r"(t.w) : "memory");
               }
-              if (q.add) {
-                const uint4 a = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(q.add) + row_off + col);
-                v[0] += bf16_lo(a.x); v[1] += bf16_hi(a.x); v[2] += bf16_lo(a.y); v[3] += bf16_hi(a.y);
-                v[4] += bf16_lo(a.z); v[5] += bf16_hi(a.z); v[6] += bf16_lo(a.w); v[7] += bf16_hi(a.w);
-              }
-              if (q.mask) {
-                const uint4 k = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(q.mask) + row_off + col);
-                if (!(bf16_lo(k.x) > 0.f)) v[0] = 0.f;
-                if (!(bf16_hi(k.x) > 0.f)) v[1] = 0.f;
-                if (!(bf16_lo(k.y) > 0.f)) v[2] = 0.f;
-                if (!(bf16_hi(k.y) > 0.f)) v[3] = 0.f;
-                if (!(bf16_lo(k.z) > 0.f)) v[4] = 0.f;
-                if (!(bf16_hi(k.z) > 0.f)) v[5] = 0.f;
-                if (!(bf16_lo(k.w) > 0.f)) v[6] = 0.f;
-                if (!(bf16_hi(k.w) > 0.f)) v[7] = 0.f;
-              }
-              if (p.relu) {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
-              }
-              if (col + 8 <= col_end) {
-                if (p.out_fp32) {
-                  float* o = static_cast<float*>(q.out) + row_off + col;
-                  *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
-                  *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
-                } else {
-                  uint4 o;
-                  o.x = pack_bf16x2(v[0], v[1]);
-                  o.y = pack_bf16x2(v[2], v[3]);
-                  o.z = pack_bf16x2(v[4], v[5]);
-                  o.w = pack_bf16x2(v[6], v[7]);
-                  *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(q.out) + row_off + col) = o;
-                }
-              } else {
-                for (int e = 0; e < col_end - col; ++e) {
-                  if (p.out_fp32)
-                    static_cast<float*>(q.out)[row_off + col + e] = v[e];
-                  else
-                    static_cast<__nv_bfloat16*>(q.out)[row_off + col + e] = __float2bfloat16(v[e]);
-                }
+              if (maskp) {
+                const uint4 t = *reinterpret_cast<const uint4*>(maskp + roff + col + cpiece * 8);
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf_m + so), "r"(t.x), "r"(t.y), "r"(t.z), "r"(t.w) : "memory");
               }
             }
           }
+          __syncwarp();
         }
+        tmem_ld_wait();
+        // ---- row-per-thread math, result into the warp's staging buffer
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int cj = col + j * 8;
+          const uint32_t so = lane * 64 + ((static_cast<uint32_t>(j) ^ own_sw) << 4);
+          float v[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j * 8 + e]);
+          if (valid && cj < col_end) {
+            if (p.shift) {
+              const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.shift + cj));
+              const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.shift + cj + 4));
+              v[0] += s0.x; v[1] += s0.y; v[2] += s0.z; v[3] += s0.w;
+              v[4] += s1.x; v[5] += s1.y; v[6] += s1.z; v[7] += s1.w;
+            }
+            uint4 a = make_uint4(0u, 0u, 0u, 0u);
+            if (addp) asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "r"(buf_a + so));
+            if (addp && !p.add_after_mask) {
+              v[0] += bf16_lo(a.x); v[1] += bf16_hi(a.x); v[2] += bf16_lo(a.y); v[3] += bf16_hi(a.y);
+              v[4] += bf16_lo(a.z); v[5] += bf16_hi(a.z); v[6] += bf16_lo(a.w); v[7] += bf16_hi(a.w);
+            }
+            if (maskp) {
+              uint4 k;
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(k.x), "=r"(k.y), "=r"(k.z), "=r"(k.w) : "r"(buf_m + so));
+              if (!(bf16_lo(k.x) > 0.f)) v[0] = 0.f;
+              if (!(bf16_hi(k.x) > 0.f)) v[1] = 0.f;
+              if (!(bf16_lo(k.y) > 0.f)) v[2] = 0.f;
+              if (!(bf16_hi(k.y) > 0.f)) v[3] = 0.f;
+              if (!(bf16_lo(k.z) > 0.f)) v[4] = 0.f;
+              if (!(bf16_hi(k.z) > 0.f)) v[5] = 0.f;
+              if (!(bf16_lo(k.w) > 0.f)) v[6] = 0.f;
+              if (!(bf16_hi(k.w) > 0.f)) v[7] = 0.f;
+            }
+            if (addp && p.add_after_mask) {
+              v[0] += bf16_lo(a.x); v[1] += bf16_hi(a.x); v[2] += bf16_lo(a.y); v[3] += bf16_hi(a.y);
+              v[4] += bf16_lo(a.z); v[5] += bf16_hi(a.z); v[6] += bf16_lo(a.w); v[7] += bf16_hi(a.w);
+            }
+            if (p.relu) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+            }
+            if (cj + 8 > col_end) {  // channel tail (Nrows not a multiple of 8): keep the padding zero
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                if (cj + e >= col_end) v[e] = 0.f;
+            }
+            const uint32_t o0 = pack_bf16x2(v[0], v[1]), o1 = pack_bf16x2(v[2], v[3]);
+            const uint32_t o2 = pack_bf16x2(v[4], v[5]), o3 = pack_bf16x2(v[6], v[7]);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf_a + so), "r"(o0), "r"(o1), "r"(o2), "r"(o3) : "memory");
+          }
+        }
+        __syncwarp();
+        // ---- coalesced smem -> global store
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int rr = i * 8 + crow;
+          const long long roff = static_cast<long long>(pix_r[i]) * p.ldo;
+          const bool ok = ((valid_mask >> rr) & 1u) && (col + cpiece * 8 < col_end_pad);
+          if (ok) {
+            const uint32_t so = rr * 64 + ((cpiece ^ ((rr >> 1) & 3)) << 4);
+            uint4 t;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(t.x), "=r"(t.y), "=r"(t.z), "=r"(t.w) : "r"(buf_a + so));
+            *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(q.out) + roff + col + cpiece * 8) = t;
+          }
+        }
+        __syncwarp();
       }
       tc_fence_before();
       mbar_arrive(tempty_bar(acc));
@@ -346,6 +416,7 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   p.shift = a->shift;
   p.relu = a->relu;
   p.out_fp32 = a->out_fp32;
+  p.add_after_mask = a->add_after_mask;
   p.os = 1;
   p.oy = p.ox = 0;
 

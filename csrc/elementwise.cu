@@ -66,9 +66,13 @@ __device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
 }
 __device__ __forceinline__ float round_bf16(float x) { return __bfloat162float(__float2bfloat16(x)); }
 
+// Forward also records, per output element, which window position (r*3+s) won (first maximum in
+// scan order; 255 when the maximum is <= 0, i.e. no gradient flows), so that backward is a pure
+// gather over <= 4 windows per input position without re-reading the conv output.
 __global__ void bn_relu_maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ scale,
-                                           const float* __restrict__ shift, __nv_bfloat16* __restrict__ y, int N,
-                                           int H, int W, int C, int OH, int OW, int pad_h, int pad_w) {
+                                           const float* __restrict__ shift, __nv_bfloat16* __restrict__ y,
+                                           uint8_t* __restrict__ idx, int N, int H, int W, int C, int OH, int OW,
+                                           int pad_h, int pad_w) {
   const int cg = C >> 3;
   const long long total = static_cast<long long>(N) * OH * OW * cg;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
@@ -80,8 +84,9 @@ __global__ void bn_relu_maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, 
     const int oh = static_cast<int>(t % OH);
     const int n = static_cast<int>(t / OH);
     float sc[8], sh[8], m[8];
+    uint32_t am[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; m[e] = 0.f; }
+    for (int e = 0; e < 8; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; m[e] = 0.f; am[e] = 255u; }
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
       const int h = oh * 2 - pad_h + r;
@@ -93,16 +98,25 @@ __global__ void bn_relu_maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, 
         float v[8];
         load8(x + ((static_cast<long long>(n) * H + h) * W + w) * C + c, v);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) m[e] = fmaxf(m[e], fmaf(v[e], sc[e], sh[e]));
+        for (int e = 0; e < 8; ++e) {
+          const float z = fmaf(v[e], sc[e], sh[e]);
+          if (z > m[e]) { m[e] = z; am[e] = r * 3 + s; }
+        }
       }
     }
-    store8(y + ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c, m);
+    const long long o = ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c;
+    store8(y + o, m);
+    if (idx) {
+      uint2 pk;
+      pk.x = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
+      pk.y = am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24);
+      *reinterpret_cast<uint2*>(idx + o) = pk;
+    }
   }
 }
 
-// dx = scale * [z > 0] * sum over windows whose (first) arg-max is this position of dy.
-__global__ void bn_relu_maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ scale,
-                                           const float* __restrict__ shift, const __nv_bfloat16* __restrict__ y,
+// dx[n,h,w,c] = scale[c] * sum over windows whose recorded arg-max is (h,w) of dy.
+__global__ void bn_relu_maxpool_bwd_kernel(const uint8_t* __restrict__ idx, const float* __restrict__ scale,
                                            const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N,
                                            int H, int W, int C, int OH, int OW, int pad_h, int pad_w) {
   const int cg = C >> 3;
@@ -115,59 +129,31 @@ __global__ void bn_relu_maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ x, 
     t /= W;
     const int h = static_cast<int>(t % H);
     const int n = static_cast<int>(t / H);
-    float sc[8], sh[8], z[8], g[8];
-    float v[8];
-    load8(x + ((static_cast<long long>(n) * H + h) * W + w) * C + c, v);
-    bool any = false;
+    float g[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      sc[e] = scale[c + e];
-      sh[e] = shift[c + e];
-      z[e] = round_bf16(fmaxf(fmaf(v[e], sc[e], sh[e]), 0.f));
-      g[e] = 0.f;
-      any |= z[e] > 0.f;
-    }
-    if (any) {
-      // windows (oh, ow) with oh*2 - pad_h <= h <= oh*2 - pad_h + 2
-      const int oh_lo = max(0, (h + pad_h - 2 + 1) >> 1), oh_hi = min(OH - 1, (h + pad_h) >> 1);
-      const int ow_lo = max(0, (w + pad_w - 2 + 1) >> 1), ow_hi = min(OW - 1, (w + pad_w) >> 1);
-      for (int oh = oh_lo; oh <= oh_hi; ++oh)
-        for (int ow = ow_lo; ow <= ow_hi; ++ow) {
-          const long long o = ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c;
-          float ym[8], gy[8];
-          load8(y + o, ym);
-          bool cand = false;
-          bool is_max[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            is_max[e] = (z[e] > 0.f) && (z[e] == ym[e]);
-            cand |= is_max[e];
-          }
-          if (!cand) continue;
-          // tie-break: an earlier window position with the same value wins
-          const int r0 = h - (oh * 2 - pad_h), s0 = w - (ow * 2 - pad_w);
-          for (int r = 0; r <= r0; ++r) {
-            const int hh = oh * 2 - pad_h + r;
-            if (hh < 0) continue;
-            const int s_end = (r == r0) ? s0 : 3;
-            for (int s = 0; s < s_end; ++s) {
-              const int ww = ow * 2 - pad_w + s;
-              if (ww < 0 || ww >= W) continue;
-              float u[8];
-              load8(x + ((static_cast<long long>(n) * H + hh) * W + ww) * C + c, u);
-#pragma unroll
-              for (int e = 0; e < 8; ++e)
-                if (is_max[e] && round_bf16(fmaxf(fmaf(u[e], sc[e], sh[e]), 0.f)) == ym[e]) is_max[e] = false;
-            }
-          }
+    for (int e = 0; e < 8; ++e) g[e] = 0.f;
+    const int oh_lo = max(0, (h + pad_h - 1) >> 1), oh_hi = min(OH - 1, (h + pad_h) >> 1);
+    const int ow_lo = max(0, (w + pad_w - 1) >> 1), ow_hi = min(OW - 1, (w + pad_w) >> 1);
+    for (int oh = oh_lo; oh <= oh_hi; ++oh)
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        const uint32_t me = static_cast<uint32_t>((h - (oh * 2 - pad_h)) * 3 + (w - (ow * 2 - pad_w)));
+        const long long o = ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c;
+        const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+        const uint32_t me4 = me * 0x01010101u;
+        // byte-wise equality test
+        const uint32_t x0 = pk.x ^ me4, x1 = pk.y ^ me4;
+        if (((x0 - 0x01010101u) & ~x0 & 0x80808080u) | ((x1 - 0x01010101u) & ~x1 & 0x80808080u)) {
+          float gy[8];
           load8(dy + o, gy);
 #pragma unroll
-          for (int e = 0; e < 8; ++e)
-            if (is_max[e]) g[e] += gy[e];
+          for (int e = 0; e < 4; ++e) {
+            if (((pk.x >> (8 * e)) & 0xffu) == me) g[e] += gy[e];
+            if (((pk.y >> (8 * e)) & 0xffu) == me) g[4 + e] += gy[4 + e];
+          }
         }
+      }
 #pragma unroll
-      for (int e = 0; e < 8; ++e) g[e] *= sc[e];
-    }
+    for (int e = 0; e < 8; ++e) g[e] *= scale[c + e];
     store8(dx + ((static_cast<long long>(n) * H + h) * W + w) * C + c, g);
   }
 }
@@ -250,22 +236,61 @@ __global__ void relu_bwd_kernel(const __nv_bfloat16* __restrict__ y, const __nv_
   }
 }
 
+__global__ void add_mask_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+                                const __nv_bfloat16* __restrict__ mask, __nv_bfloat16* __restrict__ out, long long n8) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n8;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v[8], m[8];
+    load8(a + i * 8, v);
+    if (b) {
+      float w[8];
+      load8(b + i * 8, w);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] += w[e];
+    }
+    if (mask) {
+      load8(mask + i * 8, m);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = m[e] > 0.f ? v[e] : 0.f;
+    }
+    store8(out + i * 8, v);
+  }
+}
+
 // ------------------------------------------------------------------ column sums (bias grads)
-constexpr int kColsumRows = 512;
-__global__ void colsum_kernel(const __nv_bfloat16* __restrict__ x, long long rows, int cols, int ld,
-                              float* __restrict__ out) {
+// Block = 8 row-lanes x 32 column-groups (8 channels each); each thread streams rows with 16-byte
+// loads, partial sums are combined through smem, one atomicAdd per column per block.
+constexpr int kColsumRows = 256;
+__global__ void __launch_bounds__(256) colsum_kernel(const __nv_bfloat16* __restrict__ x, long long rows, int cols,
+                                                     int ld, float* __restrict__ out) {
+  __shared__ float part[8][32][8];
+  const int cgx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int c = (blockIdx.y * 32 + cgx) * 8;
   const long long r0 = static_cast<long long>(blockIdx.x) * kColsumRows;
   const long long r1 = min(rows, r0 + kColsumRows);
-  for (int c2 = threadIdx.x; c2 * 2 < cols; c2 += blockDim.x) {
-    float a0 = 0.f, a1 = 0.f;
-    const __nv_bfloat16* p = x + r0 * ld + c2 * 2;
-    for (long long r = r0; r < r1; ++r, p += ld) {
-      const uint32_t u = *reinterpret_cast<const uint32_t*>(p);
-      a0 += bf16_lo(u);
-      a1 += bf16_hi(u);
+  float a[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) a[e] = 0.f;
+  if (c < cols) {
+#pragma unroll 4
+    for (long long r = r0 + ry; r < r1; r += 8) {
+      float v[8];
+      load8(x + r * ld + c, v);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) a[e] += v[e];
     }
-    atomicAdd(out + c2 * 2, a0);
-    if (c2 * 2 + 1 < cols) atomicAdd(out + c2 * 2 + 1, a1);
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) part[ry][cgx][e] = a[e];
+  __syncthreads();
+  // 256 threads -> 32 groups x 8 channels
+  const int g2 = threadIdx.x >> 3, e2 = threadIdx.x & 7;
+  const int cc = (blockIdx.y * 32 + g2) * 8 + e2;
+  if (cc < cols) {
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sum += part[k][g2][e2];
+    atomicAdd(out + cc, sum);
   }
 }
 
@@ -316,22 +341,23 @@ long long b200_weight_table_blocks(B200WeightEntry* host_entries, int n) {
   return b;
 }
 
-int b200_bn_relu_maxpool_fwd(const void* x, const float* scale, const float* shift, void* y, int N, int H, int W,
-                             int C, int OH, int OW, int pad_h, int pad_w, void* stream) {
+int b200_bn_relu_maxpool_fwd(const void* x, const float* scale, const float* shift, void* y, uint8_t* idx, int N,
+                             int H, int W, int C, int OH, int OW, int pad_h, int pad_w, void* stream) {
   if (C % 8) return set_error(-1, "maxpool: C must be a multiple of 8");
   const long long total = static_cast<long long>(N) * OH * OW * (C / 8);
   bn_relu_maxpool_fwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), scale, shift, static_cast<__nv_bfloat16*>(y), N, H, W, C, OH, OW, pad_h, pad_w);
+      static_cast<const __nv_bfloat16*>(x), scale, shift, static_cast<__nv_bfloat16*>(y), idx, N, H, W, C, OH, OW,
+      pad_h, pad_w);
   return check_launch("bn_relu_maxpool_fwd");
 }
 
-int b200_bn_relu_maxpool_bwd(const void* x, const float* scale, const float* shift, const void* y, const void* dy,
-                             void* dx, int N, int H, int W, int C, int OH, int OW, int pad_h, int pad_w, void* stream) {
+int b200_bn_relu_maxpool_bwd(const uint8_t* idx, const float* scale, const void* dy, void* dx, int N, int H, int W,
+                             int C, int OH, int OW, int pad_h, int pad_w, void* stream) {
   if (C % 8) return set_error(-1, "maxpool: C must be a multiple of 8");
   const long long total = static_cast<long long>(N) * H * W * (C / 8);
   bn_relu_maxpool_bwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), scale, shift, static_cast<const __nv_bfloat16*>(y),
-      static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), N, H, W, C, OH, OW, pad_h, pad_w);
+      idx, scale, static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), N, H, W, C, OH, OW, pad_h,
+      pad_w);
   return check_launch("bn_relu_maxpool_bwd");
 }
 
@@ -367,11 +393,19 @@ int b200_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* st
   return check_launch("relu_bwd");
 }
 
+int b200_add_mask(const void* a, const void* b, const void* mask, void* out, long long n, void* stream) {
+  if (n % 8) return set_error(-1, "add_mask: n must be a multiple of 8");
+  add_mask_kernel<<<grid_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b),
+      static_cast<const __nv_bfloat16*>(mask), static_cast<__nv_bfloat16*>(out), n / 8);
+  return check_launch("add_mask");
+}
+
 int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accum, void* stream) {
-  if (ld % 2) return set_error(-1, "colsum: ld must be even");
-  const long long blocks = (rows + kColsumRows - 1) / kColsumRows;
-  colsum_kernel<<<static_cast<unsigned>(blocks), 384, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), rows, cols, ld, out_accum);
+  if (ld % 8) return set_error(-1, "colsum: ld must be a multiple of 8");
+  dim3 grid(static_cast<unsigned>((rows + kColsumRows - 1) / kColsumRows), (cols + 255) / 256);
+  colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), rows, cols,
+                                                                     ld, out_accum);
   return check_launch("colsum");
 }
 

@@ -58,6 +58,7 @@ typedef struct {
   const float* shift; /* optional fp32 [Nrows] */
   int relu;
   int out_fp32;
+  int add_after_mask; /* 0: (acc+add)*mask ; 1: acc*mask + add */
 } B200ConvArgs;
 
 int b200_conv(const B200ConvArgs* args, void* stream);
@@ -101,12 +102,12 @@ typedef struct {
 long long b200_weight_table_blocks(B200WeightEntry* host_entries, int n); /* fills block_begin */
 int b200_prepare_weights(const B200WeightEntry* host_entries, int n, void* dev_table, void* stream);
 
-/* 3x3/2 'same' max-pool fused with the stem's frozen-BN affine + ReLU (G4+G5), and backward. */
-int b200_bn_relu_maxpool_fwd(const void* x, const float* scale, const float* shift, void* y, int N, int H, int W,
+/* 3x3/2 'same' max-pool fused with the stem's frozen-BN affine + ReLU (G4+G5).  Forward records the
+ * winning window position per output (uint8, 255 = no gradient); backward is a gather over it. */
+int b200_bn_relu_maxpool_fwd(const void* x, const float* scale, const float* shift, void* y, uint8_t* idx, int N,
+                             int H, int W, int C, int OH, int OW, int pad_h, int pad_w, void* stream);
+int b200_bn_relu_maxpool_bwd(const uint8_t* idx, const float* scale, const void* dy, void* dx, int N, int H, int W,
                              int C, int OH, int OW, int pad_h, int pad_w, void* stream);
-int b200_bn_relu_maxpool_bwd(const void* x, const float* scale, const float* shift, const void* y, const void* dy,
-                             void* dx, int N, int H, int W, int C, int OH, int OW, int pad_h, int pad_w,
-                             void* stream);
 /* Nearest upsample-to-shape + add (FPN top-down merge, G7) and its backward (gather-sum). */
 int b200_upsample_add(const void* lateral, const void* top, void* out, int N, int H, int W, int C, int TH, int TW,
                       void* stream);
@@ -115,6 +116,8 @@ int b200_upsample_bwd_add(const void* dmerged, void* dtop_inout, int N, int H, i
 /* y = relu(x) and dx = dy * (y > 0) on bf16 buffers (P7's input; generic). */
 int b200_relu(const void* x, void* y, long long n, void* stream);
 int b200_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* stream);
+/* out = (a + b) * (mask > 0); b optional (merge of gradient branches + ReLU backward). */
+int b200_add_mask(const void* a, const void* b, const void* mask, void* out, long long n, void* stream);
 /* Column sums of a bf16 [rows, ld] matrix into fp32 (bias gradients). */
 int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accum, void* stream);
 
