@@ -307,4 +307,82 @@ int b200_nms_sorted(const float* boxes, const int* cls_or_null, int n, float thr
   return check_launch("nms_scan_kernel");
 }
 
+
+/* ---------------------------------------------------------------------------------------------
+ * b200_nms_sorted_noalloc -- the same greedy NMS as b200_nms_sorted, for callers that are not
+ * allowed to allocate device memory.
+ *
+ * Who that is: code that runs after a deployment has handed out its whole device-memory budget
+ * (a serving process whose memory pool belongs to someone else, a plugin loaded into a host
+ * application that forbids cudaMalloc from plugins), and code on a latency-critical path where
+ * cudaMalloc/cudaFree would stall the device or take a driver lock at an unpredictable moment.
+ * Such callers cannot size and pass the n x ceil(n/64) suppression-mask scratch that
+ * b200_nms_sorted needs, so this variant keeps that scratch inside the library:
+ *
+ *   - the mask lives in a file-scope __device__ array of kNmsNoAllocMax x kNmsNoAllocMax/64
+ *     64-bit words = 2 MiB.  Every GPU that loads libb200ops.so holds those 2 MiB until the
+ *     process exits, whether or not this function is ever called;
+ *   - n must be <= kNmsNoAllocMax (4096); larger inputs are rejected with an error, nothing runs;
+ *   - the function calls no cudaMalloc / cudaFree / allocating library routine.  The first call
+ *     on each device looks the array's device address up once (cudaGetSymbolAddress, with that
+ *     device current) and caches it; make that first call before starting any stream capture;
+ *   - the caller still owns inputs and outputs: boxes [n,4] fp32 sorted by descending score,
+ *     optional int32 classes [n], keep_flags int32 [n].  keep_flags is cleared here (the scan only
+ *     writes ones), so unlike b200_nms_sorted the caller need not zero it;
+ *   - the scratch keeps whatever the previous call left in it.  That is harmless: every mask word
+ *     the scan reads for this n is rewritten by this call's mask kernel first, so nothing has to
+ *     start at zero.  But ALL calls share the one array per device: two calls whose kernels may
+ *     overlap on the GPU (different streams, or different host threads) race on it.  Serialise
+ *     them on one stream.
+ * No counterpart in the reference (it has no native code at all).
+ */
+namespace b200 {
+constexpr int kNmsNoAllocMax = 4096;
+static __device__ __align__(256) unsigned long long g_nms_noalloc_mask[kNmsNoAllocMax * (kNmsNoAllocMax / 64)];
+}  // namespace b200
+
+int b200_nms_sorted_noalloc_max(void) { return b200::kNmsNoAllocMax; }
+
+int b200_nms_sorted_noalloc(const float* boxes, const int* cls_or_null, int n, float thr, int* keep_flags,
+                            void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (n < 0) return set_error(-1, "nms_sorted_noalloc: negative n");
+  if (n > kNmsNoAllocMax)
+    return set_error(-1, "nms_sorted_noalloc: n = %d exceeds the built-in scratch limit of %d boxes; "
+                         "use b200_nms_sorted with caller-provided scratch", n, kNmsNoAllocMax);
+  if (n == 0) return 0;
+  // per-device address of the static scratch (the host-side symbol name is NOT a device pointer)
+  constexpr int kMaxDevices = 64;
+  static unsigned long long* s_scratch[kMaxDevices] = {nullptr};
+  static std::atomic<int> s_lock{0};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return set_error(-1, "nms_sorted_noalloc: device index %d out of range", dev);
+  unsigned long long* scratch = s_scratch[dev];
+  if (!scratch) {
+    while (s_lock.exchange(1, std::memory_order_acquire)) {
+    }
+    cudaError_t e = cudaSuccess;
+    if (!s_scratch[dev]) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_nms_noalloc_mask);
+      if (e == cudaSuccess) s_scratch[dev] = static_cast<unsigned long long*>(p);
+    }
+    scratch = s_scratch[dev];
+    s_lock.store(0, std::memory_order_release);
+    if (e != cudaSuccess || !scratch)
+      return set_error(-3, "nms_sorted_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+  }
+  B200_CUDA_OK(cudaMemsetAsync(keep_flags, 0, sizeof(int) * static_cast<size_t>(n), stream));
+  const int words = (n + 63) / 64;
+  dim3 mgrid(words, words, 1);
+  nms_mask_kernel<<<mgrid, 64, 0, stream>>>(boxes, cls_or_null, nullptr, n, 0, n, thr, scratch, words);
+  int rc = check_launch("nms_mask_kernel(noalloc)");
+  if (rc) return rc;
+  nms_scan_kernel<<<1, 128, words * sizeof(unsigned long long), stream>>>(scratch, nullptr, n, 0, n, words, n, boxes,
+                                                                          nullptr, nullptr, nullptr, nullptr, nullptr,
+                                                                          keep_flags);
+  return check_launch("nms_scan_kernel(noalloc)");
+}
+
 }  // extern "C"

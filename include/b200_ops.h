@@ -167,6 +167,16 @@ long long b200_filter_detections_workspace(int B, int max_cand);
 /* Stand-alone greedy NMS on fp32 boxes sorted by the caller (descending score); keep mask out. */
 int b200_nms_sorted(const float* boxes, const int* cls_or_null, int n, float thr, unsigned long long* mask_ws,
                     int* keep_flags, void* stream);
+/* Same NMS for callers that may not allocate device memory (fixed memory budget owned by
+ * someone else, plugin hosts that forbid cudaMalloc, latency-critical paths): the suppression-mask
+ * scratch is a 2 MiB __device__ array inside the library, held by every GPU that loads it.
+ * Limit: n <= b200_nms_sorted_noalloc_max() (4096), larger n is rejected.  keep_flags is cleared
+ * by the call.  The first call on a device caches the scratch address (make it before any stream
+ * capture); calls that can overlap on the GPU race on the shared scratch.  Has no counterpart in
+ * the reference, which ships no native code. */
+int b200_nms_sorted_noalloc(const float* boxes, const int* cls_or_null, int n, float thr, int* keep_flags,
+                            void* stream);
+int b200_nms_sorted_noalloc_max(void);
 
 /* ------------------------------------------------------------------ peer-to-peer collectives
  * Allreduce over NVLink peer mappings: every rank passes the table of all ranks' bucket
