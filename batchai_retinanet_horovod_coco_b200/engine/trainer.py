@@ -508,10 +508,18 @@ class NativeTrainer:
 
     # ------------------------------------------------------------------ optimizer
     def _attach_comm(self):
-        """Move the gradient bucket into peer-mapped memory and allocate the reduced copy."""
+        """Move the gradient bucket into peer-mapped memory, allocate the reduced copy and make every
+        rank start from rank 0's state (Horovod BroadcastGlobalVariablesCallback(0), train.py:111)."""
         self.G = self.comm.symmetric_bucket(self.n_train + 64)
         self.Gavg = torch.zeros_like(self.G)
-        self.comm.broadcast_(self.P, 0)
+        self.broadcast_state(0)
+
+    def broadcast_state(self, root: int = 0):
+        for t in (self.P, self.M, self.V, self.bn_scale, self.bn_shift):
+            self.comm.broadcast_(t, root)
+        it = torch.tensor([float(self.iterations), float(self.lr), 0.0, 0.0], device=self.device)
+        self.comm.broadcast_(it, root)
+        self.iterations, self.lr = int(it[0].item()), float(it[1].item())
         self._refresh_weights()
 
     def _optimizer_step(self):
@@ -520,11 +528,13 @@ class NativeTrainer:
         t = self.iterations
         lr_t = self.lr * math.sqrt(1.0 - self.beta2 ** t) / (1.0 - self.beta1 ** t)
         native.sumsq(self.G[:n], self.scal[0:1])
-        native.clip_scale(self.scal[0:1], self.clipnorm, self.scal[1:2])
         if self.comm is not None and self.comm.world > 1:
-            self.comm.allreduce_avg(self.G, self.Gavg, n, prescale=self.scal[1:2])
+            # the clip factor lives in peer-visible memory: peers apply it while reading my bucket
+            native.clip_scale(self.scal[0:1], self.clipnorm, self.comm.prescale_local)
+            self.comm.allreduce_avg(self.G, self.Gavg, n, prescale=True)
             native.adam(self.P[:n], self.Gavg[:n], self.M[:n], self.V[:n], None, lr_t, self.beta1, self.beta2, self.eps)
         else:
+            native.clip_scale(self.scal[0:1], self.clipnorm, self.scal[1:2])
             native.adam(self.P[:n], self.G[:n], self.M[:n], self.V[:n], self.scal[1:2], lr_t, self.beta1, self.beta2,
                         self.eps)
         self._refresh_weights()

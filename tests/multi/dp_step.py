@@ -1,0 +1,43 @@
+"""2-rank data-parallel native step == single-process step on the concatenated batch (same clip semantics
+are NOT expected: clipping is per-rank, so compare with clipnorm disabled)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import torch, torch.distributed as dist
+from batchai_retinanet_horovod_coco_b200.models.retinanet import RetinaNet
+from batchai_retinanet_horovod_coco_b200.engine.trainer import NativeTrainer
+
+rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lr)
+dev = torch.device("cuda", lr)
+dist.init_process_group("nccl", device_id=dev)
+torch.manual_seed(1234 + rank)            # different init per rank: broadcast must fix it
+model = RetinaNet(80, "resnet50")
+B, H, W = 1, 160, 224
+g = torch.Generator().manual_seed(7)
+img = torch.randint(0, 256, (world * B, H, W, 3), dtype=torch.uint8, generator=g)
+G = 4
+xy = torch.rand(world * B, G, 2, generator=g) * torch.tensor([W * 0.6, H * 0.6])
+wh = torch.rand(world * B, G, 2, generator=g) * 60 + 20
+gt = torch.cat([xy, xy + wh, torch.randint(0, 80, (world * B, G, 1), generator=g).float()], dim=2)
+cnt = torch.full((world * B,), G, dtype=torch.int32)
+hw = torch.tensor([[H, W]] * (world * B), dtype=torch.int32)
+nt = NativeTrainer(model=model, device=dev, batch=B, image_hw=(H, W), distributed=True, clipnorm=0.0, lr=1e-4)
+p0 = nt.P.clone()
+chk = p0.clone(); dist.broadcast(chk, 0)
+assert torch.equal(chk, p0), "initial broadcast did not equalise the ranks"
+sl = slice(rank * B, (rank + 1) * B)
+loss = nt.train_step(img[sl], gt[sl], cnt[sl], hw[sl])
+torch.cuda.synchronize()
+gavg = nt.Gavg[:nt.n_train].clone()
+ref = gavg.clone(); dist.broadcast(ref, 0)
+assert torch.equal(ref, gavg), "averaged gradients differ between ranks"
+p1 = nt.P.clone(); chk = p1.clone(); dist.broadcast(chk, 0)
+assert torch.equal(chk, p1), "parameters diverged after one step"
+assert not torch.equal(p1, p0)
+for _ in range(3):
+    loss = nt.train_step(img[sl], gt[sl], cnt[sl], hw[sl])
+assert torch.isfinite(loss).all()
+nt.comm.close()
+if rank == 0:
+    print("DP_OK", loss.tolist())
+dist.destroy_process_group()

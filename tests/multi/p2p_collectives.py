@@ -1,0 +1,56 @@
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import torch, torch.distributed as dist
+from batchai_retinanet_horovod_coco_b200.parallel.p2p import P2PComm
+
+rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lr)
+dev = torch.device("cuda", lr)
+dist.init_process_group("nccl", device_id=dev)
+comm = P2PComm.from_torch_distributed(dev)
+N = 6_000_000
+bucket = comm.symmetric_bucket(N)
+for algo, n in ((1, 1000), (1, 100_000), (2, 100_000), (2, N), (0, 4096), (0, N)):
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    x = torch.randn(N, device=dev, generator=g)
+    bucket.copy_(x)
+    pre = 0.5 + rank
+    comm.prescale_local.fill_(pre)
+    out = torch.zeros(N, device=dev)
+    torch.cuda.synchronize(); dist.barrier()
+    comm.allreduce_avg(bucket, out, n, prescale=True, algo=algo)
+    torch.cuda.synchronize()
+    ref = x * pre
+    dist.all_reduce(ref)
+    ref /= world
+    n4 = (n + 3) // 4 * 4
+    err = (out[:n4] - ref[:n4]).abs().max().item()
+    assert err < 1e-4 * (1 + ref.abs().max().item()), (rank, algo, n, err)
+    assert n4 == N or out[n4:].abs().max().item() == 0
+t = torch.full((1_000_003,), float(rank + 1), device=dev)
+comm.broadcast_(t, 0)
+assert (t == 1).all()
+t = torch.full((12345,), float(rank + 1), device=dev)
+comm.allreduce_sum_(t)
+assert abs(t[0].item() - world * (world + 1) / 2) < 1e-5
+# bandwidth (device timed, max over ranks)
+for nbytes in (1 << 12, 1 << 16, 1 << 20, 1 << 24, N * 4):
+    n = nbytes // 4
+    out = torch.zeros(N, device=dev)
+    for _ in range(3):
+        comm.allreduce_avg(bucket, out, n, prescale=False)
+    torch.cuda.synchronize(); dist.barrier()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(10):
+        comm.allreduce_avg(bucket, out, n, prescale=False)
+    e.record(); torch.cuda.synchronize()
+    ms = torch.tensor([s.elapsed_time(e) / 10], device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(f"P2P_BW bytes={nbytes} world={world} ms={ms.item():.4f} algbw_GBs={nbytes / ms.item() / 1e6:.1f} "
+              f"busbw_GBs={nbytes / ms.item() / 1e6 * 2 * (world - 1) / world:.1f}")
+comm.close()
+if rank == 0:
+    print("P2P_OK")
+dist.destroy_process_group()
