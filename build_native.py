@@ -57,7 +57,7 @@ def build(verbose: bool = False) -> dict:
     rt_dir = os.path.join(CSRC, "rt")
     rt_objs = []
     if os.path.isdir(rt_dir):
-        rt_headers = headers + [os.path.join(rt_dir, f) for f in os.listdir(rt_dir) if f.endswith((".h", ".hpp"))]
+        rt_headers = headers + [os.path.join(rt_dir, f) for f in os.listdir(rt_dir) if f.endswith((".h", ".hpp", ".inc"))]
         for f in sorted(os.listdir(rt_dir)):
             if f.endswith(".cpp"):
                 src = os.path.join(rt_dir, f)

@@ -1,0 +1,61 @@
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import torch
+import batchai_retinanet_horovod_coco_b200.parallel as hvd
+
+hvd.init()
+r, n = hvd.rank(), hvd.size()
+assert n == int(os.environ["B200_SIZE"]) and hvd.local_rank() == r and hvd.local_size() == n
+mode = sys.argv[1] if len(sys.argv) > 1 else "basic"
+if mode == "basic":
+    if r == 0 and len(sys.argv) > 2:
+        hvd.timeline_start(sys.argv[2])
+    # many small tensors enqueued together -> fused; one big tensor > fusion threshold -> chunked
+    ts = [torch.full((17 + i,), float(r + 1 + i)) for i in range(20)]
+    hs = [hvd.allreduce_async_(t, average=True, name=f"g{i}") for i, t in enumerate(ts)]
+    for i, h in enumerate(hs):
+        h.wait()
+        want = sum(q + 1 + i for q in range(n)) / n
+        assert torch.allclose(ts[i], torch.full_like(ts[i], want)), (i, ts[i][:3], want)
+    big = torch.arange(3_000_000, dtype=torch.float64) * (r + 1)
+    hvd.allreduce_(big, average=False, name="big")
+    assert torch.equal(big, torch.arange(3_000_000, dtype=torch.float64) * (n * (n + 1) // 2))
+    it = torch.tensor([r, 2 * r], dtype=torch.int64)
+    assert hvd.allreduce(it, average=False).tolist() == [sum(range(n)), 2 * sum(range(n))]
+    b = torch.full((5,), float(r))
+    hvd.broadcast_(b, root_rank=n - 1)
+    assert (b == n - 1).all()
+    g = hvd.allgather(torch.full((r + 1, 3), float(r)))
+    assert g.shape == (n * (n + 1) // 2, 3) and g[0, 0] == 0 and g[-1, 0] == n - 1
+    obj = hvd.broadcast_object({"lr": 1e-5, "who": r} if r == 0 else None, 0)
+    assert obj == {"lr": 1e-5, "who": 0}
+    m = torch.nn.Linear(4, 3)
+    hvd.broadcast_parameters(m.state_dict(), 0)
+    w = hvd.allgather(m.weight.detach().reshape(1, -1))
+    assert torch.equal(w[0], w[-1])
+    hvd.barrier()
+    st = hvd.stats()
+    assert st["fused_tensors"] >= 2, st
+    hvd.timeline_stop()
+elif mode == "mismatch":
+    t = torch.zeros(4 if r == 0 else 5)
+    try:
+        hvd.allreduce_(t, name="bad")
+    except RuntimeError as e:
+        assert "mismatched shapes" in str(e), e
+        print("MISMATCH_OK", r, flush=True)
+    else:
+        raise SystemExit(3)
+elif mode == "stall":
+    if r != 0:
+        time.sleep(1.5)
+    hvd.allreduce_(torch.ones(3), name="late")
+    hvd.barrier()
+    if r == 0:
+        assert hvd.stats()["stall_warnings"] >= 1
+elif mode == "die":
+    if r == 1:
+        os._exit(5)
+    hvd.allreduce_(torch.ones(3), name="never")
+print("WORKER_OK", r, flush=True)
+hvd.shutdown()
