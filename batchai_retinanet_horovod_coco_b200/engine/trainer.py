@@ -515,6 +515,8 @@ class NativeTrainer:
         self.broadcast_state(0)
 
     def broadcast_state(self, root: int = 0):
+        if self.comm is None or self.comm.world == 1:
+            return
         for t in (self.P, self.M, self.V, self.bn_scale, self.bn_shift):
             self.comm.broadcast_(t, root)
         it = torch.tensor([float(self.iterations), float(self.lr), 0.0, 0.0], device=self.device)
@@ -614,3 +616,50 @@ class NativeTrainer:
             w = c.wview(self.G).view(c.kh, c.kw, c.cout, c.cin).permute(2, 3, 0, 1).contiguous()
             out[c.name] = (w, c.bview(self.G).clone() if c.has_bias else None)
         return out
+
+    # ------------------------------------------------------------------ checkpoint surface
+    def optimizer_config(self) -> dict:
+        return {"lr": self.lr, "beta_1": self.beta1, "beta_2": self.beta2, "epsilon": self.eps, "decay": 0.0,
+                "amsgrad": False, "clipnorm": self.clipnorm}
+
+    def optimizer_slots(self) -> dict:
+        """{keras weight name: (m, v)} in the torch layout (OIHW kernels), on the host."""
+        out = {}
+        for c in self.convs:
+            if not c.trainable:
+                continue
+            m = c.wview(self.M).view(c.kh, c.kw, c.cout, c.cin).permute(2, 3, 0, 1).contiguous().cpu()
+            v = c.wview(self.V).view(c.kh, c.kw, c.cout, c.cin).permute(2, 3, 0, 1).contiguous().cpu()
+            out[f"{c.name}/kernel:0"] = (m, v)
+            if c.has_bias:
+                out[f"{c.name}/bias:0"] = (c.bview(self.M).cpu().clone(), c.bview(self.V).cpu().clone())
+        return out
+
+    @torch.no_grad()
+    def load_optimizer_state(self, state: dict):
+        cfg = state.get("optimizer_config") or {}
+        self.lr = float(cfg.get("lr", self.lr))
+        self.clipnorm = float(cfg.get("clipnorm", self.clipnorm) or 0.0)
+        self.iterations = int(state.get("iterations", 0))
+        slots = state.get("slots", {})
+        for c in self.convs:
+            if not c.trainable:
+                continue
+            k = slots.get(f"{c.name}/kernel:0")
+            if k is not None:
+                for flat, t in ((self.M, k[0]), (self.V, k[1])):
+                    c.wview(flat).copy_(t.to(self.device, torch.float32).permute(2, 3, 0, 1).reshape(c.taps, c.cout, c.cin))
+            b = slots.get(f"{c.name}/bias:0")
+            if b is not None and c.has_bias:
+                c.bview(self.M).copy_(b[0].to(self.device))
+                c.bview(self.V).copy_(b[1].to(self.device))
+
+    def save(self, path: str, epoch: int | None = None, weights_only: bool = False):
+        """Keras-layout ``.h5`` snapshot (ModelCheckpoint, reference ``train.py:112-114``)."""
+        from ..utils import keras_h5
+        self.store_to_model()
+        if weights_only:
+            keras_h5.save_weights(self.model, path)
+        else:
+            keras_h5.save_model(self.model, path, optimizer_config=self.optimizer_config(),
+                                optimizer_slots=self.optimizer_slots(), iterations=self.iterations, epoch=epoch)

@@ -1,0 +1,159 @@
+"""CLI + driver: argument surface of the reference, generators, callbacks, checkpoints, resume, and the
+BASELINE.json config-1 plumbing run (2 ranks on CPU through our launcher)."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from batchai_retinanet_horovod_coco_b200.bin import train as T
+from batchai_retinanet_horovod_coco_b200.preprocessing.synthetic import write_coco_dataset
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_parse_args_defaults_match_reference():
+    a = T.parse_args(["coco", "/data/coco"])
+    assert (a.backbone, a.batch_size, a.epochs, a.steps) == ("resnet50", 1, 50, 10000)
+    assert (a.snapshot_path, a.tensorboard_dir) == ("./snapshots", "./logs")
+    assert a.imagenet_weights is True and a.snapshots and a.evaluation
+    assert (a.image_min_side, a.image_max_side, a.multi_gpu) == (800, 1333, 0)
+    a = T.parse_args(["--no-weights", "--no-evaluation", "--steps", "500", "--freeze-backbone", "coco", "x"])
+    assert a.imagenet_weights is False and not a.evaluation and a.steps == 500 and a.freeze_backbone
+    a = T.parse_args(["oid", "d", "--labels-filter", "a,b", "--version", "v4"])
+    assert a.labels_filter == ["a", "b"]
+    a = T.parse_args(["csv", "ann.csv", "cls.csv", "--val-annotations", "v.csv"])
+    assert a.val_annotations == "v.csv"
+
+
+def test_check_args_errors():
+    with pytest.raises(ValueError, match="Batch size"):
+        T.parse_args(["--multi-gpu", "2", "--batch-size", "1", "coco", "x"])
+    with pytest.raises(ValueError, match="experimental"):
+        T.parse_args(["--multi-gpu", "2", "--batch-size", "2", "coco", "x"])
+    with pytest.raises(ValueError, match="snapshots"):
+        T.parse_args(["--multi-gpu", "2", "--batch-size", "2", "--snapshot", "s.h5", "coco", "x"])
+    with pytest.raises(SystemExit):
+        T.parse_args(["--snapshot", "a", "--weights", "b", "coco", "x"])  # mutually exclusive
+    with pytest.warns(UserWarning, match="experimental backbone"):
+        T.parse_args(["--backbone", "vgg16", "coco", "x"])
+
+
+def test_coco_generator_and_compact_batches(tmp_path):
+    from batchai_retinanet_horovod_coco_b200.preprocessing.coco import CocoGenerator
+    from batchai_retinanet_horovod_coco_b200.utils.transform import random_transform_generator
+    root = write_coco_dataset(str(tmp_path / "coco"), num_images=6, image_hw=(96, 128), classes=3)
+    g = CocoGenerator(root, "train2017", batch_size=2, image_min_side=96, image_max_side=128,
+                      transform_generator=random_transform_generator(flip_x_chance=0.5), seed=1)
+    assert g.size() == 6 and g.num_classes() == 3
+    assert g.label_to_coco_label(1) == 3 and g.coco_label_to_label(5) == 2 and g.label_to_name(0) == "class_0"
+    img, gt, cnt, hw = g.next_compact()
+    assert img.dtype == torch.uint8 and img.shape == (2, 96, 128, 3) and gt.shape[2] == 5 and cnt.tolist() == [3, 3]
+    x, (reg, lab) = g.next()
+    n_anchors = sum(h * w * 9 for h, w in [(12, 16), (6, 8), (3, 4), (2, 2), (1, 1)])
+    assert x.shape == (2, 96, 128, 3) and reg.shape == (2, n_anchors, 5) and lab.shape == (2, n_anchors, 4)
+    assert abs(float(x.mean())) < 40          # Caffe mean subtracted
+    # sharding: disjoint halves
+    a = CocoGenerator(root, "train2017", batch_size=1, shard=(0, 2), shuffle_groups=False)
+    b = CocoGenerator(root, "train2017", batch_size=1, shard=(1, 2), shuffle_groups=False)
+    assert not {i for g_ in a.groups for i in g_} & {i for g_ in b.groups for i in g_}
+
+
+def test_other_generators(tmp_path):
+    import cv2
+    from batchai_retinanet_horovod_coco_b200.preprocessing.csv_generator import CSVGenerator
+    from batchai_retinanet_horovod_coco_b200.preprocessing.kitti import KittiGenerator
+    from batchai_retinanet_horovod_coco_b200.preprocessing.pascal_voc import PascalVocGenerator
+    img = np.full((60, 80, 3), 127, np.uint8)
+    cv2.imwrite(str(tmp_path / "a.jpg"), img)
+    (tmp_path / "ann.csv").write_text("a.jpg,5,6,40,50,cow\na.jpg,1,2,20,30,cat\n")
+    (tmp_path / "cls.csv").write_text("cow,0\ncat,1\n")
+    g = CSVGenerator(str(tmp_path / "ann.csv"), str(tmp_path / "cls.csv"), batch_size=1, image_min_side=60, image_max_side=80)
+    assert g.size() == 1 and g.num_classes() == 2 and g.load_annotations(0).tolist() == [[5, 6, 40, 50, 0], [1, 2, 20, 30, 1]]
+    voc = tmp_path / "voc"
+    for d in ("ImageSets/Main", "Annotations", "JPEGImages"):
+        (voc / d).mkdir(parents=True)
+    (voc / "ImageSets/Main/trainval.txt").write_text("img1\n")
+    cv2.imwrite(str(voc / "JPEGImages/img1.jpg"), img)
+    (voc / "Annotations/img1.xml").write_text(
+        "<annotation><object><name>dog</name><truncated>0</truncated><difficult>0</difficult><bndbox><xmin>11</xmin>"
+        "<ymin>12</ymin><xmax>41</xmax><ymax>52</ymax></bndbox></object></annotation>")
+    g = PascalVocGenerator(str(voc), "trainval", batch_size=1)
+    assert g.num_classes() == 20 and g.load_annotations(0).tolist() == [[10, 11, 40, 51, 11]]
+    kit = tmp_path / "kitti" / "train"
+    (kit / "labels").mkdir(parents=True)
+    (kit / "images").mkdir()
+    cv2.imwrite(str(kit / "images/000.png"), img)
+    (kit / "labels/000.txt").write_text("Car 0.0 0 1.5 10.0 20.0 50.0 55.0 1 1 1 1 1 1 1\n")
+    g = KittiGenerator(str(tmp_path / "kitti"), subset="train", batch_size=1)
+    assert g.load_annotations(0).tolist() == [[10, 20, 50, 55, 0]] and g.num_classes() == 8
+
+
+def test_reduce_lr_on_plateau_and_checkpoint_names(tmp_path):
+    from batchai_retinanet_horovod_coco_b200.callbacks import ModelCheckpoint, ReduceLROnPlateau
+
+    class Tr:
+        lr = 1e-5
+        saved = []
+        model = None
+
+        def save(self, path, epoch=None, weights_only=False):
+            self.saved.append((path, epoch))
+    tr = Tr()
+    cb = ReduceLROnPlateau(monitor="loss", factor=0.1, patience=2, epsilon=1e-4)
+    cb.set_trainer(tr)
+    cb.on_train_begin()
+    for e, l in enumerate([1.0, 0.9, 0.9, 0.9, 0.9]):
+        cb.on_epoch_end(e, {"loss": l})
+    assert abs(tr.lr - 1e-6) < 1e-12                       # cut once after 2 epochs without improvement
+    ck = ModelCheckpoint(str(tmp_path / "snap" / "checkpoint-{epoch:02d}.h5"))
+    ck.set_trainer(tr)
+    ck.on_epoch_end(0, {})
+    assert tr.saved[0][0].endswith("checkpoint-01.h5") and os.path.isdir(tmp_path / "snap")
+
+
+def test_keras_adam_matches_formula():
+    from batchai_retinanet_horovod_coco_b200.parallel.optimizer import KerasAdam
+    p = torch.nn.Parameter(torch.tensor([1.0, -2.0]))
+    opt = KerasAdam([p], lr=0.1, clipnorm=0.5)
+    p.grad = torch.tensor([3.0, 4.0])                        # norm 5 -> scaled by 0.1
+    opt.step()
+    g = torch.tensor([0.3, 0.4])
+    lr_t = 0.1 * (1 - 0.999) ** 0.5 / (1 - 0.9)
+    want = torch.tensor([1.0, -2.0]) - lr_t * (0.1 * g) / ((0.001 * g * g).sqrt() + 1e-7)
+    assert torch.allclose(p.detach(), want, atol=1e-6)
+
+
+@pytest.mark.timeout(900)
+def test_two_rank_cpu_training_run(tmp_path):
+    """BASELINE.json config 1: tiny COCO-format set, batch 1, 2 ranks on CPU (reference train.py:18)."""
+    import build_native
+    build_native.build()
+    root = write_coco_dataset(str(tmp_path / "coco"), num_images=4, image_hw=(96, 128), classes=3)
+    snap, logs, tl = tmp_path / "snapshots", tmp_path / "logs", tmp_path / "timeline.json"
+    base = [sys.executable, "-m", "batchai_retinanet_horovod_coco_b200.parallel.launcher", "-np", "2", sys.executable,
+            os.path.join(ROOT, "train.py"), "--cpu", "--no-weights", "--batch-size", "1", "--image-min-side", "96",
+            "--image-max-side", "128", "--snapshot-path", str(snap), "--tensorboard-dir", str(logs), "--lr", "1e-4"]
+    env = dict(os.environ, OMP_NUM_THREADS="4", PYTHONPATH=ROOT)
+    r = subprocess.run(base + ["--steps", "2", "--epochs", "2", "--timeline", str(tl), "coco", root], capture_output=True,
+                       text=True, timeout=800, cwd=str(tmp_path), env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert sorted(os.listdir(snap)) == ["checkpoint-01.h5", "checkpoint-02.h5"]     # rank 0 only, 1-based
+    assert any(f.startswith("events.out.tfevents") for f in os.listdir(logs))
+    assert r.stdout.count("Total params") == 1                                       # summary on rank 0 only
+    ev = json.loads(tl.read_text())
+    assert any(e["name"] == "SHM_ALLREDUCE" for e in ev)
+    # resume: optimizer state and epoch counter come back, training continues at epoch 3
+    base2 = [a for a in base if a != "--no-weights"]          # --snapshot and --no-weights are mutually exclusive
+    r2 = subprocess.run(base2 + ["--steps", "1", "--epochs", "3", "--no-evaluation", "--snapshot",
+                                str(snap / "checkpoint-02.h5"), "coco", root], capture_output=True, text=True, timeout=800,
+                        cwd=str(tmp_path), env=env)
+    assert r2.returncode == 0, r2.stdout[-3000:] + r2.stderr[-3000:]
+    assert "Epoch 3/3" in r2.stdout and "Epoch 1/3" not in r2.stdout
+    assert "checkpoint-03.h5" in os.listdir(snap)
+    from batchai_retinanet_horovod_coco_b200.utils.keras_h5 import load_full_model
+    _, st = load_full_model(str(snap / "checkpoint-03.h5"))
+    assert st["iterations"] == 5 and st["epoch"] == 3
