@@ -6,11 +6,11 @@
 // (dh, dw) shift of the TMA box and the conv halo / padding is TMA's out-of-bounds zero fill),
 // N = output channels (BN <= 256 per tile), K = taps x input channels (64 per pipeline stage).
 //
-// Warp roles (384 threads, 1 CTA per SM, persistent over tiles):
+// Warp roles (640 threads, 1 CTA per SM, persistent over tiles):
 //   warp 0   TMA producer  (one lane): A box [64ch, tw, th, 1] + B box [64ch, BN rows, 1 tap]
 //   warp 1   MMA issuer    (one lane): 4 x tcgen05.mma (K=16) per stage, commit -> empty barrier
 //   warp 2   TMEM allocator (512 columns = two 256-column accumulators, double-buffered)
-//   warps 4-11 epilogue (2 per TMEM lane quarter): tcgen05.ld 32 lanes x 32 columns, fused
+//   warps 4-19 epilogue (4 per TMEM lane quarter): tcgen05.ld 32 lanes x 32 columns, fused
 //            shift/add/mask/ReLU, swizzled smem transpose, coalesced bf16 loads/stores
 //
 // Stride-2 convolutions use one tensor map per input parity class (strided views), so every
@@ -18,6 +18,8 @@
 //
 // Replaces cuDNN fprop/dgrad + separate bias/BN/ReLU/add kernels of the reference stack
 // (SURVEY.md G2-G4, G6, G8, G12); the reference itself has no CUDA source.
+#include <cstdlib>
+
 #include "../include/b200_ops.h"
 #include "common.cuh"
 #include "ptx_sm100.cuh"
@@ -32,9 +34,9 @@ constexpr int kBStageBytes = 256 * kBK * 2;       // 32 KB (BN <= 256)
 constexpr int kMaxTaps = 49;
 constexpr int kMaxMaps = 8;
 constexpr int kTmemCols = 512;
-constexpr int kEpiWarps = 8;                         // 2 warps per TMEM lane quarter (column halves)
+constexpr int kEpiWarps = 16;                        // 4 warps per TMEM lane quarter (column slots)
 constexpr int kConvThreads = 128 + 32 * kEpiWarps;
-constexpr int kStagingBytes = kEpiWarps * 4096;      // per epilogue warp: 2 KB add/out + 2 KB mask
+constexpr int kStagingBytes = kEpiWarps * 2048;      // per epilogue warp: one 32 rows x 64 B buffer
 constexpr int kSmemBytes = kStages * (kAStageBytes + kBStageBytes) + kStagingBytes + 1024 /*align*/ + 256 /*barriers*/;
 
 struct Tap {
@@ -86,6 +88,7 @@ __device__ __forceinline__ void decode_tile(const ConvParams& p, int tile, int& 
   x0 = tx << q.tw_log2;
 }
 
+template <bool kAdd, bool kMask>
 __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -136,6 +139,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      bool first_pass = true;
+      const bool weights_resident = (p.num_n_tiles == 1) && (kStages % num_k == 0);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         int pi, n, y0, x0, n_tile;
         decode_tile(p, tile, pi, n, y0, x0, n_tile);
@@ -145,12 +150,17 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           const void* amap = &p.in_maps[map_base + tap.map];
           for (int kc = 0; kc < p.num_kc; ++kc) {
             mbar_wait(empty_bar(stage), phase ^ 1);
-            mbar_expect_tx(full_bar(stage), kAStageBytes + b_bytes);
+            // Weights stay resident: when the whole K loop fits the ring (num_k divides kStages) and there
+            // is a single N tile, stage s always holds the same weight tile, so it is fetched once.
+            const bool load_b = !weights_resident || first_pass;
+            mbar_expect_tx(full_bar(stage), kAStageBytes + (load_b ? b_bytes : 0u));
             tma_load_4d(a_smem + stage * kAStageBytes, amap, full_bar(stage), kc * kBK, x0 + tap.dw, y0 + tap.dh, n);
-            tma_load_3d(b_smem + stage * kBStageBytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
+            if (load_b)
+              tma_load_3d(b_smem + stage * kBStageBytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
             if (++stage == kStages) {
               stage = 0;
               phase ^= 1;
+              first_pass = false;
             }
           }
         }
@@ -192,18 +202,32 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------------ epilogue
-    // Each warp owns 32 accumulator rows (TMEM lanes).  A thread holds one row, but row-per-thread
-    // global accesses would touch 32 lines per instruction with partial sectors, so every 32-column
-    // chunk goes through a warp-private, XOR-swizzled smem transpose: global <-> smem transfers are
-    // 8 rows x 64 B per instruction (sector-complete), smem <-> registers are row-per-thread.
+    // 16 warps: warp (quarter q, column slot cq) owns TMEM lanes 32q..32q+31 and the 32-column chunks
+    // cq, cq+4, ... of the tile.  A thread holds one accumulator row, but row-per-thread global
+    // accesses would touch 32 lines per instruction with partial sectors, so every chunk goes through a
+    // warp-private XOR-swizzled 2 KB smem buffer: global <-> smem moves are 8 rows x 64 B per
+    // instruction (sector-complete), smem <-> registers are row-per-thread.  The kernel is latency
+    // bound here for small K (ncu: long_scoreboard), hence 4 warps per scheduler and the mask/residual
+    // loads of a chunk issued back to back before anything waits on them.
     const int ew = warp - 4;
     const int quarter = ew & 3;   // TMEM lanes this warp may read: 32 * (warp_id % 4)
-    const int chalf = ew >> 2;    // which 32-column chunks of the tile this warp handles
+    const int cq = ew >> 2;       // column slot
     const int m = quarter * 32 + lane;
-    const uint32_t buf_a = stg_base + ew * 4096;  // add in / result out
-    const uint32_t buf_m = buf_a + 2048;               // mask
+    const uint32_t buf = stg_base + ew * 2048;
     const int crow = lane >> 2, cpiece = lane & 3;
     const uint32_t own_sw = (lane >> 1) & 3;
+    const uint32_t own_base = buf + lane * 64;
+    uint32_t own_off[4], so_r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) own_off[j] = own_base + ((static_cast<uint32_t>(j) ^ own_sw) << 4);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int rr = i * 8 + crow;
+      so_r[i] = buf + rr * 64 + ((cpiece ^ ((rr >> 1) & 3)) << 4);
+    }
+    const float* __restrict__ shiftp = p.shift;
+    const bool relu = p.relu != 0, add_post = p.add_after_mask != 0;
+    const int ldo = p.ldo, BN = p.BN, Nrows = p.Nrows;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -214,103 +238,107 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       const int x = x0 + (m & ((1 << q.tw_log2) - 1));
       const bool valid = (y < q.OH) && (x < q.OW);
       const int pix = (n * q.OHo + (y * p.os + p.oy)) * q.OWo + (x * p.os + p.ox);  // < 2^31 pixels
-      const long long row_off = static_cast<long long>(pix) * p.ldo;
       const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
-      int pix_r[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) pix_r[i] = __shfl_sync(0xffffffffu, pix, i * 8 + crow);
-      const int col0 = n_tile * p.BN;
-      const int col_end = min(p.Nrows, col0 + p.BN);
+      const int col0 = n_tile * BN;
+      const int col_end = min(Nrows, col0 + BN);
       const int col_end_pad = (col_end + 7) & ~7;
-      const __nv_bfloat16* addp = static_cast<const __nv_bfloat16*>(q.add);
-      const __nv_bfloat16* maskp = static_cast<const __nv_bfloat16*>(q.mask);
+      __nv_bfloat16* __restrict__ outp = static_cast<__nv_bfloat16*>(q.out);
+      const __nv_bfloat16* __restrict__ addp = static_cast<const __nv_bfloat16*>(q.add);
+      const __nv_bfloat16* __restrict__ maskp = static_cast<const __nv_bfloat16*>(q.mask);
+      long long roff_r[4];  // element offset of (row handled in the coalesced pattern, this lane's 16-byte piece)
+      bool ok_r[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int rr = i * 8 + crow;
+        roff_r[i] = static_cast<long long>(__shfl_sync(0xffffffffu, pix, rr)) * ldo + col0 + cpiece * 8;
+        ok_r[i] = (valid_mask >> rr) & 1u;
+      }
 
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * 256;
-      for (int c = chalf * 32; c < p.BN; c += 64) {
+      for (int c = cq * 32; c < BN; c += 32 * (kEpiWarps / 4)) {
         const int col = col0 + c;
         if (col >= col_end) break;
-        uint32_t r[32];
-        tmem_ld_32x32(t_row + c, r);
-        if (p.out_fp32) {
-          // rarely used (debug / fp32 head outputs): direct row-per-thread path
-          tmem_ld_wait();
-          if (valid) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              if (col + j >= col_end) continue;
-              float v = __uint_as_float(r[j]);
-              if (p.shift) v += __ldg(p.shift + col + j);
-              if (addp && !p.add_after_mask) v += __bfloat162float(addp[row_off + col + j]);
-              if (maskp && !(__bfloat162float(maskp[row_off + col + j]) > 0.f)) v = 0.f;
-              if (addp && p.add_after_mask) v += __bfloat162float(addp[row_off + col + j]);
-              if (p.relu) v = fmaxf(v, 0.f);
-              static_cast<float*>(q.out)[row_off + col + j] = v;
-            }
-          }
-          continue;
-        }
-        // ---- coalesced global -> smem for the epilogue operands
-        if (addp || maskp) {
+        const bool piece_ok = col + cpiece * 8 < col_end_pad;
+        // ---- epilogue operands: coalesced global loads (all issued before any use) -> smem -> own row
+        uint4 ka[4];
+        uint32_t mbits = 0xffffffffu;
+        if constexpr (kAdd || kMask) {
+          uint4 ta[4], tm[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const int rr = i * 8 + crow;
-            const long long roff = static_cast<long long>(pix_r[i]) * p.ldo;
-            const bool ok = ((valid_mask >> rr) & 1u) && (col + cpiece * 8 < col_end_pad);
-            const uint32_t so = rr * 64 + ((cpiece ^ ((rr >> 1) & 3)) << 4);
-            if (ok) {
-              if (addp) {
-                const uint4 t = *reinterpret_cast<const uint4*>(addp + roff + col + cpiece * 8);
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf_a + so), "r"(t.x), "r"(t.y), "r"(t.z), "r"(t.w) : "memory");
-              }
-              if (maskp) {
-                const uint4 t = *reinterpret_cast<const uint4*>(maskp + roff + col + cpiece * 8);
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf_m + so), "r"(t.x), "r"(t.y), "r"(t.z), "r"(t.w) : "memory");
+            if (kMask && ok_r[i] && piece_ok) tm[i] = *reinterpret_cast<const uint4*>(maskp + roff_r[i] + c);
+            if (kAdd && ok_r[i] && piece_ok) ta[i] = *reinterpret_cast<const uint4*>(addp + roff_r[i] + c);
+          }
+          if constexpr (kMask) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(so_r[i]), "r"(tm[i].x), "r"(tm[i].y), "r"(tm[i].z), "r"(tm[i].w) : "memory");
+            __syncwarp();
+            mbits = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 k;
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(k.x), "=r"(k.y), "=r"(k.z), "=r"(k.w) : "r"(own_off[j]));
+              const uint32_t w4[4] = {k.x, k.y, k.z, k.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                // bf16 > 0  <=>  the 16-bit pattern, as a signed integer, is > 0 (no NaNs expected in masks)
+                if (static_cast<int>(w4[e] << 16) > 0) mbits |= 1u << (j * 8 + 2 * e);
+                if (static_cast<int>(w4[e] & 0xffff0000u) > 0) mbits |= 1u << (j * 8 + 2 * e + 1);
               }
             }
+            __syncwarp();
           }
-          __syncwarp();
+          if constexpr (kAdd) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(so_r[i]), "r"(ta[i].x), "r"(ta[i].y), "r"(ta[i].z), "r"(ta[i].w) : "memory");
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(ka[j].x), "=r"(ka[j].y), "=r"(ka[j].z), "=r"(ka[j].w) : "r"(own_off[j]));
+            __syncwarp();
+          }
         }
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c, r);
         tmem_ld_wait();
-        // ---- row-per-thread math, result into the warp's staging buffer
+        // ---- row-per-thread math, result into the staging buffer (issue-bound: keep it short)
+        if (valid) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int cj = col + j * 8;
-          const uint32_t so = lane * 64 + ((static_cast<uint32_t>(j) ^ own_sw) << 4);
-          float v[8];
+          for (int j = 0; j < 4; ++j) {
+            const int cj = col + j * 8;
+            if (cj >= col_end) break;
+            float v[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j * 8 + e]);
-          if (valid && cj < col_end) {
-            if (p.shift) {
-              const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.shift + cj));
-              const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.shift + cj + 4));
+            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j * 8 + e]);
+            if (shiftp) {
+              const float4 s0 = __ldg(reinterpret_cast<const float4*>(shiftp + cj));
+              const float4 s1 = __ldg(reinterpret_cast<const float4*>(shiftp + cj + 4));
               v[0] += s0.x; v[1] += s0.y; v[2] += s0.z; v[3] += s0.w;
               v[4] += s1.x; v[5] += s1.y; v[6] += s1.z; v[7] += s1.w;
             }
-            uint4 a = make_uint4(0u, 0u, 0u, 0u);
-            if (addp) asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "r"(buf_a + so));
-            if (addp && !p.add_after_mask) {
-              v[0] += bf16_lo(a.x); v[1] += bf16_hi(a.x); v[2] += bf16_lo(a.y); v[3] += bf16_hi(a.y);
-              v[4] += bf16_lo(a.z); v[5] += bf16_hi(a.z); v[6] += bf16_lo(a.w); v[7] += bf16_hi(a.w);
+            if constexpr (kAdd) {
+              if (!add_post) {
+                v[0] += bf16_lo(ka[j].x); v[1] += bf16_hi(ka[j].x); v[2] += bf16_lo(ka[j].y); v[3] += bf16_hi(ka[j].y);
+                v[4] += bf16_lo(ka[j].z); v[5] += bf16_hi(ka[j].z); v[6] += bf16_lo(ka[j].w); v[7] += bf16_hi(ka[j].w);
+              }
             }
-            if (maskp) {
-              uint4 k;
-              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(k.x), "=r"(k.y), "=r"(k.z), "=r"(k.w) : "r"(buf_m + so));
-              if (!(bf16_lo(k.x) > 0.f)) v[0] = 0.f;
-              if (!(bf16_hi(k.x) > 0.f)) v[1] = 0.f;
-              if (!(bf16_lo(k.y) > 0.f)) v[2] = 0.f;
-              if (!(bf16_hi(k.y) > 0.f)) v[3] = 0.f;
-              if (!(bf16_lo(k.z) > 0.f)) v[4] = 0.f;
-              if (!(bf16_hi(k.z) > 0.f)) v[5] = 0.f;
-              if (!(bf16_lo(k.w) > 0.f)) v[6] = 0.f;
-              if (!(bf16_hi(k.w) > 0.f)) v[7] = 0.f;
+            if constexpr (kMask) {
+              const uint32_t mb = mbits >> (j * 8);
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                if (!((mb >> e) & 1u)) v[e] = 0.f;
             }
-            if (addp && p.add_after_mask) {
-              v[0] += bf16_lo(a.x); v[1] += bf16_hi(a.x); v[2] += bf16_lo(a.y); v[3] += bf16_hi(a.y);
-              v[4] += bf16_lo(a.z); v[5] += bf16_hi(a.z); v[6] += bf16_lo(a.w); v[7] += bf16_hi(a.w);
+            if constexpr (kAdd) {
+              if (add_post) {
+                v[0] += bf16_lo(ka[j].x); v[1] += bf16_hi(ka[j].x); v[2] += bf16_lo(ka[j].y); v[3] += bf16_hi(ka[j].y);
+                v[4] += bf16_lo(ka[j].z); v[5] += bf16_hi(ka[j].z); v[6] += bf16_lo(ka[j].w); v[7] += bf16_hi(ka[j].w);
+              }
             }
-            if (p.relu) {
+            if (relu) {
 #pragma unroll
               for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
             }
@@ -321,21 +349,17 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             }
             const uint32_t o0 = pack_bf16x2(v[0], v[1]), o1 = pack_bf16x2(v[2], v[3]);
             const uint32_t o2 = pack_bf16x2(v[4], v[5]), o3 = pack_bf16x2(v[6], v[7]);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf_a + so), "r"(o0), "r"(o1), "r"(o2), "r"(o3) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_off[j]), "r"(o0), "r"(o1), "r"(o2), "r"(o3) : "memory");
           }
         }
         __syncwarp();
         // ---- coalesced smem -> global store
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const int rr = i * 8 + crow;
-          const long long roff = static_cast<long long>(pix_r[i]) * p.ldo;
-          const bool ok = ((valid_mask >> rr) & 1u) && (col + cpiece * 8 < col_end_pad);
-          if (ok) {
-            const uint32_t so = rr * 64 + ((cpiece ^ ((rr >> 1) & 3)) << 4);
+          if (ok_r[i] && piece_ok) {
             uint4 t;
-            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(t.x), "=r"(t.y), "=r"(t.z), "=r"(t.w) : "r"(buf_a + so));
-            *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(q.out) + roff + col + cpiece * 8) = t;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(t.x), "=r"(t.y), "=r"(t.z), "=r"(t.w) : "r"(so_r[i]));
+            *reinterpret_cast<uint4*>(outp + roff_r[i] + c) = t;
           }
         }
         __syncwarp();
@@ -399,11 +423,19 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   if (a->KH * a->KW > kMaxTaps) return set_error(-1, "b200_conv: too many taps");
   if ((a->ldi % 8) || (a->ldw % 8) || (a->ldo % 8)) return set_error(-1, "b200_conv: ld* must be multiples of 8");
 
+  if (a->out_fp32) return set_error(-1, "b200_conv: fp32 output is not supported (bf16 activations only)");
   static bool attr_set = false;
   if (!attr_set) {
-    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr_set = true;
   }
+  const bool has_add = a->prob[0].add != nullptr, has_mask = a->prob[0].mask != nullptr;
+  for (int i = 1; i < a->num_problems; ++i)
+    if ((a->prob[i].add != nullptr) != has_add || (a->prob[i].mask != nullptr) != has_mask)
+      return set_error(-1, "b200_conv: all problems of a grouped launch must agree on add/mask presence");
 
   ConvParams p;
   memset(&p, 0, sizeof(p));
@@ -520,6 +552,9 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
 
   const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles;
   const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
-  conv_igemm_kernel<<<grid, kConvThreads, kSmemBytes, stream>>>(p);
+  if (has_add && has_mask) conv_igemm_kernel<true, true><<<grid, kConvThreads, kSmemBytes, stream>>>(p);
+  else if (has_add) conv_igemm_kernel<true, false><<<grid, kConvThreads, kSmemBytes, stream>>>(p);
+  else if (has_mask) conv_igemm_kernel<false, true><<<grid, kConvThreads, kSmemBytes, stream>>>(p);
+  else conv_igemm_kernel<false, false><<<grid, kConvThreads, kSmemBytes, stream>>>(p);
   return check_launch("conv_igemm_kernel");
 }
