@@ -258,32 +258,50 @@ __global__ void add_mask_kernel(const __nv_bfloat16* __restrict__ a, const __nv_
 }
 
 // ------------------------------------------------------------------ column sums (bias grads)
-// Block = 8 row-lanes x 32 column-groups (8 channels each); each thread streams rows with 16-byte
-// loads, partial sums are combined through smem, one atomicAdd per column per block.
-constexpr int kColsumRows = 256;
-__global__ void __launch_bounds__(256) colsum_kernel(const __nv_bfloat16* __restrict__ x, long long rows, int cols,
-                                                     int ld, float* __restrict__ out) {
+// Block = 8 row-lanes x 32 column-groups (8 channels each); 64 rows per block so that a thread only
+// chains 8 loads (the kernel is latency bound, not bandwidth bound, on the small pyramid levels);
+// up to 5 matrices (pyramid levels) per launch; one atomicAdd per column per block.
+constexpr int kColsumRows = 64;
+struct ColsumArgs {
+  const __nv_bfloat16* x[5];
+  long long rows[5];
+  long long block_begin[6];
+  int n;
+};
+__global__ void __launch_bounds__(256) colsum_kernel(ColsumArgs a, int cols, int ld, float* __restrict__ out) {
   __shared__ float part[8][32][8];
+  int pi = 0;
+#pragma unroll
+  for (int i = 1; i < 5; ++i)
+    if (i < a.n && static_cast<long long>(blockIdx.x) >= a.block_begin[i]) pi = i;
+  const __nv_bfloat16* __restrict__ x = a.x[pi];
+  const long long rows = a.rows[pi];
   const int cgx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int c = (blockIdx.y * 32 + cgx) * 8;
-  const long long r0 = static_cast<long long>(blockIdx.x) * kColsumRows;
-  const long long r1 = min(rows, r0 + kColsumRows);
-  float a[8];
+  const long long r0 = (static_cast<long long>(blockIdx.x) - a.block_begin[pi]) * kColsumRows;
+  float acc[8];
 #pragma unroll
-  for (int e = 0; e < 8; ++e) a[e] = 0.f;
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
   if (c < cols) {
-#pragma unroll 4
-    for (long long r = r0 + ry; r < r1; r += 8) {
-      float v[8];
-      load8(x + r * ld + c, v);
+    float v[8][8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) a[e] += v[e];
+    for (int k = 0; k < 8; ++k) {
+      const long long r = r0 + ry + 8 * k;
+      if (r < rows) {
+        load8(x + r * ld + c, v[k]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[k][e] = 0.f;
+      }
     }
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += v[k][e];
   }
 #pragma unroll
-  for (int e = 0; e < 8; ++e) part[ry][cgx][e] = a[e];
+  for (int e = 0; e < 8; ++e) part[ry][cgx][e] = acc[e];
   __syncthreads();
-  // 256 threads -> 32 groups x 8 channels
   const int g2 = threadIdx.x >> 3, e2 = threadIdx.x & 7;
   const int cc = (blockIdx.y * 32 + g2) * 8 + e2;
   if (cc < cols) {
@@ -401,12 +419,28 @@ int b200_add_mask(const void* a, const void* b, const void* mask, void* out, lon
   return check_launch("add_mask");
 }
 
-int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accum, void* stream) {
+int b200_colsum_multi(const void* const* xs, const long long* rows, int n, int cols, int ld, float* out_accum,
+                      void* stream) {
   if (ld % 8) return set_error(-1, "colsum: ld must be a multiple of 8");
-  dim3 grid(static_cast<unsigned>((rows + kColsumRows - 1) / kColsumRows), (cols + 255) / 256);
-  colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), rows, cols,
-                                                                     ld, out_accum);
+  if (n < 1 || n > 5) return set_error(-1, "colsum: 1..5 matrices");
+  ColsumArgs a;
+  long long blocks = 0;
+  for (int i = 0; i < 5; ++i) {
+    a.x[i] = i < n ? static_cast<const __nv_bfloat16*>(xs[i]) : nullptr;
+    a.rows[i] = i < n ? rows[i] : 0;
+    a.block_begin[i] = blocks;
+    if (i < n) blocks += (rows[i] + kColsumRows - 1) / kColsumRows;
+  }
+  a.block_begin[5] = blocks;
+  a.n = n;
+  if (blocks == 0) return 0;
+  dim3 grid(static_cast<unsigned>(blocks), (cols + 255) / 256);
+  colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a, cols, ld, out_accum);
   return check_launch("colsum");
+}
+
+int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accum, void* stream) {
+  return b200_colsum_multi(&x, &rows, 1, cols, ld, out_accum, stream);
 }
 
 int b200_preprocess(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean, void* stream) {

@@ -220,7 +220,8 @@ static void pick_tile64(int OH, int OW, int& th_log2, int& tw_log2) {
 
 }  // namespace b200
 
-extern "C" int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accum, void* stream);
+extern "C" int b200_colsum_multi(const void* const* xs, const long long* rows, int n, int cols, int ld, float* out_accum,
+                                 void* stream);
 
 extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
   using namespace b200;
@@ -310,7 +311,8 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
 
   const long long units = static_cast<long long>(p.num_taps) * p.num_m_tiles * p.num_n_tiles;
   // ~3 waves of CTAs, but at least 8 pixel tiles (512 pixels) per CTA to amortise the epilogue
-  long long ks = (3LL * num_sms() + units - 1) / units;
+  // whole waves only: 3.04 waves cost as much as 4, so round the split DOWN to <= 3 waves of CTAs
+  long long ks = (3LL * num_sms()) / units;
   const long long max_ks = (p.num_pixel_tiles + 7) / 8;
   if (ks > max_ks) ks = max_ks;
   if (ks < 1) ks = 1;
@@ -323,11 +325,14 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
   int rc = check_launch("wgrad_kernel");
   if (rc) return rc;
   if (a->dbias) {
+    const void* ptrs[B200_MAX_PROBLEMS];
+    long long rows[B200_MAX_PROBLEMS];
     for (int i = 0; i < a->num_problems; ++i) {
-      const B200WgradProblem& q = a->prob[i];
-      rc = b200_colsum(q.dy, static_cast<long long>(q.N) * q.OH * q.OW, a->Cout, a->ldy, a->dbias, stream_);
-      if (rc) return rc;
+      ptrs[i] = a->prob[i].dy;
+      rows[i] = static_cast<long long>(a->prob[i].N) * a->prob[i].OH * a->prob[i].OW;
     }
+    rc = b200_colsum_multi(ptrs, rows, a->num_problems, a->Cout, a->ldy, a->dbias, stream_);
+    if (rc) return rc;
   }
   return 0;
 }

@@ -120,6 +120,8 @@ int b200_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* st
 int b200_add_mask(const void* a, const void* b, const void* mask, void* out, long long n, void* stream);
 /* Column sums of a bf16 [rows, ld] matrix into fp32 (bias gradients). */
 int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accum, void* stream);
+int b200_colsum_multi(const void* const* xs, const long long* rows, int n, int cols, int ld, float* out_accum,
+                      void* stream); /* up to 5 matrices (pyramid levels) in one launch */
 
 /* Image normalise + pad (G19): uint8 HWC (BGR) -> bf16 NHWC with Caffe mean subtraction. */
 int b200_preprocess(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean,
