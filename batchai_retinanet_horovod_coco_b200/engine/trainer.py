@@ -194,6 +194,8 @@ class NativeTrainer:
         # small device scalars
         self.scal = torch.zeros(8, device=dev)           # [0] sumsq  [1] clip scale  [2] reg loss  [3] cls loss
         self.npos = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.ones64 = torch.ones(64, device=dev)
+        self.zeros64 = torch.zeros(64, device=dev)
 
     # ------------------------------------------------------------------ parameter import / export
     @torch.no_grad()
@@ -223,6 +225,7 @@ class NativeTrainer:
         s = self.stem
         w = s.wview(self.P).view(s.kh, s.kw, s.cout, s.cin).permute(2, 3, 0, 1)
         self.stem_w = w.to(BF16).contiguous(memory_format=torch.channels_last)
+        self.stem_wp = native.pack_stem_weight(s.wview(self.P), s.scale)
 
     def optimizer_state(self):
         """Adam slots as {keras layer name: {'kernel': (m, v), 'bias': (m, v)}} views + iterations."""
@@ -239,13 +242,14 @@ class NativeTrainer:
         def buf(h, w, c, zero=False):
             return (torch.zeros if zero else torch.empty)(B, h, w, c, device=dev, dtype=BF16)
 
-        p["img"] = torch.empty(B, H, W, 3, device=dev, dtype=BF16)
+        p["img"] = torch.empty(B, H, W, 4, device=dev, dtype=BF16)   # 4th channel is zero padding
         h1, w1 = -(-H // 2), -(-W // 2)
         p["stem_raw_hw"] = (h1, w1)
         ph, pw = tf_same_pad(h1, 3, 2), tf_same_pad(w1, 3, 2)
         p["pool_pad"] = (ph[0], pw[0])
         h2, w2 = -(-h1 // 2), -(-w1 // 2)
         p["pool"] = buf(h2, w2, 64)
+        p["stem_out"] = buf(h1, w1, 64)
         p["pool_idx"] = torch.empty(B, h2, w2, 64, device=dev, dtype=torch.uint8)
         acts = []
         hh, ww = h2, w2
@@ -348,13 +352,8 @@ class NativeTrainer:
     def _forward(self, p, images_u8):
         B, H, W, _ = images_u8.shape
         native.preprocess(images_u8, p["img"], CAFFE_MEAN_BGR)
-        x = p["img"].permute(0, 3, 1, 2)
-        raw = F.conv2d(x, self.stem_w, stride=2, padding=3)  # cuDNN; Cin=3 does not fit a 64-wide K tile
-        p["stem_raw"] = raw.permute(0, 2, 3, 1)
-        if not p["stem_raw"].is_contiguous():
-            p["stem_raw"] = p["stem_raw"].contiguous()
-        native.bn_relu_maxpool_fwd(p["stem_raw"], self.stem.scale, self.stem.shift, p["pool"], p["pool_idx"],
-                                   *p["pool_pad"])
+        native.stem_conv(p["img"], self.stem_wp, self.stem.shift, p["stem_out"])     # conv + BN + ReLU
+        native.bn_relu_maxpool_fwd(p["stem_out"], self.ones64, self.zeros64, p["pool"], p["pool_idx"], *p["pool_pad"])
         self._mark("fwd_stem")
         x = p["pool"]
         for si, st in enumerate(self.blocks):
@@ -497,14 +496,16 @@ class NativeTrainer:
                 g = g_next
         self._mark("bwd_backbone")
         # stem: max-pool + ReLU + BN backward, then cuDNN wgrad for the 7x7x3 filter
-        native.bn_relu_maxpool_bwd(p["pool_idx"], self.stem.scale, g, p["dstem"], *p["pool_pad"])
+        native.bn_relu_maxpool_bwd(p["pool_idx"], self.ones64, g, p["dstem"], *p["pool_pad"])
         if self.stem.trainable:
-            x = p["img"].permute(0, 3, 1, 2)
+            # filter gradient of the 7x7x3 stem: cuDNN backward-filter (0.3% of the step's FLOPs)
+            x = p["img"][..., :3].permute(0, 3, 1, 2)
             gy = p["dstem"].permute(0, 3, 1, 2)
             _, dw, _ = torch.ops.aten.convolution_backward(gy, x, self.stem_w, None, [2, 2], [3, 3], [1, 1], False,
                                                            [0, 0], 1, [False, True, False])
             s = self.stem
-            s.wview(self.G).add_(dw.float().permute(2, 3, 0, 1).reshape(s.taps, s.cout, s.cin))
+            dwm = dw.float().permute(2, 3, 0, 1).reshape(s.taps, s.cout, s.cin) * s.scale.view(1, -1, 1)
+            s.wview(self.G).add_(dwm)
 
     # ------------------------------------------------------------------ optimizer
     def _attach_comm(self):

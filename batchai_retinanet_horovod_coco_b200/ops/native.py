@@ -171,6 +171,25 @@ def wgrad_raw(problems, dw: torch.Tensor, Cin: int, ldx: int, Cout: int, ldy: in
     _check(lib.b200_wgrad(C.byref(a), _stream()), "b200_wgrad")
 
 
+def stem_conv(x4, w_packed, shift, y):
+    """x4 bf16 [N,H,W,4] -> y bf16 [N,ceil(H/2),ceil(W/2),64] = relu(conv7x7/2(x) + shift)."""
+    n, h, w, c = x4.shape
+    assert c == 4 and w_packed.shape == (64, 256)
+    _check(require().b200_stem_conv(_ptr(x4), _ptr(w_packed), _ptr(shift), _ptr(y), n, h, w, _stream()), "b200_stem_conv")
+
+
+def pack_stem_weight(master_tci, scale=None):
+    """master fp32 [49, 64, 3] (tap, co, ci) -> bf16 [64, 256], k = r*28 + s*4 + c, BN scale folded."""
+    w = master_tci.view(7, 7, 64, 3).permute(2, 0, 1, 3)          # co, r, s, c
+    if scale is not None:
+        w = w * scale.view(64, 1, 1, 1)
+    out = torch.zeros(64, 7, 7, 4, device=master_tci.device, dtype=torch.float32)
+    out[..., :3] = w
+    full = torch.zeros(64, 256, device=master_tci.device, dtype=torch.bfloat16)
+    full[:, :196] = out.reshape(64, 196).to(torch.bfloat16)
+    return full
+
+
 class WeightTable:
     """Device table driving the one-launch master->bf16 working-weight preparation."""
 

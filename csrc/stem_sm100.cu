@@ -1,0 +1,225 @@
+// RetinaNet/ResNet stem: 7x7 stride-2 convolution, Cin = 3 (stored as 4), Cout = 64, fused with the
+// frozen-BN shift and ReLU, on tcgen05 tensor cores.
+//
+// Cin = 3 cannot feed a 64-wide K tile through TMA, so this kernel builds the implicit-GEMM A tile
+// itself: the input is NHWC with 4 channels (8 bytes per pixel), one filter row of an output pixel
+// is 7 pixels = 28 contiguous bf16, and K = 7 rows x 28 = 196, zero-padded to 256 (four 64-wide K
+// blocks).  128 producer threads (one per output pixel of the 8x16 tile) copy 49 eight-byte pieces
+// each into a SWIZZLE_128B K-major tile in shared memory, fence them to the async proxy, and the MMA
+// warp issues 16 tcgen05.mma (M=128, N=64, K=16) per tile with the packed weights resident in smem.
+// Two smem stages and two TMEM accumulators overlap gather, MMA and the epilogue (shift + ReLU,
+// one 128-byte line per pixel).
+//
+// Replaces cuDNN's conv1 forward; the reference has no CUDA source.
+#include "../include/b200_ops.h"
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace b200 {
+
+constexpr int kStemKB = 4;                       // K blocks of 64
+constexpr int kStemABytes = kStemKB * 128 * 128; // 64 KB per stage
+constexpr int kStemBBytes = kStemKB * 64 * 128;  // 32 KB, resident
+constexpr int kStemStages = 2;
+constexpr int kStemThreads = 384;                // w0 MMA, w1 TMEM alloc, w4-7 epilogue, w8-11 producers
+constexpr int kStemSmem = kStemStages * kStemABytes + kStemBBytes + 1024 + 128;
+
+struct StemParams {
+  const __nv_bfloat16* x;   // [N, H, W, 4]
+  const __nv_bfloat16* w;   // [64][256] packed, k = r*28 + s*4 + c, BN scale folded in
+  const float* shift;       // [64]
+  __nv_bfloat16* y;         // [N, OH, OW, 64]
+  int N, H, W, OH, OW;
+  int tiles_h, tiles_w, total_tiles;
+};
+
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__global__ void __launch_bounds__(kStemThreads, 1) stem_conv_kernel(const StemParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_smem = smem_base;
+  const uint32_t b_smem = smem_base + kStemStages * kStemABytes;
+  const uint32_t bar_base = b_smem + kStemBBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (2 + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (4 + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (6 + a); };
+  const uint32_t tmem_ptr_smem = bar_base + 64;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // zero the A stages once (K padding 196..255 is never written again and must not hold NaNs),
+  // and copy the packed weights into the swizzled resident B tile
+  for (int i = threadIdx.x; i < kStemStages * kStemABytes / 16; i += kStemThreads)
+    reinterpret_cast<uint4*>(smem_gen)[i] = make_uint4(0u, 0u, 0u, 0u);
+  for (int i = threadIdx.x; i < 64 * 32; i += kStemThreads) {  // 64 rows x 32 sixteen-byte pieces
+    const int row = i >> 5, piece = i & 31;
+    const int kb = piece >> 3, ch = piece & 7;
+    const uint4 v = *reinterpret_cast<const uint4*>(p.w + row * 256 + piece * 8);
+    *reinterpret_cast<uint4*>(smem_gen + kStemStages * kStemABytes + kb * 8192 + row * 128 + ((ch ^ (row & 7)) << 4)) = v;
+  }
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(full_bar(s), 128);
+      mbar_init(empty_bar(s), 1);
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr_smem, 128);
+    tmem_relinquish();
+  }
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
+
+  auto decode = [&](int tile, int& n, int& y0, int& x0) {
+    const int per_img = p.tiles_h * p.tiles_w;
+    n = tile / per_img;
+    const int rem = tile - n * per_img;
+    y0 = (rem / p.tiles_w) * 8;
+    x0 = (rem % p.tiles_w) * 16;
+  };
+
+  if (warp >= 8) {
+    // ---------------------------------------------------------------- producers: gather the A tile
+    const int m = (warp - 8) * 32 + lane;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      int n, y0, x0;
+      decode(tile, n, y0, x0);
+      const int oy = y0 + (m >> 4), ox = x0 + (m & 15);
+      mbar_wait(empty_bar(stage), phase ^ 1);
+      uint8_t* a_row = smem_gen + stage * kStemABytes + m * 128;
+      const int sw = m & 7;
+#pragma unroll
+      for (int r = 0; r < 7; ++r) {
+        const int iy = 2 * oy + r - 3;
+        const bool row_ok = iy >= 0 && iy < p.H;
+        const __nv_bfloat16* src = p.x + (static_cast<long long>(n) * p.H + (row_ok ? iy : 0)) * p.W * 4;
+#pragma unroll
+        for (int s = 0; s < 7; ++s) {
+          const int ix = 2 * ox + s - 3;
+          uint2 v = make_uint2(0u, 0u);
+          if (row_ok && ix >= 0 && ix < p.W) v = __ldg(reinterpret_cast<const uint2*>(src + static_cast<long long>(ix) * 4));
+          const int kbyte = (r * 28 + s * 4) * 2;          // byte offset of this piece inside the K axis
+          const int kb = kbyte >> 7, within = kbyte & 127;
+          *reinterpret_cast<uint2*>(a_row + kb * 16384 + (((within >> 4) ^ sw) << 4) + (within & 15)) = v;
+        }
+      }
+      fence_async_smem();   // generic-proxy stores -> visible to the tensor core (async proxy)
+      mbar_arrive(full_bar(stage));
+      if (++stage == kStemStages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+  } else if (warp == 0) {
+    // ---------------------------------------------------------------- MMA issuer
+    const uint32_t idesc = make_idesc_bf16(128, 64, 0, 0);
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+      mbar_wait(full_bar(stage), phase);
+      tc_fence_after();
+      if (lane == 0) {
+#pragma unroll
+        for (int kb = 0; kb < kStemKB; ++kb) {
+          const uint64_t adesc = make_smem_desc(a_smem + stage * kStemABytes + kb * 16384, 16, 1024);
+          const uint64_t bdesc = make_smem_desc(b_smem + kb * 8192, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + acc * 64, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+        }
+        umma_commit(empty_bar(stage));
+        umma_commit(tfull_bar(acc));
+      }
+      __syncwarp();
+      if (++stage == kStemStages) {
+        stage = 0;
+        phase ^= 1;
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ---------------------------------------------------------------- epilogue: + shift, ReLU, bf16
+    const int quarter = warp - 4;
+    const int m = quarter * 32 + lane;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      int n, y0, x0;
+      decode(tile, n, y0, x0);
+      const int oy = y0 + (m >> 4), ox = x0 + (m & 15);
+      const bool valid = oy < p.OH && ox < p.OW;
+      __nv_bfloat16* dst = p.y + ((static_cast<long long>(n) * p.OH + oy) * p.OW + ox) * 64;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * 64;
+#pragma unroll
+      for (int c = 0; c < 64; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c, r);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.shift + c + j));
+            const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.shift + c + j + 4));
+            uint4 o;
+            o.x = pack_bf16x2(fmaxf(__uint_as_float(r[j]) + s0.x, 0.f), fmaxf(__uint_as_float(r[j + 1]) + s0.y, 0.f));
+            o.y = pack_bf16x2(fmaxf(__uint_as_float(r[j + 2]) + s0.z, 0.f), fmaxf(__uint_as_float(r[j + 3]) + s0.w, 0.f));
+            o.z = pack_bf16x2(fmaxf(__uint_as_float(r[j + 4]) + s1.x, 0.f), fmaxf(__uint_as_float(r[j + 5]) + s1.y, 0.f));
+            o.w = pack_bf16x2(fmaxf(__uint_as_float(r[j + 6]) + s1.z, 0.f), fmaxf(__uint_as_float(r[j + 7]) + s1.w, 0.f));
+            *reinterpret_cast<uint4*>(dst + c + j) = o;
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(tempty_bar(acc));
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 128);
+}
+
+}  // namespace b200
+
+extern "C" int b200_stem_conv(const void* x, const void* w_packed, const float* shift, void* y, int N, int H, int W,
+                              void* stream) {
+  using namespace b200;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA_OK(cudaFuncSetAttribute(stem_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+    attr = true;
+  }
+  StemParams p;
+  p.x = static_cast<const __nv_bfloat16*>(x);
+  p.w = static_cast<const __nv_bfloat16*>(w_packed);
+  p.shift = shift;
+  p.y = static_cast<__nv_bfloat16*>(y);
+  p.N = N;
+  p.H = H;
+  p.W = W;
+  p.OH = (H + 1) / 2;
+  p.OW = (W + 1) / 2;
+  p.tiles_h = (p.OH + 7) / 8;
+  p.tiles_w = (p.OW + 15) / 16;
+  p.total_tiles = N * p.tiles_h * p.tiles_w;
+  const int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
+  stem_conv_kernel<<<grid, kStemThreads, kStemSmem, static_cast<cudaStream_t>(stream)>>>(p);
+  return check_launch("stem_conv_kernel");
+}

@@ -19,15 +19,14 @@
 
 namespace b200 {
 
-constexpr int kWStages = 4;
+constexpr int kWStages = 3;
 constexpr int kKT = 64;                           // pixels per pipeline stage
 constexpr int kChunkBytes = kKT * 128;            // one [64 px][64 ch] chunk = 8 KB
-constexpr int kWAStage = 2 * kChunkBytes;         // M = 128 -> 2 chunks
+constexpr int kWAStage = 4 * kChunkBytes;         // up to two 128-row M tiles -> 4 chunks
 constexpr int kWBStage = 4 * kChunkBytes;         // N <= 256 -> 4 chunks
-constexpr int kWThreads = 256;
+constexpr int kWThreads = 128 + 8 * 32;           // TMA, MMA, TMEM alloc, spare + 8 epilogue warps
 constexpr int kWSmemBytes = kWStages * (kWAStage + kWBStage) + 1024 + 256;
 constexpr int kWMaxTaps = 49;
-constexpr int kWMaxMaps = 4 * B200_MAX_PROBLEMS;  // stride-2 parity maps only with 1 problem
 
 struct WTap {
   int8_t dh, dw, map, pad;
@@ -41,6 +40,10 @@ struct WProblem {
   int xmap_base;
 };
 
+// One CTA = one output block [MT x 128 rows of co] x [up to 4 packed 64-column chunks], over a range
+// of pixel tiles.  A packed chunk is (tap, 64-channel slice of ci): for Cin >= 256 the four chunks are
+// four ci slices of one tap; for Cin = 128 two taps x two slices; for Cin = 64 four taps.  The B tile
+// (shifted X) is shared by both M tiles, and for small Cin the A tile (dY) is shared by several taps.
 struct WgradParams {
   CUtensorMap x_maps[8];
   CUtensorMap dy_maps[B200_MAX_PROBLEMS];
@@ -49,8 +52,8 @@ struct WgradParams {
   float* dw;
   const float* rowscale;
   int num_problems, num_pixel_tiles;
-  int num_taps, num_m_tiles, num_n_tiles, ksplit, chunk;
-  int Cin, Cout, BN;
+  int num_taps, taps_per_unit, chunks_per_tap, num_tap_groups, num_m_groups, num_n_tiles, mt, ksplit, chunk;
+  int Cin, Cout;
 };
 
 __device__ __forceinline__ void w_decode(const WgradParams& p, int pt, int& pi, int& n, int& y0, int& x0) {
@@ -83,18 +86,27 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // unit decode: blockIdx.x = ((tap * num_m + m_tile) * num_n + n_tile) * ksplit + split
+  // unit decode: blockIdx.x = ((tap_group * num_m_groups + m_group) * num_n_tiles + n_tile) * ksplit + split
   int u = blockIdx.x;
   const int split = u % p.ksplit;
   u /= p.ksplit;
   const int n_tile = u % p.num_n_tiles;
   u /= p.num_n_tiles;
-  const int m_tile = u % p.num_m_tiles;
-  const int tap_i = u / p.num_m_tiles;
+  const int m_group = u % p.num_m_groups;
+  const int tap_group = u / p.num_m_groups;
   const int pt_begin = split * p.chunk;
   const int pt_end = min(p.num_pixel_tiles, pt_begin + p.chunk);
-  const int n_chunks = p.BN >> 6;
-  const uint32_t stage_bytes = (2 + n_chunks) * kChunkBytes;
+  const int tap0 = tap_group * p.taps_per_unit;
+  const int ntaps_here = min(p.taps_per_unit, p.num_taps - tap0);
+  // packed B chunks of this unit
+  const int n_chunks = (p.taps_per_unit > 1) ? ntaps_here * p.chunks_per_tap : min(4, (p.Cin - n_tile * 256) >> 6);
+  const int N = n_chunks * 64;
+  // A chunks: MT tiles x 2 halves of 64 output channels, loaded only where co < Cout
+  const int co_base = m_group * p.mt * 128;
+  int a_chunks = 0;
+  for (int c = 0; c < 2 * p.mt; ++c) a_chunks += (co_base + c * 64 < p.Cout) ? 1 : 0;
+  const int mt_valid = (a_chunks + 1) >> 1;
+  const uint32_t stage_bytes = static_cast<uint32_t>(a_chunks + n_chunks) * kChunkBytes;
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < 8; ++i) tma_prefetch_desc(&p.x_maps[i]);
@@ -109,7 +121,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_ptr_smem, 256);
+    tmem_alloc(tmem_ptr_smem, 512);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -121,23 +133,32 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   if (pt_begin < pt_end) {
     if (warp == 0) {
       if (lane == 0) {
-        const WTap tap = p.taps[tap_i];
         int stage = 0;
         uint32_t phase = 0;
         for (int pt = pt_begin; pt < pt_end; ++pt) {
           int pi, n, y0, x0;
           w_decode(p, pt, pi, n, y0, x0);
-          const void* xmap = &p.x_maps[p.prob[pi].xmap_base + tap.map];
+          const int xbase = p.prob[pi].xmap_base;
           const void* dymap = &p.dy_maps[pi];
           mbar_wait(empty_bar(stage), phase ^ 1);
           mbar_expect_tx(full_bar(stage), stage_bytes);
           const uint32_t a_dst = a_smem + stage * kWAStage;
           const uint32_t b_dst = b_smem + stage * kWBStage;
-          tma_load_4d(a_dst, dymap, full_bar(stage), m_tile * 128, x0, y0, n);
-          tma_load_4d(a_dst + kChunkBytes, dymap, full_bar(stage), m_tile * 128 + 64, x0, y0, n);
-          for (int c = 0; c < n_chunks; ++c)
-            tma_load_4d(b_dst + c * kChunkBytes, xmap, full_bar(stage), n_tile * p.BN + c * 64, x0 + tap.dw,
+          for (int c = 0; c < a_chunks; ++c)
+            tma_load_4d(a_dst + c * kChunkBytes, dymap, full_bar(stage), co_base + c * 64, x0, y0, n);
+          for (int c = 0; c < n_chunks; ++c) {
+            int t, ci;
+            if (p.taps_per_unit > 1) {
+              t = tap0 + c / p.chunks_per_tap;
+              ci = (c % p.chunks_per_tap) * 64;
+            } else {
+              t = tap0;
+              ci = n_tile * 256 + c * 64;
+            }
+            const WTap tap = p.taps[t];
+            tma_load_4d(b_dst + c * kChunkBytes, &p.x_maps[xbase + tap.map], full_bar(stage), ci, x0 + tap.dw,
                         y0 + tap.dh, n);
+          }
           if (++stage == kWStages) {
             stage = 0;
             phase ^= 1;
@@ -145,7 +166,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
         }
       }
     } else if (warp == 1) {
-      const uint32_t idesc = make_idesc_bf16(128, p.BN, 1, 1);
+      const uint32_t idesc = make_idesc_bf16(128, N, 1, 1);
       int stage = 0;
       uint32_t phase = 0;
       for (int pt = pt_begin; pt < pt_end; ++pt) {
@@ -153,12 +174,14 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
         tc_fence_after();
         if (lane == 0) {
           // MN-major: LBO = distance between 64-channel chunks, SBO = 8 pixel rows = 1024 B
-          const uint64_t adesc = make_smem_desc(a_smem + stage * kWAStage, kChunkBytes, 1024);
           const uint64_t bdesc = make_smem_desc(b_smem + stage * kWBStage, kChunkBytes, 1024);
+          for (int mt = 0; mt < mt_valid; ++mt) {
+            const uint64_t adesc = make_smem_desc(a_smem + stage * kWAStage + mt * 2 * kChunkBytes, kChunkBytes, 1024);
 #pragma unroll
-          for (int k = 0; k < kKT / 16; ++k) {
-            // 16 pixel rows = 2048 bytes -> +128 in (addr >> 4) units
-            umma_bf16(tmem_base, adesc + 128 * k, bdesc + 128 * k, idesc, (pt != pt_begin) || (k != 0));
+            for (int k = 0; k < kKT / 16; ++k) {
+              // 16 pixel rows = 2048 bytes -> +128 in (addr >> 4) units
+              umma_bf16(tmem_base + mt * 256, adesc + 128 * k, bdesc + 128 * k, idesc, (pt != pt_begin) || (k != 0));
+            }
           }
           umma_commit(empty_bar(stage));
           if (pt == pt_end - 1) umma_commit(tfull_bar);
@@ -170,23 +193,34 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
         }
       }
     } else if (warp >= 4) {
-      const int quarter = warp - 4;
-      const int co = m_tile * 128 + quarter * 32 + lane;
-      const bool valid = co < p.Cout;
-      const float rs = (valid && p.rowscale) ? __ldg(p.rowscale + co) : 1.f;
-      float* row = p.dw + (static_cast<long long>(tap_i) * p.Cout + (valid ? co : 0)) * p.Cin + n_tile * p.BN;
-      mbar_wait(tfull_bar, 0);
-      tc_fence_after();
-      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
-      for (int c = 0; c < p.BN; c += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(t_row + c, r);
-        tmem_ld_wait();
-        if (valid) {
+      const int ew = warp - 4;
+      const int quarter = ew & 3;
+      const int mt = ew >> 2;
+      if (mt < mt_valid) {
+        const int co = co_base + mt * 128 + quarter * 32 + lane;
+        const bool valid = co < p.Cout;
+        const float rs = (valid && p.rowscale) ? __ldg(p.rowscale + co) : 1.f;
+        mbar_wait(tfull_bar, 0);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + mt * 256;
+        for (int c = 0; c < N; c += 32) {
+          uint32_t r[32];
+          tmem_ld_32x32(t_row + c, r);
+          tmem_ld_wait();
+          const int pc = c >> 6;  // packed chunk
+          int t, ci;
+          if (p.taps_per_unit > 1) {
+            t = tap0 + pc / p.chunks_per_tap;
+            ci = (pc % p.chunks_per_tap) * 64;
+          } else {
+            t = tap0;
+            ci = n_tile * 256 + pc * 64;
+          }
+          if (valid) {
+            float* row = p.dw + (static_cast<long long>(t) * p.Cout + co) * p.Cin + ci + (c & 63);
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            if (n_tile * p.BN + c + j < p.Cin) {
-              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(row + c + j),
+            for (int j = 0; j < 32; j += 4) {
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(row + j),
                            "f"(__uint_as_float(r[j]) * rs), "f"(__uint_as_float(r[j + 1]) * rs),
                            "f"(__uint_as_float(r[j + 2]) * rs), "f"(__uint_as_float(r[j + 3]) * rs)
                            : "memory");
@@ -199,7 +233,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, 256);
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
 }
 
 static int floordiv_w(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
@@ -246,9 +280,11 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
   p.num_problems = a->num_problems;
   p.Cin = a->Cin;
   p.Cout = a->Cout;
-  p.BN = a->Cin >= 256 ? 256 : a->Cin;
-  p.num_n_tiles = (a->Cin + p.BN - 1) / p.BN;
-  p.num_m_tiles = (a->Cout + 127) / 128;
+  p.chunks_per_tap = a->Cin >= 256 ? 4 : a->Cin / 64;
+  p.taps_per_unit = a->Cin >= 256 ? 1 : 4 / p.chunks_per_tap;   // pack taps into N when Cin is small
+  p.num_n_tiles = a->Cin >= 256 ? (a->Cin + 255) / 256 : 1;
+  p.mt = a->Cout > 128 ? 2 : 1;
+  p.num_m_groups = (a->Cout + 128 * p.mt - 1) / (128 * p.mt);
   const int s = a->stride;
   int nt = 0;
   for (int r = 0; r < a->KH; ++r)
@@ -262,6 +298,8 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
       p.taps[nt++] = t;
     }
   p.num_taps = nt;
+  if (p.taps_per_unit > nt) p.taps_per_unit = nt;
+  p.num_tap_groups = (nt + p.taps_per_unit - 1) / p.taps_per_unit;
 
   int tile_begin = 0, map_count = 0;
   for (int i = 0; i < a->num_problems; ++i) {
@@ -309,10 +347,11 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
   for (int i = a->num_problems; i < B200_MAX_PROBLEMS; ++i) p.dy_maps[i] = p.dy_maps[0];
   p.num_pixel_tiles = tile_begin;
 
-  const long long units = static_cast<long long>(p.num_taps) * p.num_m_tiles * p.num_n_tiles;
+  const long long units = static_cast<long long>(p.num_tap_groups) * p.num_m_groups * p.num_n_tiles;
   // ~3 waves of CTAs, but at least 8 pixel tiles (512 pixels) per CTA to amortise the epilogue
-  // whole waves only: 3.04 waves cost as much as 4, so round the split DOWN to <= 3 waves of CTAs
-  long long ks = (3LL * num_sms()) / units;
+  // One wave: every CTA does the same amount of MMA work, so <= #SM CTAs is balanced, and each extra
+  // split only adds another atomic flush of the whole dW block (the dominant cost at 3 waves).
+  long long ks = static_cast<long long>(num_sms()) / units;
   const long long max_ks = (p.num_pixel_tiles + 7) / 8;
   if (ks > max_ks) ks = max_ks;
   if (ks < 1) ks = 1;

@@ -85,6 +85,13 @@ typedef struct {
 
 int b200_wgrad(const B200WgradArgs* args, void* stream);
 
+/* Stem: 7x7/2 convolution, Cin = 3 stored as 4 channels, Cout = 64, + shift + ReLU on tcgen05.
+ * x bf16 [N,H,W,4]; w_packed bf16 [64][256] with k = r*28 + s*4 + c (zero padded, BN scale folded);
+ * shift fp32 [64]; y bf16 [N,ceil(H/2),ceil(W/2),64].  Producer warps gather the im2col rows into a
+ * swizzled smem tile (Cin=3 cannot feed TMA).  Replaces cuDNN conv1 forward (G1). */
+int b200_stem_conv(const void* x, const void* w_packed, const float* shift, void* y, int N, int H, int W,
+                   void* stream);
+
 /* ------------------------------------------------------------------ bandwidth-bound fused ops */
 
 /* Frozen-BN scale fold + layout transform of master weights into the bf16 working copies

@@ -191,3 +191,20 @@ def test_prepare_weights_kernel():
     for (m, s), (wf, wd) in zip(((m1, s1), (m2, None)), outs):
         rf, rd = cv.pack_working(m, s)
         assert torch.equal(wf, rf) and torch.equal(wd, rd)
+
+
+@pytest.mark.parametrize("n,h,w", [(2, 64, 96), (1, 75, 101), (3, 256, 320)])
+def test_stem_conv(n, h, w):
+    torch.manual_seed(0)
+    x = torch.zeros(n, h, w, 4, device="cuda", dtype=torch.bfloat16)
+    x[..., :3] = (torch.randn(n, h, w, 3, device="cuda") * 60).to(torch.bfloat16)
+    wt = torch.randn(64, 3, 7, 7, device="cuda") * 0.05
+    scale = torch.rand(64, device="cuda") + 0.5
+    shift = torch.randn(64, device="cuda")
+    wp = native.pack_stem_weight(cv.pack_master(wt), scale)
+    oh, ow = (h + 1) // 2, (w + 1) // 2
+    y = torch.empty(n, oh, ow, 64, device="cuda", dtype=torch.bfloat16)
+    native.stem_conv(x, wp, shift, y)
+    w_eff = (wt * scale.view(64, 1, 1, 1)).to(torch.bfloat16).float()
+    ref = F.conv2d(x[..., :3].float().permute(0, 3, 1, 2), w_eff, stride=2, padding=3).permute(0, 2, 3, 1) + shift
+    _close(y, ref.clamp(min=0))
