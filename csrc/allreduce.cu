@@ -10,6 +10,8 @@
 //
 // Replaces Horovod's fusion-buffer memcpy + ncclAllReduce/MPI_Allreduce + tf.div
 // (SURVEY.md C4-C7, X1-X3); the reference has no CUDA source of its own.
+#include <cstdlib>
+
 #include "../include/b200_ops.h"
 #include "common.cuh"
 
@@ -17,7 +19,7 @@ namespace b200 {
 
 constexpr int kMaxWorld = 8;
 constexpr int kArThreads = 512;
-constexpr int kArMaxBlocks = 64;
+constexpr int kArMaxBlocks = 296;  // 2 per SM; flag pad = blocks x 8 peers x 4 B
 
 struct ArParams {
   float* bufs[kMaxWorld];
@@ -54,9 +56,12 @@ __device__ __forceinline__ void rank_barrier(const ArParams& p, uint32_t value) 
   __syncthreads();
 }
 
+// Peer data is read with plain streaming loads: it was published before the flag barrier
+// (st.release.sys / ld.acquire.sys), peer memory is never in the local L2, and L1 starts empty at
+// kernel launch and is bypassed here, so no stale line can be hit.
 __device__ __forceinline__ float4 ld_peer(const float* p) {
   float4 v;
-  asm volatile("ld.global.relaxed.sys.v4.f32 {%0, %1, %2, %3}, [%4];"
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
                : "l"(p)
                : "memory");
@@ -95,35 +100,54 @@ __global__ void __launch_bounds__(kArThreads) allreduce_twoshot_kernel(const ArP
   for (int r = 0; r < kWorld; ++r) pre[r] = p.has_prescale ? *p.prescale[r] : 1.f;
   const long long n4 = p.count >> 2;
   const long long slice = (n4 + kWorld - 1) / kWorld;
-  // phase 1: reduce-scatter my slice, write it back into my own bucket (only I read that slice)
+  // phase 1: reduce-scatter my slice, write it back into my own bucket (only I read that slice).
+  // kUnroll iterations are batched so that every thread keeps ~8 sixteen-byte peer loads in flight.
+  constexpr int kUnroll = kWorld >= 8 ? 1 : 8 / kWorld;
   {
     const long long s0 = slice * p.rank, s1 = min(n4, s0 + slice);
-    for (long long i = s0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < s1;
-         i += static_cast<long long>(gridDim.x) * blockDim.x) {
-      float4 v[kWorld];
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i0 = s0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i0 < s1; i0 += stride * kUnroll) {
+      float4 v[kUnroll][kWorld];
 #pragma unroll
-      for (int r = 0; r < kWorld; ++r) v[r] = ld_peer(p.bufs[(p.rank + r) % kWorld] + p.offset + i * 4);
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < s1) {
 #pragma unroll
-      for (int r = 0; r < kWorld; ++r) {
-        const float s = pre[(p.rank + r) % kWorld];
-        acc.x += s * v[r].x; acc.y += s * v[r].y; acc.z += s * v[r].z; acc.w += s * v[r].w;
+          for (int r = 0; r < kWorld; ++r) v[u][r] = ld_peer(p.bufs[(p.rank + r) % kWorld] + p.offset + i * 4);
+        }
       }
-      acc.x *= p.postscale; acc.y *= p.postscale; acc.z *= p.postscale; acc.w *= p.postscale;
-      reinterpret_cast<float4*>(p.bufs[p.rank] + p.offset)[i] = acc;
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < s1) {
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int r = 0; r < kWorld; ++r) {
+            const float s = pre[(p.rank + r) % kWorld];
+            acc.x += s * v[u][r].x; acc.y += s * v[u][r].y; acc.z += s * v[u][r].z; acc.w += s * v[u][r].w;
+          }
+          acc.x *= p.postscale; acc.y *= p.postscale; acc.z *= p.postscale; acc.w *= p.postscale;
+          reinterpret_cast<float4*>(p.bufs[p.rank] + p.offset)[i] = acc;
+        }
+      }
     }
   }
   __threadfence_system();
   rank_barrier(p, p.epoch + 2);
-  // phase 2: all-gather the reduced slices
+  // phase 2: all-gather the reduced slices (4 loads in flight per thread per peer slice)
 #pragma unroll
   for (int r = 0; r < kWorld; ++r) {
     const int src = (p.rank + r) % kWorld;
     const long long s0 = slice * src, s1 = min(n4, s0 + slice);
-    for (long long i = s0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < s1;
-         i += static_cast<long long>(gridDim.x) * blockDim.x) {
-      const float4 v = ld_peer(p.bufs[src] + p.offset + i * 4);
-      reinterpret_cast<float4*>(p.out + p.offset)[i] = v;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i0 = s0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i0 < s1; i0 += stride * 4) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * stride < s1) v[u] = ld_peer(p.bufs[src] + p.offset + (i0 + u * stride) * 4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * stride < s1) reinterpret_cast<float4*>(p.out + p.offset)[i0 + u * stride] = v[u];
     }
   }
   rank_barrier(p, p.epoch + 3);
@@ -197,7 +221,14 @@ int b200_allreduce_host(const B200ArHostArgs* a, void* stream_) {
                                                                     p.has_prescale ? p.prescale[0] : nullptr, p.postscale);
     return check_launch("scale_copy_kernel");
   }
-  int blocks = a->max_blocks > 0 ? a->max_blocks : kArMaxBlocks;
+  static int env_blocks = -1;
+  if (env_blocks < 0) { const char* e = getenv("B200_AR_BLOCKS"); env_blocks = e ? atoi(e) : 0; }
+  // enough blocks to keep NVLink busy for big buckets (measured: 64 -> 0.29, 296 -> 0.68 of the link
+  // roofline at 2 GPUs), few for small ones where the flag barriers dominate
+  int auto_blocks = static_cast<int>(p.count * 4 / (64 << 10));
+  if (auto_blocks < 8) auto_blocks = 8;
+  if (auto_blocks > 2 * num_sms()) auto_blocks = 2 * num_sms();
+  int blocks = a->max_blocks > 0 ? a->max_blocks : (env_blocks > 0 ? env_blocks : auto_blocks);
   if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
   const long long bytes = p.count * 4;
   int algo = a->algo;
