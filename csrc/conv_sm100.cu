@@ -261,45 +261,18 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         const int col = col0 + c;
         if (col >= col_end) break;
         const bool piece_ok = col + cpiece * 8 < col_end_pad;
-        // ---- epilogue operands: coalesced global loads (all issued before any use) -> smem -> own row
-        uint4 ka[4];
-        uint32_t mbits = 0xffffffffu;
+        // ---- epilogue operands: each thread reads the 64 contiguous bytes of its own row (4 x 16 B, all
+        // issued before any use).  A warp-wide load touches 32 rows, but every 32-byte sector is fully
+        // consumed by two of the four loads (second one hits L1), so DRAM traffic stays minimal and the
+        // smem round trips + syncs that a transposed load would need are avoided (issue-bound epilogue).
+        uint4 ka[4], km[4];
         if constexpr (kAdd || kMask) {
-          uint4 ta[4], tm[4];
+          const long long own = static_cast<long long>(pix) * ldo + col;
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            if (kMask && ok_r[i] && piece_ok) tm[i] = *reinterpret_cast<const uint4*>(maskp + roff_r[i] + c);
-            if (kAdd && ok_r[i] && piece_ok) ta[i] = *reinterpret_cast<const uint4*>(addp + roff_r[i] + c);
-          }
-          if constexpr (kMask) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(so_r[i]), "r"(tm[i].x), "r"(tm[i].y), "r"(tm[i].z), "r"(tm[i].w) : "memory");
-            __syncwarp();
-            mbits = 0;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 k;
-              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(k.x), "=r"(k.y), "=r"(k.z), "=r"(k.w) : "r"(own_off[j]));
-              const uint32_t w4[4] = {k.x, k.y, k.z, k.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                // bf16 > 0  <=>  the 16-bit pattern, as a signed integer, is > 0 (no NaNs expected in masks)
-                if (static_cast<int>(w4[e] << 16) > 0) mbits |= 1u << (j * 8 + 2 * e);
-                if (static_cast<int>(w4[e] & 0xffff0000u) > 0) mbits |= 1u << (j * 8 + 2 * e + 1);
-              }
-            }
-            __syncwarp();
-          }
-          if constexpr (kAdd) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(so_r[i]), "r"(ta[i].x), "r"(ta[i].y), "r"(ta[i].z), "r"(ta[i].w) : "memory");
-            __syncwarp();
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(ka[j].x), "=r"(ka[j].y), "=r"(ka[j].z), "=r"(ka[j].w) : "r"(own_off[j]));
-            __syncwarp();
+          for (int j = 0; j < 4; ++j) {
+            const bool ok = valid && (col + j * 8 < col_end_pad);
+            if constexpr (kMask) km[j] = ok ? *reinterpret_cast<const uint4*>(maskp + own + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+            if constexpr (kAdd) ka[j] = ok ? *reinterpret_cast<const uint4*>(addp + own + j * 8) : make_uint4(0u, 0u, 0u, 0u);
           }
         }
         uint32_t r[32];
@@ -327,10 +300,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
               }
             }
             if constexpr (kMask) {
-              const uint32_t mb = mbits >> (j * 8);
+              // bf16 > 0  <=>  its 16-bit pattern, read as a signed integer, is > 0
+              const uint32_t w4[4] = {km[j].x, km[j].y, km[j].z, km[j].w};
 #pragma unroll
-              for (int e = 0; e < 8; ++e)
-                if (!((mb >> e) & 1u)) v[e] = 0.f;
+              for (int e = 0; e < 4; ++e) {
+                if (static_cast<int>(w4[e] << 16) <= 0) v[2 * e] = 0.f;
+                if (static_cast<int>(w4[e] & 0xffff0000u) <= 0) v[2 * e + 1] = 0.f;
+              }
             }
             if constexpr (kAdd) {
               if (add_post) {
