@@ -20,31 +20,67 @@ struct LevelTable {
   int num_levels;
 };
 
+// Threshold + compaction.  Slots are claimed with ONE atomic per warp (prefix sum over the lanes'
+// pass counts) whenever the warp sits inside a single image, which is almost always: with an
+// untrained network millions of scores can pass and per-element atomics on one counter serialise.
 __global__ void collect_kernel(const __nv_bfloat16* __restrict__ logits, long long pixels_total, int HW, int K, int ld,
                                int a_off, float logit_thr, int max_cand, int* __restrict__ count,
                                unsigned long long* __restrict__ keys) {
   const int groups = (9 * K + 7) >> 3;
   const long long total = pixels_total * groups;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int g = static_cast<int>(i % groups);
-    const long long pix = i / groups;
-    const int b = static_cast<int>(pix / HW);
-    const int p = static_cast<int>(pix - static_cast<long long>(b) * HW);
-    const uint4 u = *reinterpret_cast<const uint4*>(logits + pix * ld + g * 8);
-    const float x[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
-                        bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  for (long long i0 = blockIdx.x * static_cast<long long>(blockDim.x) + (threadIdx.x & ~31); i0 < total; i0 += stride) {
+    const long long i = i0 + lane;
+    const bool in = i < total;
+    int g = 0, b = -1, p = 0;
+    float x[8];
+    uint32_t pass = 0;
+    if (in) {
+      g = static_cast<int>(i % groups);
+      const long long pix = i / groups;
+      b = static_cast<int>(pix / HW);
+      p = static_cast<int>(pix - static_cast<long long>(b) * HW);
+      const uint4 u = *reinterpret_cast<const uint4*>(logits + pix * ld + g * 8);
+      x[0] = bf16_lo(u.x); x[1] = bf16_hi(u.x); x[2] = bf16_lo(u.y); x[3] = bf16_hi(u.y);
+      x[4] = bf16_lo(u.z); x[5] = bf16_hi(u.z); x[6] = bf16_lo(u.w); x[7] = bf16_hi(u.w);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int ch = g * 8 + e;
-      if (ch < 9 * K && x[e] > logit_thr) {
-        const float score = 1.f / (1.f + __expf(-x[e]));
-        const int j = ch / K, k = ch - j * K;
-        const unsigned int id = static_cast<unsigned int>((a_off + p * 9 + j)) * static_cast<unsigned int>(K) + k;
-        const int slot = atomicAdd(count + b, 1);
-        if (slot < max_cand)
-          keys[static_cast<long long>(b) * max_cand + slot] =
-              (static_cast<unsigned long long>(__float_as_uint(score)) << 32) | static_cast<unsigned int>(~id);
+      for (int e = 0; e < 8; ++e)
+        if (g * 8 + e < 9 * K && x[e] > logit_thr) pass |= 1u << e;
+    }
+    const int mine = __popc(pass);
+    const int b0 = __shfl_sync(0xffffffffu, b, 0);
+    const bool uniform = __all_sync(0xffffffffu, !in || b == b0);
+    int slot;
+    if (uniform && b0 >= 0) {
+      int incl = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      const int tot = __shfl_sync(0xffffffffu, incl, 31);
+      int base = 0;
+      if (lane == 0 && tot) base = atomicAdd(count + b0, tot);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      slot = base + incl - mine;
+    } else {
+      slot = (in && mine) ? atomicAdd(count + b, mine) : 0;
+    }
+    if (in && mine) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        if ((pass >> e) & 1u) {
+          if (slot < max_cand) {
+            const int ch = g * 8 + e;
+            const int j = ch / K, k = ch - j * K;
+            const float score = 1.f / (1.f + __expf(-x[e]));
+            const unsigned int id = static_cast<unsigned int>((a_off + p * 9 + j)) * static_cast<unsigned int>(K) + k;
+            keys[static_cast<long long>(b) * max_cand + slot] =
+                (static_cast<unsigned long long>(__float_as_uint(score)) << 32) | static_cast<unsigned int>(~id);
+          }
+          ++slot;
+        }
       }
     }
   }
