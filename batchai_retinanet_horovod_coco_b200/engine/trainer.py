@@ -512,7 +512,7 @@ class NativeTrainer:
         """Move the gradient bucket into peer-mapped memory, allocate the reduced copy and make every
         rank start from rank 0's state (Horovod BroadcastGlobalVariablesCallback(0), train.py:111)."""
         self.G = self.comm.symmetric_bucket(self.n_train + 64)
-        self.Gavg = torch.zeros_like(self.G)
+        self.Gavg = self.comm.result[:self.G.numel()]   # peer-writable: the allreduce pushes results into it
         self.broadcast_state(0)
 
     def broadcast_state(self, root: int = 0):

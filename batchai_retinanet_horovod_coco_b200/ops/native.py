@@ -58,7 +58,7 @@ class WeightEntry(C.Structure):
 
 class ArHostArgs(C.Structure):
     _fields_ = [("bufs", C.c_void_p * 8), ("flags", C.c_void_p * 8), ("prescale", C.c_void_p * 8),
-                ("out", C.c_void_p), ("rank", C.c_int), ("world", C.c_int), ("offset", C.c_longlong),
+                ("outs", C.c_void_p * 8), ("out", C.c_void_p), ("rank", C.c_int), ("world", C.c_int), ("offset", C.c_longlong),
                 ("count", C.c_longlong), ("postscale", C.c_float), ("epoch", C.c_uint32), ("algo", C.c_int),
                 ("max_blocks", C.c_int), ("has_prescale", C.c_int)]
 

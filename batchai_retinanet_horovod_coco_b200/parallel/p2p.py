@@ -3,7 +3,7 @@
 Replaces Horovod's NCCL/MPI data plane, fusion-buffer memcpys and the separate ``tf.div``
 (reference ``train.py:103``).  Each rank ``cudaMalloc``s ONE region
 
-    [ flag pad | 256 B scalars (this rank's clip factor) | fp32 bucket ]
+    [ flag pad | 256 B scalars (this rank's clip factor) | fp32 bucket | fp32 result ]
 
 exports it with CUDA IPC, and maps every peer's region.  The engine's gradients are written
 straight into the bucket by the wgrad kernels, so there is nothing to copy in or out; the kernel
@@ -65,7 +65,7 @@ class P2PComm:
             return self.bucket[:nfloats]
         nfloats = (nfloats + 3) // 4 * 4
         self.bucket_elems = nfloats
-        total = self.flag_bytes + SCALARS_BYTES + 4 * nfloats
+        total = self.flag_bytes + SCALARS_BYTES + 8 * nfloats   # bucket + peer-writable result buffer
         with torch.cuda.device(self.device):
             self.base = native.ipc_alloc(total)
             handle = native.ipc_get_handle(self.base) if self.world > 1 else b""
@@ -83,6 +83,7 @@ class P2PComm:
         self.prescale_local = raw[off:off + 4].view(torch.float32)
         self.prescale_local.fill_(1.0)
         self.bucket = raw[off + SCALARS_BYTES:off + SCALARS_BYTES + 4 * nfloats].view(torch.float32)
+        self.result = raw[off + SCALARS_BYTES + 4 * nfloats:off + SCALARS_BYTES + 8 * nfloats].view(torch.float32)
         torch.cuda.synchronize(self.device)
         self.barrier_host()
         return self.bucket
@@ -92,12 +93,14 @@ class P2PComm:
             self._gather(b"x")
 
     # ------------------------------------------------------------------ collectives
-    def _args(self, out: torch.Tensor, offset: int, count: int, postscale: float, has_prescale: bool, algo: int):
+    def _args(self, out: torch.Tensor, offset: int, count: int, postscale: float, has_prescale: bool, algo: int,
+              push: bool = False):
         a = native.ArHostArgs()
         for r in range(self.world):
             a.bufs[r] = self.peer_base[r] + self.flag_bytes + SCALARS_BYTES
             a.flags[r] = self.peer_base[r]
             a.prescale[r] = self.peer_base[r] + self.flag_bytes
+            a.outs[r] = (self.peer_base[r] + self.flag_bytes + SCALARS_BYTES + 4 * self.bucket_elems) if push else 0
         a.out = out.data_ptr()
         a.rank, a.world = self.rank, self.world
         a.offset, a.count = offset, count
@@ -113,7 +116,9 @@ class P2PComm:
         """out[:n] = (1/world) * sum_r prescale_r * bucket_r[:n]  (bucket must be the symmetric bucket)."""
         assert bucket.data_ptr() == self.bucket.data_ptr(), "allreduce source must be the symmetric bucket"
         n4 = (n + 3) // 4 * 4
-        a = self._args(out, 0, n4, 1.0 / self.world, prescale, algo)
+        # results can be pushed into every rank's `result` buffer when `out` IS that buffer
+        push = out.data_ptr() == self.result.data_ptr()
+        a = self._args(out, 0, n4, 1.0 / self.world, prescale, algo, push=push)
         native.allreduce_host(a)
 
     def allreduce_sum_(self, t: torch.Tensor, average: bool = False):

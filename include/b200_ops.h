@@ -196,12 +196,13 @@ typedef struct {
   void* bufs[8];            /* every rank's fp32 bucket base (peer-mapped device pointers) */
   uint32_t* flags[8];       /* every rank's flag pad (b200_flag_pad_bytes(), zero-initialised) */
   const float* prescale[8]; /* every rank's device scalar (its clip factor), if has_prescale */
+  void* outs[8];            /* every rank's peer-mapped output buffer (algo 3, push); null entries otherwise */
   float* out;               /* LOCAL result buffer (same offsets as the bucket) */
   int rank, world;          /* world in {1, 2, 4, 8} */
   long long offset, count;  /* element range of the bucket, multiples of 4 */
   float postscale;          /* e.g. 1/world */
   uint32_t epoch;           /* flag base; advance by 4 per call, same on every rank */
-  int algo;                 /* 0 auto, 1 one-shot, 2 two-shot */
+  int algo;                 /* 0 auto, 1 one-shot, 2 two-shot (pull), 3 fused reduce + push all-gather */
   int max_blocks;           /* <= 64; 0 = default */
   int has_prescale;
 } B200ArHostArgs;

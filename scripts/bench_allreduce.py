@@ -5,7 +5,7 @@ same buffers, 1 KB .. 1 GB, device-timed with CUDA events, max over ranks.
 
 Prints one JSON line per size on rank 0: algorithm bandwidth (bytes / time), bus bandwidth
 (x 2(N-1)/N) and the fraction of the NVLink roofline (770 GB/s measured peer copy per direction:
-two-shot moves 2(N-1)/N * S bytes per direction per GPU)."""
+the fused reduce+push algorithm moves (N-1)/N * S bytes per direction per GPU)."""
 import json
 import os
 import sys
@@ -49,10 +49,11 @@ while size <= MAXB:
     n = size // 4
     iters = 50 if size <= (1 << 22) else (10 if size <= (1 << 27) else 4)
     row = {"bytes": size, "world": world}
-    for name, algo in (("oneshot", 1), ("twoshot", 2)):
+    for name, algo in (("oneshot", 1), ("twoshot", 2), ("push", 3)):
         if algo == 1 and size > (8 << 20):
             continue
-        ms = timeit(lambda: comm.allreduce_avg(bucket, out, n, prescale=True, algo=algo), iters)
+        dst = comm.result if algo == 3 else out
+        ms = timeit(lambda: comm.allreduce_avg(bucket, dst, n, prescale=True, algo=algo), iters)
         row[name + "_us"] = ms * 1e3
     best = min(v for k, v in row.items() if k.endswith("_us"))
     ms_n = timeit(lambda: dist.all_reduce(nccl_buf[:n]), iters)
@@ -60,7 +61,7 @@ while size <= MAXB:
     row["p2p_algbw_GBs"] = size / best / 1e3
     row["p2p_busbw_GBs"] = row["p2p_algbw_GBs"] * 2 * (world - 1) / world
     row["nccl_busbw_GBs"] = size / (ms_n * 1e3) / 1e3 * 2 * (world - 1) / world
-    roof_us = 2 * (world - 1) / world * size / LINK * 1e6
+    roof_us = (world - 1) / world * size / LINK * 1e6   # per direction: reads in, pushes out
     row["frac_of_nvlink_roofline"] = roof_us / best
     row["speedup_vs_nccl"] = ms_n * 1e3 / best
     if rank == 0:

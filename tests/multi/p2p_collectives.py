@@ -10,13 +10,14 @@ dist.init_process_group("nccl", device_id=dev)
 comm = P2PComm.from_torch_distributed(dev)
 N = 6_000_000
 bucket = comm.symmetric_bucket(N)
-for algo, n in ((1, 1000), (1, 100_000), (2, 100_000), (2, N), (0, 4096), (0, N)):
+for algo, n in ((1, 1000), (1, 100_000), (2, 100_000), (2, N), (0, 4096), (0, N), (3, 100_000), (3, N)):
     g = torch.Generator(device=dev).manual_seed(100 + rank)
     x = torch.randn(N, device=dev, generator=g)
     bucket.copy_(x)
     pre = 0.5 + rank
     comm.prescale_local.fill_(pre)
-    out = torch.zeros(N, device=dev)
+    out = comm.result if algo == 3 else torch.zeros(N, device=dev)
+    out.zero_()
     torch.cuda.synchronize(); dist.barrier()
     comm.allreduce_avg(bucket, out, n, prescale=True, algo=algo)
     torch.cuda.synchronize()
