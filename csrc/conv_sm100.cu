@@ -254,54 +254,77 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         ok_r[i] = (valid_mask >> rr) & 1u;
       }
 
+      // A warp owns at most two 32-column chunks of a tile (c0 and c0 + 128).  Their epilogue operands
+      // (residual / ReLU mask: the 64 contiguous bytes of this thread's row, 4 x 16 B, every sector fully
+      // consumed) and the shift row (one coalesced float per lane, broadcast later with shuffles) are all
+      // requested BEFORE waiting for the accumulator: the epilogue is bound by DRAM latency x bytes in
+      // flight, so everything a tile needs is put in flight at once, behind the MMA.
+      constexpr int kChunkStep = 32 * (kEpiWarps / 4);
+      const int c0 = cq * 32;
+      const long long own_row = static_cast<long long>(pix) * ldo + col0;
+      uint4 ka[2][4], km[2][4];
+      float sh[2] = {0.f, 0.f};
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int c = c0 + h * kChunkStep;
+        const bool chunk_ok = c < BN && col0 + c < col_end;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const bool ok = chunk_ok && valid && (col0 + c + j * 8 < col_end_pad);
+          if constexpr (kMask && !kAdd) km[h][j] = ok ? *reinterpret_cast<const uint4*>(maskp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+          if constexpr (kAdd && !kMask) ka[h][j] = ok ? *reinterpret_cast<const uint4*>(addp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+          if constexpr (kAdd && kMask) {
+            if (h == 0) {  // both operands: only the first chunk up front (register budget)
+              km[0][j] = ok ? *reinterpret_cast<const uint4*>(maskp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+              ka[0][j] = ok ? *reinterpret_cast<const uint4*>(addp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+            }
+          }
+        }
+        if (shiftp && chunk_ok && col0 + c + lane < col_end_pad) sh[h] = __ldg(shiftp + col0 + c + lane);
+      }
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * 256;
-      for (int c = cq * 32; c < BN; c += 32 * (kEpiWarps / 4)) {
-        const int col = col0 + c;
-        if (col >= col_end) break;
-        const bool piece_ok = col + cpiece * 8 < col_end_pad;
-        // ---- epilogue operands: each thread reads the 64 contiguous bytes of its own row (4 x 16 B, all
-        // issued before any use).  A warp-wide load touches 32 rows, but every 32-byte sector is fully
-        // consumed by two of the four loads (second one hits L1), so DRAM traffic stays minimal and the
-        // smem round trips + syncs that a transposed load would need are avoided (issue-bound epilogue).
-        uint4 ka[4], km[4];
-        if constexpr (kAdd || kMask) {
-          const long long own = static_cast<long long>(pix) * ldo + col;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const bool ok = valid && (col + j * 8 < col_end_pad);
-            if constexpr (kMask) km[j] = ok ? *reinterpret_cast<const uint4*>(maskp + own + j * 8) : make_uint4(0u, 0u, 0u, 0u);
-            if constexpr (kAdd) ka[j] = ok ? *reinterpret_cast<const uint4*>(addp + own + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+      for (int h = 0; h < 2; ++h) {
+        const int c = c0 + h * kChunkStep;
+        const int col = col0 + c;
+        if (c >= BN || col >= col_end) break;
+        const bool piece_ok = col + cpiece * 8 < col_end_pad;
+        if constexpr (kAdd && kMask) {
+          if (h == 1) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const bool ok = valid && (col + j * 8 < col_end_pad);
+              km[1][j] = ok ? *reinterpret_cast<const uint4*>(maskp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+              ka[1][j] = ok ? *reinterpret_cast<const uint4*>(addp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+            }
           }
         }
         uint32_t r[32];
         tmem_ld_32x32(t_row + c, r);
         tmem_ld_wait();
         // ---- row-per-thread math, result into the staging buffer (issue-bound: keep it short)
-        if (valid) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int cj = col + j * 8;
-            if (cj >= col_end) break;
-            float v[8];
+        for (int j = 0; j < 4; ++j) {
+          const int cj = col + j * 8;
+          float v[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j * 8 + e]);
-            if (shiftp) {
-              const float4 s0 = __ldg(reinterpret_cast<const float4*>(shiftp + cj));
-              const float4 s1 = __ldg(reinterpret_cast<const float4*>(shiftp + cj + 4));
-              v[0] += s0.x; v[1] += s0.y; v[2] += s0.z; v[3] += s0.w;
-              v[4] += s1.x; v[5] += s1.y; v[6] += s1.z; v[7] += s1.w;
-            }
+          for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j * 8 + e]);
+          if (shiftp) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] += __shfl_sync(0xffffffffu, sh[h], j * 8 + e);
+          }
+          if (valid && cj < col_end) {
             if constexpr (kAdd) {
               if (!add_post) {
-                v[0] += bf16_lo(ka[j].x); v[1] += bf16_hi(ka[j].x); v[2] += bf16_lo(ka[j].y); v[3] += bf16_hi(ka[j].y);
-                v[4] += bf16_lo(ka[j].z); v[5] += bf16_hi(ka[j].z); v[6] += bf16_lo(ka[j].w); v[7] += bf16_hi(ka[j].w);
+                v[0] += bf16_lo(ka[h][j].x); v[1] += bf16_hi(ka[h][j].x); v[2] += bf16_lo(ka[h][j].y); v[3] += bf16_hi(ka[h][j].y);
+                v[4] += bf16_lo(ka[h][j].z); v[5] += bf16_hi(ka[h][j].z); v[6] += bf16_lo(ka[h][j].w); v[7] += bf16_hi(ka[h][j].w);
               }
             }
             if constexpr (kMask) {
               // bf16 > 0  <=>  its 16-bit pattern, read as a signed integer, is > 0
-              const uint32_t w4[4] = {km[j].x, km[j].y, km[j].z, km[j].w};
+              const uint32_t w4[4] = {km[h][j].x, km[h][j].y, km[h][j].z, km[h][j].w};
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 if (static_cast<int>(w4[e] << 16) <= 0) v[2 * e] = 0.f;
@@ -310,8 +333,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             }
             if constexpr (kAdd) {
               if (add_post) {
-                v[0] += bf16_lo(ka[j].x); v[1] += bf16_hi(ka[j].x); v[2] += bf16_lo(ka[j].y); v[3] += bf16_hi(ka[j].y);
-                v[4] += bf16_lo(ka[j].z); v[5] += bf16_hi(ka[j].z); v[6] += bf16_lo(ka[j].w); v[7] += bf16_hi(ka[j].w);
+                v[0] += bf16_lo(ka[h][j].x); v[1] += bf16_hi(ka[h][j].x); v[2] += bf16_lo(ka[h][j].y); v[3] += bf16_hi(ka[h][j].y);
+                v[4] += bf16_lo(ka[h][j].z); v[5] += bf16_hi(ka[h][j].z); v[6] += bf16_lo(ka[h][j].w); v[7] += bf16_hi(ka[h][j].w);
               }
             }
             if (relu) {
