@@ -221,11 +221,21 @@ class NativeTrainer:
         return self.model
 
     def _refresh_weights(self):
+        """fp32 masters -> bf16 working weights (BN scale folded): one table-driven kernel for every
+        TMA-fed conv plus a gather for the stem's packed [64][256] filter."""
         self.wtable.run()
         s = self.stem
-        w = s.wview(self.P).view(s.kh, s.kw, s.cout, s.cin).permute(2, 3, 0, 1)
-        self.stem_w = w.to(BF16).contiguous(memory_format=torch.channels_last)
-        self.stem_wp = native.pack_stem_weight(s.wview(self.P), s.scale)
+        if not hasattr(self, "_stem_idx"):
+            # packed k = r*28 + s*4 + c  <-  master (tap = r*7 + s, co, ci); padding entries read a zero slot
+            k = torch.arange(256, device=self.device)
+            r, rem = k // 28, k % 28
+            sx, c = rem // 4, rem % 4
+            ok = (k < 196) & (c < 3)
+            co = torch.arange(64, device=self.device).view(64, 1)
+            idx = ((r * 7 + sx).view(1, 256) * 64 + co) * 3 + c.view(1, 256)
+            self._stem_idx = torch.where(ok.view(1, 256), idx, torch.zeros_like(idx))
+            self._stem_ok = ok.view(1, 256).float() * s.scale.view(64, 1)
+        self.stem_wp = (s.wview(self.P).reshape(-1)[self._stem_idx] * self._stem_ok).to(BF16)
 
     def optimizer_state(self):
         """Adam slots as {keras layer name: {'kernel': (m, v), 'bias': (m, v)}} views + iterations."""
@@ -498,14 +508,7 @@ class NativeTrainer:
         # stem: max-pool + ReLU + BN backward, then cuDNN wgrad for the 7x7x3 filter
         native.bn_relu_maxpool_bwd(p["pool_idx"], self.ones64, g, p["dstem"], *p["pool_pad"])
         if self.stem.trainable:
-            # filter gradient of the 7x7x3 stem: cuDNN backward-filter (0.3% of the step's FLOPs)
-            x = p["img"][..., :3].permute(0, 3, 1, 2)
-            gy = p["dstem"].permute(0, 3, 1, 2)
-            _, dw, _ = torch.ops.aten.convolution_backward(gy, x, self.stem_w, None, [2, 2], [3, 3], [1, 1], False,
-                                                           [0, 0], 1, [False, True, False])
-            s = self.stem
-            dwm = dw.float().permute(2, 3, 0, 1).reshape(s.taps, s.cout, s.cin) * s.scale.view(1, -1, 1)
-            s.wview(self.G).add_(dwm)
+            native.stem_wgrad(p["img"], p["dstem"], self.stem.scale, self.stem.wview(self.G))
 
     # ------------------------------------------------------------------ optimizer
     def _attach_comm(self):

@@ -178,6 +178,12 @@ def stem_conv(x4, w_packed, shift, y):
     _check(require().b200_stem_conv(_ptr(x4), _ptr(w_packed), _ptr(shift), _ptr(y), n, h, w, _stream()), "b200_stem_conv")
 
 
+def stem_wgrad(x4, dy, scale, dw):
+    """dw fp32 [49,64,3] += scale[co] * grad of the stem filter (x4 bf16 [N,H,W,4], dy bf16 [N,H/2,W/2,64])."""
+    n, h, w, c = x4.shape
+    _check(require().b200_stem_wgrad(_ptr(x4), _ptr(dy), _ptr(scale), _ptr(dw), n, h, w, _stream()), "b200_stem_wgrad")
+
+
 def pack_stem_weight(master_tci, scale=None):
     """master fp32 [49, 64, 3] (tap, co, ci) -> bf16 [64, 256], k = r*28 + s*4 + c, BN scale folded."""
     w = master_tci.view(7, 7, 64, 3).permute(2, 0, 1, 3)          # co, r, s, c

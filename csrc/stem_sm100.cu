@@ -223,3 +223,211 @@ extern "C" int b200_stem_conv(const void* x, const void* w_packed, const float* 
   stem_conv_kernel<<<grid, kStemThreads, kStemSmem, static_cast<cudaStream_t>(stream)>>>(p);
   return check_launch("stem_conv_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Stem weight gradient:  dW[k][co] += scale[co] * sum_pixels dY[p, co] * Xcol[p, k],  k = r*28 + s*4 + c.
+// GEMM: M = co (64 valid of 128), N = 256 (196 valid), K = output pixels.  A = dY tiles by TMA
+// (MN-major), B = the same gathered im2col tile as the forward kernel, used as an MN-major operand
+// (rows = pixels).  One CTA per SM accumulates its share of the pixels in TMEM and flushes once with
+// fp32 atomics into the master-layout gradient [49][64][3].
+namespace b200 {
+
+constexpr int kSwStages = 3;
+constexpr int kSwAStage = 2 * 8192;   // chunk 0 = dY [64 px][64 co]; chunk 1 stays zero (co 64..127)
+constexpr int kSwBStage = 4 * 8192;   // [64 px][256 k] as four 64-column chunks
+constexpr int kSwThreads = 384;       // w0 TMA+MMA, w1 TMEM alloc, w4-7 epilogue, w8-11 producers
+constexpr int kSwSmem = kSwStages * (kSwAStage + kSwBStage) + 1024 + 128;
+
+struct StemWgradParams {
+  CUtensorMap dy_map;
+  const __nv_bfloat16* x;   // [N, H, W, 4]
+  const float* scale;       // [64] or null
+  float* dw;                // fp32 [49][64][3], accumulated into
+  int N, H, W, OH, OW;
+  int tiles_h, tiles_w, total_tiles;
+};
+
+__global__ void __launch_bounds__(kSwThreads, 1) stem_wgrad_kernel(const __grid_constant__ StemWgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_smem = smem_base;
+  const uint32_t b_smem = smem_base + kSwStages * kSwAStage;
+  const uint32_t bar_base = b_smem + kSwStages * kSwBStage;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kSwStages + s); };
+  const uint32_t tfull_bar = bar_base + 8u * (2 * kSwStages);
+  const uint32_t tmem_ptr_smem = bar_base + 64;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  for (int i = threadIdx.x; i < kSwStages * (kSwAStage + kSwBStage) / 16; i += kSwThreads)
+    reinterpret_cast<uint4*>(smem_gen)[i] = make_uint4(0u, 0u, 0u, 0u);
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.dy_map);
+    for (int s = 0; s < kSwStages; ++s) {
+      mbar_init(full_bar(s), 129);   // 128 gather threads + the TMA issuer
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr_smem, 256);
+    tmem_relinquish();
+  }
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
+
+  auto decode = [&](int tile, int& n, int& y0, int& x0) {
+    const int per_img = p.tiles_h * p.tiles_w;
+    n = tile / per_img;
+    const int rem = tile - n * per_img;
+    y0 = (rem / p.tiles_w) * 4;
+    x0 = (rem % p.tiles_w) * 16;
+  };
+  const int my_tiles = (p.total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+
+  if (warp >= 8) {
+    // gather: thread -> (pixel m, half of the filter rows)
+    const int t = (warp - 8) * 32 + lane;
+    const int m = t & 63, part = t >> 6;
+    const int r_lo = part ? 4 : 0, r_hi = part ? 7 : 4;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      int n, y0, x0;
+      decode(tile, n, y0, x0);
+      const int oy = y0 + (m >> 4), ox = x0 + (m & 15);
+      const bool pix_ok = oy < p.OH && ox < p.OW;   // dY is zero-filled there, but keep X finite anyway
+      mbar_wait(empty_bar(stage), phase ^ 1);
+      uint8_t* b_row = smem_gen + kSwStages * kSwAStage + stage * kSwBStage + m * 128;
+      const int sw = m & 7;
+      for (int r = r_lo; r < r_hi; ++r) {
+        const int iy = 2 * oy + r - 3;
+        const bool row_ok = pix_ok && iy >= 0 && iy < p.H;
+        const __nv_bfloat16* src = p.x + (static_cast<long long>(n) * p.H + (row_ok ? iy : 0)) * p.W * 4;
+#pragma unroll
+        for (int s = 0; s < 7; ++s) {
+          const int ix = 2 * ox + s - 3;
+          uint2 v = make_uint2(0u, 0u);
+          if (row_ok && ix >= 0 && ix < p.W) v = __ldg(reinterpret_cast<const uint2*>(src + static_cast<long long>(ix) * 4));
+          const int kbyte = (r * 28 + s * 4) * 2;
+          const int kb = kbyte >> 7, within = kbyte & 127;
+          *reinterpret_cast<uint2*>(b_row + kb * 8192 + (((within >> 4) ^ sw) << 4) + (within & 15)) = v;
+        }
+      }
+      fence_async_smem();
+      mbar_arrive(full_bar(stage));
+      if (++stage == kSwStages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+  } else if (warp == 0) {
+    // TMA issue for dY + MMA issue (one lane does both: the loop is short and strictly ordered)
+    const uint32_t idesc = make_idesc_bf16(128, 256, 1, 1);
+    int stage_p = 0, stage_c = 0;
+    uint32_t phase_p = 0, phase_c = 0;
+    int issued = 0;
+    int tile_p = blockIdx.x;
+    for (int it = 0; it < my_tiles; ++it) {
+      // keep the dY loads kSwStages ahead
+      while (issued < my_tiles && issued < it + kSwStages) {
+        mbar_wait(empty_bar(stage_p), phase_p ^ 1);
+        if (lane == 0) {
+          int n, y0, x0;
+          decode(tile_p, n, y0, x0);
+          mbar_expect_tx(full_bar(stage_p), 8192);
+          tma_load_4d(a_smem + stage_p * kSwAStage, &p.dy_map, full_bar(stage_p), 0, x0, y0, n);
+        }
+        __syncwarp();
+        tile_p += gridDim.x;
+        ++issued;
+        if (++stage_p == kSwStages) {
+          stage_p = 0;
+          phase_p ^= 1;
+        }
+      }
+      mbar_wait(full_bar(stage_c), phase_c);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint64_t adesc = make_smem_desc(a_smem + stage_c * kSwAStage, 8192, 1024);
+        const uint64_t bdesc = make_smem_desc(b_smem + stage_c * kSwBStage, 8192, 1024);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_bf16(tmem_base, adesc + 128 * k, bdesc + 128 * k, idesc, (it | k) != 0);
+        umma_commit(empty_bar(stage_c));
+        if (it == my_tiles - 1) umma_commit(tfull_bar);
+      }
+      __syncwarp();
+      if (++stage_c == kSwStages) {
+        stage_c = 0;
+        phase_c ^= 1;
+      }
+    }
+  } else if (warp >= 4 && warp < 6 && my_tiles > 0) {
+    // epilogue: rows co = 0..63 live in TMEM lanes 0..63 (quarters 0 and 1)
+    const int quarter = warp - 4;
+    const int co = quarter * 32 + lane;
+    const float rs = p.scale ? __ldg(p.scale + co) : 1.f;
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    for (int c = 0; c < 224; c += 32) {
+      uint32_t r[32];
+      tmem_ld_32x32(t_row + c, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int k = c + j;
+        const int ci = k & 3;
+        if (k < 196 && ci < 3) {
+          const int tap = (k / 28) * 7 + (k % 28) / 4;
+          atomicAdd(p.dw + (tap * 64 + co) * 3 + ci, __uint_as_float(r[j]) * rs);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
+}  // namespace b200
+
+extern "C" int b200_stem_wgrad(const void* x, const void* dy, const float* scale, float* dw, int N, int H, int W,
+                               void* stream) {
+  using namespace b200;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA_OK(cudaFuncSetAttribute(stem_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSwSmem));
+    attr = true;
+  }
+  StemWgradParams p;
+  memset(&p, 0, sizeof(p));
+  p.x = static_cast<const __nv_bfloat16*>(x);
+  p.scale = scale;
+  p.dw = dw;
+  p.N = N;
+  p.H = H;
+  p.W = W;
+  p.OH = (H + 1) / 2;
+  p.OW = (W + 1) / 2;
+  p.tiles_h = (p.OH + 3) / 4;
+  p.tiles_w = (p.OW + 15) / 16;
+  p.total_tiles = N * p.tiles_h * p.tiles_w;
+  unsigned long long dims[4] = {64ull, static_cast<unsigned long long>(p.OW), static_cast<unsigned long long>(p.OH),
+                                static_cast<unsigned long long>(N)};
+  unsigned long long strides[3] = {128ull, static_cast<unsigned long long>(p.OW) * 128ull,
+                                   static_cast<unsigned long long>(p.OH) * p.OW * 128ull};
+  const unsigned int box[4] = {64u, 16u, 4u, 1u};
+  int rc = make_tmap_bf16(&p.dy_map, dy, 4, dims, strides, box);
+  if (rc) return rc;
+  const int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
+  stem_wgrad_kernel<<<grid, kSwThreads, kSwSmem, static_cast<cudaStream_t>(stream)>>>(p);
+  return check_launch("stem_wgrad_kernel");
+}

@@ -91,6 +91,9 @@ int b200_wgrad(const B200WgradArgs* args, void* stream);
  * swizzled smem tile (Cin=3 cannot feed TMA).  Replaces cuDNN conv1 forward (G1). */
 int b200_stem_conv(const void* x, const void* w_packed, const float* shift, void* y, int N, int H, int W,
                    void* stream);
+/* Stem weight gradient: dw fp32 [49][64][3] (tap, co, ci) += scale[co] * dY^T * im2col(x).
+ * dy bf16 [N,ceil(H/2),ceil(W/2),64].  Replaces cuDNN backward-filter for conv1 (G12). */
+int b200_stem_wgrad(const void* x, const void* dy, const float* scale, float* dw, int N, int H, int W, void* stream);
 
 /* ------------------------------------------------------------------ bandwidth-bound fused ops */
 

@@ -208,3 +208,20 @@ def test_stem_conv(n, h, w):
     w_eff = (wt * scale.view(64, 1, 1, 1)).to(torch.bfloat16).float()
     ref = F.conv2d(x[..., :3].float().permute(0, 3, 1, 2), w_eff, stride=2, padding=3).permute(0, 2, 3, 1) + shift
     _close(y, ref.clamp(min=0))
+
+
+@pytest.mark.parametrize("n,h,w", [(2, 64, 96), (1, 75, 101), (3, 200, 264)])
+def test_stem_wgrad(n, h, w):
+    torch.manual_seed(0)
+    x = torch.zeros(n, h, w, 4, device="cuda", dtype=torch.bfloat16)
+    x[..., :3] = (torch.randn(n, h, w, 3, device="cuda") * 40).to(torch.bfloat16)
+    oh, ow = (h + 1) // 2, (w + 1) // 2
+    dy = (torch.randn(n, oh, ow, 64, device="cuda") * 0.1).to(torch.bfloat16)
+    scale = torch.rand(64, device="cuda") + 0.5
+    dw = torch.zeros(49, 64, 3, device="cuda")
+    native.stem_wgrad(x, dy, scale, dw)
+    wz = torch.zeros(64, 3, 7, 7, device="cuda", requires_grad=True)
+    y = F.conv2d(x[..., :3].float().permute(0, 3, 1, 2), wz, stride=2, padding=3)
+    y.backward(dy.float().permute(0, 3, 1, 2))
+    ref = cv.pack_master(wz.grad) * scale.view(1, 64, 1)
+    _close(dw, ref)
