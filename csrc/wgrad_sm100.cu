@@ -132,37 +132,40 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
 
   if (pt_begin < pt_end) {
     if (warp == 0) {
-      if (lane == 0) {
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int pt = pt_begin; pt < pt_end; ++pt) {
-          int pi, n, y0, x0;
-          w_decode(p, pt, pi, n, y0, x0);
-          const int xbase = p.prob[pi].xmap_base;
-          const void* dymap = &p.dy_maps[pi];
-          mbar_wait(empty_bar(stage), phase ^ 1);
-          mbar_expect_tx(full_bar(stage), stage_bytes);
-          const uint32_t a_dst = a_smem + stage * kWAStage;
-          const uint32_t b_dst = b_smem + stage * kWBStage;
-          for (int c = 0; c < a_chunks; ++c)
-            tma_load_4d(a_dst + c * kChunkBytes, dymap, full_bar(stage), co_base + c * 64, x0, y0, n);
-          for (int c = 0; c < n_chunks; ++c) {
-            int t, ci;
-            if (p.taps_per_unit > 1) {
-              t = tap0 + c / p.chunks_per_tap;
-              ci = (c % p.chunks_per_tap) * 64;
-            } else {
-              t = tap0;
-              ci = n_tile * 256 + c * 64;
-            }
-            const WTap tap = p.taps[t];
-            tma_load_4d(b_dst + c * kChunkBytes, &p.x_maps[xbase + tap.map], full_bar(stage), ci, x0 + tap.dw,
-                        y0 + tap.dh, n);
-          }
-          if (++stage == kWStages) {
-            stage = 0;
-            phase ^= 1;
-          }
+      // Producer warp: lane 0 arms the barrier, then lanes 0..(a_chunks + n_chunks - 1) each issue ONE of the
+      // stage's TMA boxes, so the (up to 8) box issues of a stage overlap instead of serialising in one thread.
+      int stage = 0;
+      uint32_t phase = 0;
+      int t = tap0, ci = 0;
+      bool is_a = lane < a_chunks;
+      const int bc = lane - a_chunks;   // packed B chunk of this lane
+      if (!is_a && bc < n_chunks) {
+        if (p.taps_per_unit > 1) {
+          t = tap0 + bc / p.chunks_per_tap;
+          ci = (bc % p.chunks_per_tap) * 64;
+        } else {
+          ci = n_tile * 256 + bc * 64;
+        }
+      }
+      const bool active = lane < a_chunks + n_chunks;
+      const WTap tap = p.taps[t];
+      for (int pt = pt_begin; pt < pt_end; ++pt) {
+        int pi, n, y0, x0;
+        w_decode(p, pt, pi, n, y0, x0);
+        mbar_wait(empty_bar(stage), phase ^ 1);
+        if (lane == 0) mbar_expect_tx(full_bar(stage), stage_bytes);
+        __syncwarp();
+        if (active) {
+          if (is_a)
+            tma_load_4d(a_smem + stage * kWAStage + lane * kChunkBytes, &p.dy_maps[pi], full_bar(stage), co_base + lane * 64,
+                        x0, y0, n);
+          else
+            tma_load_4d(b_smem + stage * kWBStage + bc * kChunkBytes, &p.x_maps[p.prob[pi].xmap_base + tap.map],
+                        full_bar(stage), ci, x0 + tap.dw, y0 + tap.dh, n);
+        }
+        if (++stage == kWStages) {
+          stage = 0;
+          phase ^= 1;
         }
       }
     } else if (warp == 1) {
