@@ -136,32 +136,36 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      bool first_pass = true;
-      const bool weights_resident = (p.num_n_tiles == 1) && (kStages % num_k == 0);
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        int pi, n, y0, x0, n_tile;
-        decode_tile(p, tile, pi, n, y0, x0, n_tile);
-        const int map_base = p.prob[pi].map_base;
-        for (int t = 0; t < p.num_taps; ++t) {
-          const Tap tap = p.taps[t];
-          const void* amap = &p.in_maps[map_base + tap.map];
-          for (int kc = 0; kc < p.num_kc; ++kc) {
-            mbar_wait(empty_bar(stage), phase ^ 1);
-            // Weights stay resident: when the whole K loop fits the ring (num_k divides kStages) and there
-            // is a single N tile, stage s always holds the same weight tile, so it is fetched once.
-            const bool load_b = !weights_resident || first_pass;
+    // The whole warp runs the loop; lane 0 arms the barrier and issues the activation box, lane 1 issues
+    // the weight box, so the two TMA issues of a stage overlap (a single issuing thread was measurably
+    // the bottleneck in the weight-gradient kernel).
+    int stage = 0;
+    uint32_t phase = 0;
+    bool first_pass = true;
+    // Weights stay resident: when the whole K loop fits the ring (num_k divides kStages) and there is a
+    // single N tile, stage s always holds the same weight tile, so it is fetched once.
+    const bool weights_resident = (p.num_n_tiles == 1) && (kStages % num_k == 0);
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int pi, n, y0, x0, n_tile;
+      decode_tile(p, tile, pi, n, y0, x0, n_tile);
+      const int map_base = p.prob[pi].map_base;
+      for (int t = 0; t < p.num_taps; ++t) {
+        const Tap tap = p.taps[t];
+        const void* amap = &p.in_maps[map_base + tap.map];
+        for (int kc = 0; kc < p.num_kc; ++kc) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const bool load_b = !weights_resident || first_pass;
+          if (lane == 0) {
             mbar_expect_tx(full_bar(stage), kAStageBytes + (load_b ? b_bytes : 0u));
             tma_load_4d(a_smem + stage * kAStageBytes, amap, full_bar(stage), kc * kBK, x0 + tap.dw, y0 + tap.dh, n);
-            if (load_b)
-              tma_load_3d(b_smem + stage * kBStageBytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
-            if (++stage == kStages) {
-              stage = 0;
-              phase ^= 1;
-              first_pass = false;
-            }
+          }
+          __syncwarp();
+          if (lane == 1 && load_b)
+            tma_load_3d(b_smem + stage * kBStageBytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+            first_pass = false;
           }
         }
       }
