@@ -18,7 +18,7 @@ def create_trainer(model, device, lr=1e-5, clipnorm=0.001, batch=1, image_hw=(80
             from ..parallel.p2p import P2PComm
             comm = P2PComm(hvd.rank(), hvd.size(), device, hvd._allgather_bytes)
         return NativeTrainer(model=model, device=device, lr=lr, clipnorm=clipnorm, batch=batch, image_hw=image_hw,
-                             freeze_backbone=freeze_backbone, comm=comm)
+                             freeze_backbone=freeze_backbone, comm=comm, shape_bucket=64)
     from .spec import SpecTrainer
     if freeze_backbone:
         model.freeze_backbone()

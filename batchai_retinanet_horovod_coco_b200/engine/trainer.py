@@ -81,7 +81,8 @@ class Conv:
 class NativeTrainer:
     def __init__(self, backbone: str = "resnet50", num_classes: int = 80, device="cuda", batch: int = 8,
                  image_hw=(800, 1333), lr: float = 1e-5, clipnorm: float = 0.001, distributed: bool = False,
-                 model: RetinaNet | None = None, freeze_backbone: bool = False, comm=None):
+                 model: RetinaNet | None = None, freeze_backbone: bool = False, comm=None, shape_bucket: int = 1,
+                 max_plans: int = 4):
         native.require()
         self.device = torch.device(device)
         self.num_classes = num_classes
@@ -90,6 +91,10 @@ class NativeTrainer:
         self.beta1, self.beta2, self.eps = 0.9, 0.999, 1e-7
         self.iterations = 0
         self.freeze_backbone = freeze_backbone
+        # Real batches are padded to their own max HxW (reference generator), so shapes change every step:
+        # sizes are rounded up to `shape_bucket` and only the `max_plans` most recent buffer plans are kept.
+        self.shape_bucket = max(1, int(shape_bucket))
+        self.max_plans = max(1, int(max_plans))
         self.model = model if model is not None else RetinaNet(num_classes, backbone)
         if freeze_backbone:
             self.model.freeze_backbone()
@@ -245,7 +250,10 @@ class NativeTrainer:
     def _plan(self, B, H, W):
         key = (B, H, W)
         if key in self._plans:
+            self._plans[key] = self._plans.pop(key)   # most recently used last
             return self._plans[key]
+        while len(self._plans) >= self.max_plans:
+            self._plans.pop(next(iter(self._plans)))  # evict the least recently used plan
         dev = self.device
         p = {}
 
@@ -359,9 +367,9 @@ class NativeTrainer:
                          c.kw, c.stride, ph, pw, rowscale=c.scale, dbias=c.bview(self.G) if c.has_bias else None)
 
     # ------------------------------------------------------------------ forward
-    def _forward(self, p, images_u8):
+    def _forward(self, p, images_u8, img_hw=None):
         B, H, W, _ = images_u8.shape
-        native.preprocess(images_u8, p["img"], CAFFE_MEAN_BGR)
+        native.preprocess(images_u8, p["img"], CAFFE_MEAN_BGR, img_hw)
         native.stem_conv(p["img"], self.stem_wp, self.stem.shift, p["stem_out"])     # conv + BN + ReLU
         native.bn_relu_maxpool_fwd(p["stem_out"], self.ones64, self.zeros64, p["pool"], p["pool_idx"], *p["pool_pad"])
         self._mark("fwd_stem")
@@ -563,6 +571,20 @@ class NativeTrainer:
         self._prof = None
         return out
 
+    def _bucket(self, images_u8):
+        """Pad H, W up to a multiple of ``shape_bucket`` with the mean colour (zero after preprocessing).
+        Anchors whose centre falls in the padding are ignored through ``img_hw`` exactly as for the
+        reference's batch padding."""
+        b = self.shape_bucket
+        H, W = images_u8.shape[1:3]
+        Hp, Wp = -(-H // b) * b, -(-W // b) * b
+        if (Hp, Wp) == (H, W):
+            return images_u8
+        out = torch.empty(images_u8.shape[0], Hp, Wp, 3, dtype=torch.uint8, device=images_u8.device)
+        out[..., 0], out[..., 1], out[..., 2] = 104, 117, 124
+        out[:, :H, :W] = images_u8
+        return out
+
     # ------------------------------------------------------------------ public API
     def train_step(self, images_u8, gt, gt_count, img_hw):
         """One optimisation step.  Inputs may live in (pinned) host memory or on the device:
@@ -574,11 +596,12 @@ class NativeTrainer:
         gt = gt.to(dev, torch.float32, non_blocking=True)
         gt_count = gt_count.to(dev, torch.int32, non_blocking=True)
         img_hw = img_hw.to(dev, torch.int32, non_blocking=True)
+        images_u8 = self._bucket(images_u8)
         B, H, W, _ = images_u8.shape
         p = self._plan(B, H, W)
         self.G.zero_()
         self._mark("h2d+zero")
-        self._forward(p, images_u8)
+        self._forward(p, images_u8, img_hw)
         self._mark("forward")
         self._losses(p, gt, gt_count, img_hw)
         self._mark("losses")
@@ -592,12 +615,13 @@ class NativeTrainer:
     def forward_loss(self, images_u8, gt, gt_count, img_hw):
         """Forward + losses + backward WITHOUT the optimizer (testing / gradient checks)."""
         dev = self.device
-        images_u8 = images_u8.to(dev)
+        images_u8 = self._bucket(images_u8.to(dev))
         B, H, W, _ = images_u8.shape
         p = self._plan(B, H, W)
         self.G.zero_()
-        self._forward(p, images_u8)
-        self._losses(p, gt.to(dev, torch.float32), gt_count.to(dev, torch.int32), img_hw.to(dev, torch.int32))
+        img_hw = img_hw.to(dev, torch.int32)
+        self._forward(p, images_u8, img_hw)
+        self._losses(p, gt.to(dev, torch.float32), gt_count.to(dev, torch.int32), img_hw)
         self._backward(p)
         return torch.stack([self.scal[2] + self.scal[3], self.scal[2], self.scal[3]]), p
 
@@ -605,10 +629,12 @@ class NativeTrainer:
     def predict(self, images_u8, score_threshold=0.05, max_detections=300, nms_threshold=0.5):
         """Prediction graph (reference train.py:95): boxes [B,300,4], scores [B,300], labels [B,300]."""
         images_u8 = images_u8.to(self.device)
+        H0, W0 = images_u8.shape[1:3]
+        images_u8 = self._bucket(images_u8)
         B, H, W, _ = images_u8.shape
         p = self._plan(B, H, W)
         self._forward(p, images_u8)
-        return native.filter_detections_levels(p["cls_o"], p["reg_o"], self.num_classes, p["anchors"], (H, W),
+        return native.filter_detections_levels(p["cls_o"], p["reg_o"], self.num_classes, p["anchors"], (H0, W0),
                                                score_threshold, nms_threshold, max_detections)
 
     def gradients_by_layer(self):

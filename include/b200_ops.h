@@ -135,7 +135,7 @@ int b200_colsum_multi(const void* const* xs, const long long* rows, int n, int c
 
 /* Image normalise + pad (G19): uint8 HWC (BGR) -> bf16 NHWC with Caffe mean subtraction. */
 int b200_preprocess(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean,
-                    void* stream);
+                    const int* img_hw /* optional device int32 [N,2]: pixels outside (h,w) are zeroed */, void* stream);
 
 /* Anchor generation (G15): 9 anchors per location, level l, written at anchors[offset..]. */
 int b200_generate_anchors(float* anchors, int H, int W, int stride, float size, void* stream);

@@ -93,3 +93,19 @@ def test_engine_predict_shapes():
     img, *_ = _inputs(1, 128, 160)
     b, s, l = nt.predict(img)
     assert b.shape == (1, 300, 4) and s.shape == (1, 300) and l.shape == (1, 300)
+
+
+def test_engine_shape_buckets_and_plan_lru():
+    """Real batches change shape every step: sizes are rounded up to the bucket and old plans are evicted."""
+    from batchai_retinanet_horovod_coco_b200.engine.trainer import NativeTrainer
+    nt = NativeTrainer("resnet50", 80, device="cuda", batch=1, image_hw=(128, 160), shape_bucket=64, max_plans=2,
+                       lr=1e-4, clipnorm=0.0)
+    for (h, w) in [(150, 200), (130, 170), (100, 250), (150, 200)]:
+        img, gt, cnt, hw = _inputs(1, h, w)
+        gt = gt.clamp(max=float(min(h, w) - 1))
+        loss = nt.train_step(img, gt, cnt, hw)
+        assert torch.isfinite(loss).all()
+        assert len(nt._plans) <= 2
+        assert all(k[1] % 64 == 0 and k[2] % 64 == 0 for k in nt._plans)
+    b, s, l = nt.predict(_inputs(1, 90, 140)[0])
+    assert b.shape == (1, 300, 4) and float(b.max()) <= 140.0
