@@ -125,12 +125,16 @@ __global__ void focal_kernel(const __nv_bfloat16* __restrict__ logits, __nv_bflo
                   bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
     float gr[8];
     int j_cached = -1, st = 0, cid = 0;
+    int j = (g * 8) / K, k = g * 8 - j * K - 1;   // one division per thread; (j, k) then advance incrementally
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int ch = g * 8 + e;
       gr[e] = 0.f;
+      if (++k == K) {
+        k = 0;
+        ++j;
+      }
       if (ch >= 9 * K) continue;
-      const int j = ch / K, k = ch - j * K;
       if (j != j_cached) {
         const long long t = static_cast<long long>(b) * A_total + a_off + p * 9 + j;
         st = state[t];
@@ -140,9 +144,12 @@ __global__ void focal_kernel(const __nv_bfloat16* __restrict__ logits, __nv_bflo
       if (st < 0) continue;
       const bool pos = (st == 1) && (cid == k);
       const float xv = x[e];
-      const float pr = 1.f / (1.f + __expf(-xv));
-      const float sp_pos = softplus(xv);    // -log(1-p)
-      const float sp_neg = sp_pos - xv;     // -log(p)
+      // one exp shared by sigmoid and softplus: e = exp(-|x|)
+      const float ex = __expf(-fabsf(xv));
+      const float inv = __frcp_rn(1.f + ex);
+      const float pr = xv >= 0.f ? inv : ex * inv;
+      const float sp_pos = fmaxf(xv, 0.f) + __logf(1.f + ex);   // -log(1-p)
+      const float sp_neg = sp_pos - xv;                          // -log(p)
       float l, d;
       if (gamma == 2.f) {
         if (pos) {
