@@ -20,8 +20,8 @@ namespace b200 {
 constexpr int kStemKB = 4;                       // K blocks of 64
 constexpr int kStemABytes = kStemKB * 128 * 128; // 64 KB per stage
 constexpr int kStemBBytes = kStemKB * 64 * 128;  // 32 KB, resident
-constexpr int kStemStages = 2;
-constexpr int kStemThreads = 384;                // w0 MMA, w1 TMEM alloc, w4-7 epilogue, w8-11 producers
+constexpr int kStemStages = 3;
+constexpr int kStemThreads = 512;                // w0 MMA, w1 TMEM alloc, w4-7 epilogue, w8-15 producers
 constexpr int kStemSmem = kStemStages * kStemABytes + kStemBBytes + 1024 + 128;
 
 struct StemParams {
@@ -42,10 +42,10 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_conv_kernel(const StemPa
   const uint32_t b_smem = smem_base + kStemStages * kStemABytes;
   const uint32_t bar_base = b_smem + kStemBBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (2 + s); };
-  auto tfull_bar = [&](int a) { return bar_base + 8u * (4 + a); };
-  auto tempty_bar = [&](int a) { return bar_base + 8u * (6 + a); };
-  const uint32_t tmem_ptr_smem = bar_base + 64;
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStemStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStemStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStemStages + 2 + a); };
+  const uint32_t tmem_ptr_smem = bar_base + 96;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -61,9 +61,11 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_conv_kernel(const StemPa
     *reinterpret_cast<uint4*>(smem_gen + kStemStages * kStemABytes + kb * 8192 + row * 128 + ((ch ^ (row & 7)) << 4)) = v;
   }
   if (warp == 0 && lane == 0) {
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(full_bar(s), 128);
+    for (int s = 0; s < kStemStages; ++s) {
+      mbar_init(full_bar(s), 256);
       mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
       mbar_init(tempty_bar(s), 128);
     }
@@ -90,7 +92,9 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_conv_kernel(const StemPa
 
   if (warp >= 8) {
     // ---------------------------------------------------------------- producers: gather the A tile
-    const int m = (warp - 8) * 32 + lane;
+    const int t = (warp - 8) * 32 + lane;          // 256 gather threads: (pixel m, half of the filter rows)
+    const int m = t & 127, part = t >> 7;
+    const int r_lo = part ? 4 : 0, r_hi = part ? 7 : 4;
     int stage = 0;
     uint32_t phase = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -100,19 +104,31 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_conv_kernel(const StemPa
       mbar_wait(empty_bar(stage), phase ^ 1);
       uint8_t* a_row = smem_gen + stage * kStemABytes + m * 128;
       const int sw = m & 7;
+      // all loads of this thread's rows first (28 in flight), then the swizzled stores
+      uint2 v[4][7];
 #pragma unroll
-      for (int r = 0; r < 7; ++r) {
+      for (int rr = 0; rr < 4; ++rr) {
+        const int r = r_lo + rr;
         const int iy = 2 * oy + r - 3;
-        const bool row_ok = iy >= 0 && iy < p.H;
+        const bool row_ok = r < r_hi && iy >= 0 && iy < p.H;
         const __nv_bfloat16* src = p.x + (static_cast<long long>(n) * p.H + (row_ok ? iy : 0)) * p.W * 4;
 #pragma unroll
         for (int s = 0; s < 7; ++s) {
           const int ix = 2 * ox + s - 3;
-          uint2 v = make_uint2(0u, 0u);
-          if (row_ok && ix >= 0 && ix < p.W) v = __ldg(reinterpret_cast<const uint2*>(src + static_cast<long long>(ix) * 4));
-          const int kbyte = (r * 28 + s * 4) * 2;          // byte offset of this piece inside the K axis
-          const int kb = kbyte >> 7, within = kbyte & 127;
-          *reinterpret_cast<uint2*>(a_row + kb * 16384 + (((within >> 4) ^ sw) << 4) + (within & 15)) = v;
+          v[rr][s] = make_uint2(0u, 0u);
+          if (row_ok && ix >= 0 && ix < p.W) v[rr][s] = __ldg(reinterpret_cast<const uint2*>(src + static_cast<long long>(ix) * 4));
+        }
+      }
+#pragma unroll
+      for (int rr = 0; rr < 4; ++rr) {
+        const int r = r_lo + rr;
+        if (r < r_hi) {
+#pragma unroll
+          for (int s = 0; s < 7; ++s) {
+            const int kbyte = (r * 28 + s * 4) * 2;          // byte offset of this piece inside the K axis
+            const int kb = kbyte >> 7, within = kbyte & 127;
+            *reinterpret_cast<uint2*>(a_row + kb * 16384 + (((within >> 4) ^ sw) << 4) + (within & 15)) = v[rr][s];
+          }
         }
       }
       fence_async_smem();   // generic-proxy stores -> visible to the tensor core (async proxy)
@@ -235,7 +251,7 @@ namespace b200 {
 constexpr int kSwStages = 3;
 constexpr int kSwAStage = 2 * 8192;   // chunk 0 = dY [64 px][64 co]; chunk 1 stays zero (co 64..127)
 constexpr int kSwBStage = 4 * 8192;   // [64 px][256 k] as four 64-column chunks
-constexpr int kSwThreads = 384;       // w0 TMA+MMA, w1 TMEM alloc, w4-7 epilogue, w8-11 producers
+constexpr int kSwThreads = 512;       // w0 TMA+MMA, w1 TMEM alloc, w4-7 epilogue, w8-15 producers
 constexpr int kSwSmem = kSwStages * (kSwAStage + kSwBStage) + 1024 + 128;
 
 struct StemWgradParams {
@@ -265,7 +281,7 @@ __global__ void __launch_bounds__(kSwThreads, 1) stem_wgrad_kernel(const __grid_
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.dy_map);
     for (int s = 0; s < kSwStages; ++s) {
-      mbar_init(full_bar(s), 129);   // 128 gather threads + the TMA issuer
+      mbar_init(full_bar(s), 257);   // 256 gather threads + the TMA issuer
       mbar_init(empty_bar(s), 1);
     }
     mbar_init(tfull_bar, 1);
@@ -294,8 +310,8 @@ __global__ void __launch_bounds__(kSwThreads, 1) stem_wgrad_kernel(const __grid_
   if (warp >= 8) {
     // gather: thread -> (pixel m, half of the filter rows)
     const int t = (warp - 8) * 32 + lane;
-    const int m = t & 63, part = t >> 6;
-    const int r_lo = part ? 4 : 0, r_hi = part ? 7 : 4;
+    const int m = t & 63, part = t >> 6;            // 4 parts: filter rows {0,1} {2,3} {4,5} {6}
+    const int r_lo = part * 2, r_hi = part == 3 ? 7 : part * 2 + 2;
     int stage = 0;
     uint32_t phase = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -306,18 +322,30 @@ __global__ void __launch_bounds__(kSwThreads, 1) stem_wgrad_kernel(const __grid_
       mbar_wait(empty_bar(stage), phase ^ 1);
       uint8_t* b_row = smem_gen + kSwStages * kSwAStage + stage * kSwBStage + m * 128;
       const int sw = m & 7;
-      for (int r = r_lo; r < r_hi; ++r) {
+      uint2 v[2][7];                                // both rows' loads in flight before the first store
+#pragma unroll
+      for (int rr = 0; rr < 2; ++rr) {
+        const int r = r_lo + rr;
         const int iy = 2 * oy + r - 3;
-        const bool row_ok = pix_ok && iy >= 0 && iy < p.H;
+        const bool row_ok = r < r_hi && pix_ok && iy >= 0 && iy < p.H;
         const __nv_bfloat16* src = p.x + (static_cast<long long>(n) * p.H + (row_ok ? iy : 0)) * p.W * 4;
 #pragma unroll
         for (int s = 0; s < 7; ++s) {
           const int ix = 2 * ox + s - 3;
-          uint2 v = make_uint2(0u, 0u);
-          if (row_ok && ix >= 0 && ix < p.W) v = __ldg(reinterpret_cast<const uint2*>(src + static_cast<long long>(ix) * 4));
-          const int kbyte = (r * 28 + s * 4) * 2;
-          const int kb = kbyte >> 7, within = kbyte & 127;
-          *reinterpret_cast<uint2*>(b_row + kb * 8192 + (((within >> 4) ^ sw) << 4) + (within & 15)) = v;
+          v[rr][s] = make_uint2(0u, 0u);
+          if (row_ok && ix >= 0 && ix < p.W) v[rr][s] = __ldg(reinterpret_cast<const uint2*>(src + static_cast<long long>(ix) * 4));
+        }
+      }
+#pragma unroll
+      for (int rr = 0; rr < 2; ++rr) {
+        const int r = r_lo + rr;
+        if (r < r_hi) {
+#pragma unroll
+          for (int s = 0; s < 7; ++s) {
+            const int kbyte = (r * 28 + s * 4) * 2;
+            const int kb = kbyte >> 7, within = kbyte & 127;
+            *reinterpret_cast<uint2*>(b_row + kb * 8192 + (((within >> 4) ^ sw) << 4) + (within & 15)) = v[rr][s];
+          }
         }
       }
       fence_async_smem();
