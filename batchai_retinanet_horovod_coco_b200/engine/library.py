@@ -81,19 +81,20 @@ class LibraryTrainer:
         self.mean = torch.tensor(CAFFE_MEAN_BGR, device=self.device).view(1, 3, 1, 1)
         self._anchors = {}
 
-    def anchors(self, hw):
+    def anchors(self, hw, feature_shapes=None):
         if hw not in self._anchors:
-            self._anchors[hw] = anchor_ops.anchors_for_shape(hw).to(self.device)
+            self._anchors[hw] = anchor_ops.anchors_for_shape(hw, feature_shapes=feature_shapes).to(self.device)
         return self._anchors[hw]
 
     def loss(self, images_u8: torch.Tensor, gt: torch.Tensor, gt_count: torch.Tensor, img_hw: torch.Tensor):
-        x = images_u8.permute(0, 3, 1, 2).float() - self.mean
+        x = images_u8.permute(0, 3, 1, 2).float()
+        x = x / 127.5 - 1.0 if getattr(self.model, "preprocess_mode", "caffe") == "tf" else x - self.mean
         if self.device.type == "cuda":
             x = x.contiguous(memory_format=torch.channels_last)
         with torch.autocast(self.device.type, dtype=self.dtype, enabled=self.dtype != torch.float32):
             out = self.train_model(x)
         h, w = images_u8.shape[1:3]
-        anchors = self.anchors((h, w))
+        anchors = self.anchors((h, w), out["feature_shapes"])
         with torch.no_grad():
             state, cls, reg_t = assign_targets_batched(anchors, gt, gt_count, img_hw)
         npos = (state == 1).sum()

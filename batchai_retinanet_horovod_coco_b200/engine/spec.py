@@ -50,7 +50,10 @@ class SpecTrainer:
 
     # ---- steps --------------------------------------------------------------------------------
     def _prep(self, images_u8):
-        return images_u8.to(self.device).permute(0, 3, 1, 2).float() - self.mean
+        x = images_u8.to(self.device).permute(0, 3, 1, 2).float()
+        if getattr(self.model, "preprocess_mode", "caffe") == "tf":
+            return x / 127.5 - 1.0      # keras-retinanet preprocess_image(mode='tf'): mobilenet / densenet
+        return x - self.mean
 
     def train_step(self, images_u8, gt, gt_count, img_hw):
         dev = self.device
@@ -59,7 +62,8 @@ class SpecTrainer:
         out = self.model(x)
         hw = tuple(images_u8.shape[1:3])
         if hw not in self._anchors:
-            self._anchors[hw] = anchor_ops.anchors_for_shape(hw).to(dev)
+            # pyramid shapes come from the tensors (VGG / DenseNet pools floor, ResNet ceils)
+            self._anchors[hw] = anchor_ops.anchors_for_shape(hw, feature_shapes=out["feature_shapes"]).to(dev)
         with torch.no_grad():
             state, cls, reg_t = assign_targets_batched(self._anchors[hw], gt.to(dev).float(), gt_count.to(dev),
                                                        img_hw.to(dev))

@@ -115,8 +115,11 @@ class NativeTrainer:
 
     # ------------------------------------------------------------------ structure
     def _build_layers(self):
-        m = self.model
-        bb = m.backbone
+        self.convs = self._build_top() + self._build_backbone()
+
+    def _build_backbone(self):
+        """ResNet convs in backward-completion order (stages 5..2, then the stem)."""
+        bb = self.model.backbone
         self.stem = Conv("conv1", bb.conv1, bb.bn_conv1, stride=2)
         self.blocks = []  # list of stages, each a list of dicts
         for stage in bb.stages:
@@ -129,6 +132,16 @@ class NativeTrainer:
                      "stride": blk.stride}
                 st.append(d)
             self.blocks.append(st)
+        order = []
+        for st in self.blocks[::-1]:
+            for d in st[::-1]:
+                order += [d["c"], d["b"], d["a"]] + ([d["s"]] if d["s"] is not None else [])
+        order.append(self.stem)
+        return order
+
+    def _build_top(self):
+        """FPN + heads in backward-completion order."""
+        m = self.model
         f = m.fpn
         self.fpn = {n: Conv(n, getattr(f, n), stride=(2 if n in ("P6", "P7") else 1), same=n in ("P6", "P7"))
                     for n in f.LAYER_ORDER}
@@ -136,14 +149,16 @@ class NativeTrainer:
         self.reg_out = Conv("pyramid_regression", m.regression_submodel.out)
         self.cls_tower = [Conv(f"pyramid_classification_{i}", c) for i, c in enumerate(m.classification_submodel.tower)]
         self.cls_out = Conv("pyramid_classification", m.classification_submodel.out)
-        # backward-completion order: heads, FPN, backbone stages 5..2, stem
         order = [self.cls_out] + self.cls_tower[::-1] + [self.reg_out] + self.reg_tower[::-1]
         order += [self.fpn[n] for n in ("P7", "P6", "P3", "C3_reduced", "P4", "C4_reduced", "P5", "C5_reduced")]
-        for st in self.blocks[::-1]:
-            for d in st[::-1]:
-                order += [d["c"], d["b"], d["a"]] + ([d["s"]] if d["s"] is not None else [])
-        order.append(self.stem)
-        self.convs = order
+        return order
+
+    # hooks for engines that keep part of the model outside the conv table (engine/hybrid.py)
+    def _alloc_extra(self, off: int, trainable: bool) -> int:
+        return off
+
+    def _bind_extra(self):
+        pass
 
     def _alloc_params(self):
         dev = self.device
@@ -156,6 +171,7 @@ class NativeTrainer:
             if c.has_bias:
                 c.b_off = off
                 off = _align4(off + c.cout)
+        off = self._alloc_extra(off, True)
         self.n_train = off
         for c in self.convs:
             if c.trainable:
@@ -165,6 +181,7 @@ class NativeTrainer:
             if c.has_bias:
                 c.b_off = off
                 off = _align4(off + c.cout)
+        off = self._alloc_extra(off, False)
         self.n_params = off
         pad = 64
         self.P = torch.zeros(off + pad, device=dev)
@@ -201,6 +218,7 @@ class NativeTrainer:
         self.npos = torch.zeros(1, dtype=torch.int32, device=dev)
         self.ones64 = torch.ones(64, device=dev)
         self.zeros64 = torch.zeros(64, device=dev)
+        self._bind_extra()
 
     # ------------------------------------------------------------------ parameter import / export
     @torch.no_grad()
@@ -230,6 +248,8 @@ class NativeTrainer:
         TMA-fed conv plus a gather for the stem's packed [64][256] filter."""
         self.wtable.run()
         s = self.stem
+        if s is None:
+            return
         if not hasattr(self, "_stem_idx"):
             # packed k = r*28 + s*4 + c  <-  master (tap = r*7 + s, co, ci); padding entries read a zero slot
             k = torch.arange(256, device=self.device)
@@ -247,19 +267,9 @@ class NativeTrainer:
         return {"iterations": self.iterations, "lr": self.lr, "M": self.M, "V": self.V}
 
     # ------------------------------------------------------------------ per-shape plan
-    def _plan(self, B, H, W):
-        key = (B, H, W)
-        if key in self._plans:
-            self._plans[key] = self._plans.pop(key)   # most recently used last
-            return self._plans[key]
-        while len(self._plans) >= self.max_plans:
-            self._plans.pop(next(iter(self._plans)))  # evict the least recently used plan
+    def _plan_backbone(self, p, B, H, W, buf):
+        """Backbone activations and gradient buffers; returns the (h, w) of C3, C4, C5."""
         dev = self.device
-        p = {}
-
-        def buf(h, w, c, zero=False):
-            return (torch.zeros if zero else torch.empty)(B, h, w, c, device=dev, dtype=BF16)
-
         p["img"] = torch.empty(B, H, W, 4, device=dev, dtype=BF16)   # 4th channel is zero padding
         h1, w1 = -(-H // 2), -(-W // 2)
         p["stem_raw_hw"] = (h1, w1)
@@ -283,7 +293,32 @@ class NativeTrainer:
                 hh, ww = ho, wo
             acts.append(sacts)
         p["acts"] = acts
-        c3hw, c4hw, c5hw = acts[1][-1]["hw"], acts[2][-1]["hw"], acts[3][-1]["hw"]
+        # backbone gradient buffers, sized per stage
+        gb = []
+        for si, st in enumerate(self.blocks):
+            a0 = acts[si][0]
+            f = st[0]["a"].cout
+            ho, wo = a0["hw"]
+            gb.append({"g": buf(ho, wo, f * 4), "ga": buf(ho, wo, f), "gb": buf(ho, wo, f),
+                       "gx": buf(*a0["in_hw"], st[0]["a"].cin), "tmp": buf(*a0["in_hw"], st[0]["a"].cin)})
+        p["gb"] = gb
+        p["dstem"] = torch.empty(B, h1, w1, 64, device=dev, dtype=BF16)
+        return acts[1][-1]["hw"], acts[2][-1]["hw"], acts[3][-1]["hw"]
+
+    def _plan(self, B, H, W):
+        key = (B, H, W)
+        if key in self._plans:
+            self._plans[key] = self._plans.pop(key)   # most recently used last
+            return self._plans[key]
+        while len(self._plans) >= self.max_plans:
+            self._plans.pop(next(iter(self._plans)))  # evict the least recently used plan
+        dev = self.device
+        p = {}
+
+        def buf(h, w, c, zero=False):
+            return (torch.zeros if zero else torch.empty)(B, h, w, c, device=dev, dtype=BF16)
+
+        c3hw, c4hw, c5hw = self._plan_backbone(p, B, H, W, buf)
         p6hw = (-(-c5hw[0] // 2), -(-c5hw[1] // 2))
         p7hw = (-(-p6hw[0] // 2), -(-p6hw[1] // 2))
         lv = [c3hw, c4hw, c5hw, p6hw, p7hw]
@@ -302,16 +337,6 @@ class NativeTrainer:
         p["dt"] = [[buf(h, w, 256) for (h, w) in lv] for _ in range(2)]
         p["dP"] = [buf(h, w, 256) for (h, w) in lv]
         p["dfpn"] = {"m3": buf(*c3hw, 256), "m4": buf(*c4hw, 256), "c5r": buf(*c5hw, 256), "p6": buf(*p6hw, 256)}
-        # backbone gradient buffers, sized per stage
-        gb = []
-        for si, st in enumerate(self.blocks):
-            a0 = acts[si][0]
-            f = st[0]["a"].cout
-            ho, wo = a0["hw"]
-            gb.append({"g": buf(ho, wo, f * 4), "ga": buf(ho, wo, f), "gb": buf(ho, wo, f),
-                       "gx": buf(*a0["in_hw"], st[0]["a"].cin), "tmp": buf(*a0["in_hw"], st[0]["a"].cin)})
-        p["gb"] = gb
-        p["dstem"] = torch.empty(B, h1, w1, 64, device=dev, dtype=BF16)
         # anchors + targets
         p["anchors"] = native.anchors_for_shape_gpu(lv, dev)
         A = p["anchors"].shape[0]
@@ -368,7 +393,11 @@ class NativeTrainer:
 
     # ------------------------------------------------------------------ forward
     def _forward(self, p, images_u8, img_hw=None):
-        B, H, W, _ = images_u8.shape
+        p["C"] = self._forward_backbone(p, images_u8, img_hw)
+        self._forward_top(p, *p["C"])
+
+    def _forward_backbone(self, p, images_u8, img_hw=None):
+        """Pixels -> (C3, C4, C5) NHWC bf16."""
         native.preprocess(images_u8, p["img"], CAFFE_MEAN_BGR, img_hw)
         native.stem_conv(p["img"], self.stem_wp, self.stem.shift, p["stem_out"])     # conv + BN + ReLU
         native.bn_relu_maxpool_fwd(p["stem_out"], self.ones64, self.zeros64, p["pool"], p["pool_idx"], *p["pool_pad"])
@@ -387,7 +416,10 @@ class NativeTrainer:
                 a["x"] = x
                 x = a["o"]
         self._mark("fwd_backbone")
-        c3, c4, c5 = p["acts"][1][-1]["o"], p["acts"][2][-1]["o"], p["acts"][3][-1]["o"]
+        return p["acts"][1][-1]["o"], p["acts"][2][-1]["o"], p["acts"][3][-1]["o"]
+
+    def _forward_top(self, p, c3, c4, c5):
+        """FPN + the two shared heads over five levels."""
         fp, f = p["fpn"], self.fpn
         P3, P4, P5, P6, P7 = fp["P"]
         self._fprop(f["C5_reduced"], c5, fp["c5r"])
@@ -444,7 +476,7 @@ class NativeTrainer:
         self._mark("bwd_heads")
         dP3, dP4, dP5, dP6, dP7 = dP
         df = p["dfpn"]
-        c3, c4, c5 = p["acts"][1][-1]["o"], p["acts"][2][-1]["o"], p["acts"][3][-1]["o"]
+        c3, c4, c5 = p["C"]
         P6 = feats[3]
         # P7 = conv(relu(P6)); P6 also feeds the heads directly
         self._wgrad(f["P7"], [fp["r6"]], [dP7])
@@ -465,8 +497,12 @@ class NativeTrainer:
         native.upsample_bwd_add(df["m4"], df["c5r"])
         self._wgrad(f["C5_reduced"], [c5], [df["c5r"]])
         self._mark("bwd_fpn")
-        if self.freeze_backbone:
-            return
+        if not self.freeze_backbone:
+            self._backward_backbone(p)
+
+    def _backward_backbone(self, p):
+        fp, f, df = p["fpn"], self.fpn, p["dfpn"]
+        c3, c4, c5 = p["C"]
         gb = p["gb"]
         # gradient w.r.t. C5 / C4 / C3 from the FPN (masked by the ReLU of the block output)
         g5 = gb[3]["g"]
@@ -524,6 +560,7 @@ class NativeTrainer:
         rank start from rank 0's state (Horovod BroadcastGlobalVariablesCallback(0), train.py:111)."""
         self.G = self.comm.symmetric_bucket(self.n_train + 64)
         self.Gavg = self.comm.result[:self.G.numel()]   # peer-writable: the allreduce pushes results into it
+        self._bind_extra()
         self.broadcast_state(0)
 
     def broadcast_state(self, root: int = 0):
@@ -571,6 +608,10 @@ class NativeTrainer:
         self._prof = None
         return out
 
+    def _pad_bgr(self):
+        """uint8 colour that preprocesses to (about) zero, the value the reference pads batches with."""
+        return (104, 117, 124) if getattr(self.model, "preprocess_mode", "caffe") == "caffe" else (127, 127, 127)
+
     def _bucket(self, images_u8):
         """Pad H, W up to a multiple of ``shape_bucket`` with the mean colour (zero after preprocessing).
         Anchors whose centre falls in the padding are ignored through ``img_hw`` exactly as for the
@@ -581,7 +622,7 @@ class NativeTrainer:
         if (Hp, Wp) == (H, W):
             return images_u8
         out = torch.empty(images_u8.shape[0], Hp, Wp, 3, dtype=torch.uint8, device=images_u8.device)
-        out[..., 0], out[..., 1], out[..., 2] = 104, 117, 124
+        out[..., 0], out[..., 1], out[..., 2] = self._pad_bgr()
         out[:, :H, :W] = images_u8
         return out
 

@@ -57,19 +57,77 @@ class Backbone:
         if self.backbone not in BLOCKS:
             raise ValueError(f"Backbone ('{self.backbone}') not in allowed backbones ({sorted(BLOCKS)}).")
 
+    def preprocess_image(self, x):
+        """caffe mode: BGR mean subtraction (keras-retinanet ``preprocess_image``)."""
+        from ..utils.image import preprocess_image
+        return preprocess_image(x, mode="caffe")
 
-class UnsupportedBackbone(Backbone):
+
+class VGGBackbone(Backbone):
     def validate(self):
-        raise NotImplementedError(
-            f"Backbone '{self.backbone}' is recognised by the reference CLI (train.py:323-324 warns it is "
-            f"experimental) but only resnet50/101/152 are implemented here.")
+        from .vgg import VGG_CFG
+        if self.backbone not in VGG_CFG:
+            raise ValueError(f"Backbone ('{self.backbone}') not in allowed backbones ({sorted(VGG_CFG)}).")
+
+    def download_imagenet(self):
+        return _local_weights(f"{self.backbone}_weights_tf_dim_ordering_tf_kernels_notop.h5")
+
+
+class MobileNetBackbone(Backbone):
+    def validate(self):
+        from .mobilenet import ALLOWED
+        if self.backbone not in ALLOWED:
+            raise ValueError(f"Backbone ('{self.backbone}') not in allowed backbones ({ALLOWED}).")
+
+    def download_imagenet(self):
+        res, alpha = self.backbone[len("mobilenet"):].split("_")
+        a = {"1.0": "1_0", "0.75": "7_5", "0.5": "5_0", "0.25": "2_5"}[alpha]
+        return _local_weights(f"mobilenet_{a}_{res}_tf_no_top.h5")
+
+    def preprocess_image(self, x):
+        from ..utils.image import preprocess_image
+        return preprocess_image(x, mode="tf")
+
+
+class DenseNetBackbone(Backbone):
+    def validate(self):
+        from .densenet import DENSENET_BLOCKS
+        if self.backbone not in DENSENET_BLOCKS:
+            raise ValueError(f"Backbone ('{self.backbone}') not in allowed backbones ({sorted(DENSENET_BLOCKS)}).")
+
+    def download_imagenet(self):
+        return _local_weights(f"{self.backbone}_weights_tf_dim_ordering_tf_kernels_notop.h5")
+
+    def preprocess_image(self, x):
+        from ..utils.image import preprocess_image
+        return preprocess_image(x, mode="tf")
+
+
+def _local_weights(fname: str):
+    """Keras ``get_file`` without the network: ``$RETINANET_IMAGENET_WEIGHTS`` or ``~/.keras/models``."""
+    cands = []
+    env = os.environ.get("RETINANET_IMAGENET_WEIGHTS")
+    if env:
+        cands += [env, os.path.join(env, fname)]
+    cands.append(os.path.join(os.path.expanduser("~"), ".keras", "models", fname))
+    for c in cands:
+        if os.path.isfile(c):
+            return c
+    warnings.warn(f"ImageNet weights '{fname}' not found locally and there is no network; continuing with random "
+                  f"initialisation (same as --no-weights). Set RETINANET_IMAGENET_WEIGHTS to use them.")
+    return None
 
 
 def backbone(name: str) -> Backbone:
+    """Dispatch by substring exactly like keras-retinanet (reference ``train.py:43,390``)."""
     if "resnet" in name:
         return Backbone(name)
-    if any(k in name for k in ("mobilenet", "vgg", "densenet")):
-        return UnsupportedBackbone(name)
+    if "mobilenet" in name:
+        return MobileNetBackbone(name)
+    if "vgg" in name:
+        return VGGBackbone(name)
+    if "densenet" in name:
+        return DenseNetBackbone(name)
     raise NotImplementedError(f"Backbone class for '{name}' not implemented.")
 
 

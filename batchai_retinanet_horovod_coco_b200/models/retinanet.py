@@ -29,6 +29,22 @@ import torch.nn.functional as F
 
 from .resnet import ResNet, tf_same_pad
 
+
+def make_backbone(name: str) -> nn.Module:
+    """Backbone module by substring, like keras-retinanet's ``models.backbone`` (reference ``train.py:390``)."""
+    if "resnet" in name:
+        return ResNet(name)
+    if "vgg" in name:
+        from .vgg import VGG
+        return VGG(name)
+    if "mobilenet" in name:
+        from .mobilenet import MobileNet
+        return MobileNet(name)
+    if "densenet" in name:
+        from .densenet import DenseNet
+        return DenseNet(name)
+    raise NotImplementedError(f"Backbone class for '{name}' not implemented.")
+
 NUM_ANCHORS = 9
 FEATURE_SIZE = 256
 PRIOR_PROBABILITY = 0.01
@@ -121,7 +137,8 @@ class RetinaNet(nn.Module):
         self.num_classes = num_classes
         self.backbone_name = backbone
         self.return_logits = return_logits
-        self.backbone = ResNet(backbone)
+        self.backbone = make_backbone(backbone)
+        self.preprocess_mode = getattr(self.backbone, "preprocess_mode", "caffe")
         c2, c3, c4, c5 = self.backbone.out_channels
         self.fpn = FPN(c3, c4, c5)
         self.regression_submodel = SubModel("pyramid_regression", 4)

@@ -19,8 +19,14 @@ def read_image_bgr(path: str) -> np.ndarray:
     return img
 
 
-def preprocess_image(x: np.ndarray) -> np.ndarray:
-    return x.astype(np.float32) - CAFFE_MEAN_BGR
+def preprocess_image(x: np.ndarray, mode: str = "caffe") -> np.ndarray:
+    """``caffe``: subtract the BGR ImageNet mean (ResNet, VGG); ``tf``: scale to [-1, 1] (MobileNet, DenseNet)."""
+    x = x.astype(np.float32)
+    if mode == "tf":
+        return x / 127.5 - 1.0
+    if mode != "caffe":
+        raise ValueError(f"unknown preprocessing mode '{mode}'")
+    return x - CAFFE_MEAN_BGR
 
 
 def compute_resize_scale(image_shape, min_side=800, max_side=1333) -> float:

@@ -41,6 +41,22 @@ def _layer_groups(model):
     return groups
 
 
+def _is_depthwise(mod) -> bool:
+    return getattr(mod, "groups", 1) > 1 and mod.groups == mod.weight.shape[0]
+
+
+def _to_keras_layout(wname: str, arr):
+    if arr.ndim != 4:
+        return arr
+    return arr.transpose(2, 3, 0, 1) if "depthwise_kernel" in wname else arr.transpose(2, 3, 1, 0)
+
+
+def _from_keras_layout(wname: str, arr):
+    if arr.ndim != 4:
+        return arr
+    return arr.transpose(2, 3, 0, 1) if "depthwise_kernel" in wname else arr.transpose(3, 2, 0, 1)
+
+
 def _module_weights(name, mod):
     """[(keras weight name, numpy array in Keras layout, torch tensor)]"""
     out = []
@@ -50,7 +66,10 @@ def _module_weights(name, mod):
             out.append((f"{name}/{k}:0", t.detach().cpu().numpy(), t))
     else:
         w = mod.weight
-        out.append((f"{name}/kernel:0", w.detach().cpu().permute(2, 3, 1, 0).contiguous().numpy(), w))
+        if _is_depthwise(mod):   # Keras DepthwiseConv2D: (kh, kw, channels, multiplier)
+            out.append((f"{name}/depthwise_kernel:0", w.detach().cpu().permute(2, 3, 0, 1).contiguous().numpy(), w))
+        else:
+            out.append((f"{name}/kernel:0", w.detach().cpu().permute(2, 3, 1, 0).contiguous().numpy(), w))
         if mod.bias is not None:
             out.append((f"{name}/bias:0", mod.bias.detach().cpu().numpy(), mod.bias))
     return out
@@ -90,9 +109,7 @@ def trainable_weight_list(model):
     """Keras ``model.trainable_weights`` order: layer order, kernel then bias."""
     out = []
     for name, mod in model.keras_layers().items():
-        if hasattr(mod, "moving_variance"):
-            continue
-        for wname, _, t in _module_weights(name, mod):
+        for wname, _, t in _module_weights(name, mod):   # frozen BN vectors are buffers: requires_grad is False
             if t.requires_grad:
                 out.append((wname, t))
     return out
@@ -128,8 +145,7 @@ def save_model(model, path: str, optimizer_config: dict | None = None, optimizer
                     arr = np.zeros(tuple(t.shape), np.float32) if slot is None else \
                         np.asarray(slot[which].detach().cpu() if isinstance(slot[which], torch.Tensor) else slot[which],
                                    dtype=np.float32)
-                    if arr.ndim == 4:
-                        arr = np.ascontiguousarray(arr.transpose(2, 3, 1, 0))
+                    arr = np.ascontiguousarray(_to_keras_layout(wname, arr))
                     n = "training/Adam/Variable:0" if idx == 0 else f"training/Adam/Variable_{idx}:0"
                     names.append(n.encode())
                     f.write_dataset(f"/optimizer_weights/{n}", arr)
@@ -171,8 +187,8 @@ def load_weights(model, path: str, by_name: bool = True, skip_mismatch: bool = T
                     continue  # by_name: layers absent from the model are ignored
                 arr = f.dataset(f"{gpath}/{wname}")
                 t = None
-                if leaf == "kernel" and hasattr(mod, "weight") and not hasattr(mod, "moving_variance"):
-                    t, arr = mod.weight, arr.transpose(3, 2, 0, 1) if arr.ndim == 4 else arr
+                if leaf in ("kernel", "depthwise_kernel") and hasattr(mod, "weight") and not hasattr(mod, "moving_variance"):
+                    t, arr = mod.weight, _from_keras_layout(leaf, arr)
                 elif leaf == "bias" and getattr(mod, "bias", None) is not None:
                     t = mod.bias
                 elif leaf in ("gamma", "beta", "moving_mean", "moving_variance") and hasattr(mod, leaf):
@@ -229,8 +245,7 @@ def load_full_model(path: str, backbone_name: str = "resnet50", num_classes: int
                 if len(rest) == 2 * len(tw):
                     for i, (wname, t) in enumerate(tw):
                         m, v = rest[i], rest[len(tw) + i]
-                        if m.ndim == 4:
-                            m, v = m.transpose(3, 2, 0, 1), v.transpose(3, 2, 0, 1)
+                        m, v = _from_keras_layout(wname, m), _from_keras_layout(wname, v)
                         state["slots"][wname] = (torch.from_numpy(np.ascontiguousarray(m)),
                                                  torch.from_numpy(np.ascontiguousarray(v)))
     load_weights(model, path, by_name=True, skip_mismatch=False, verbose=False)

@@ -1,0 +1,100 @@
+"""HybridTrainer (non-ResNet backbone through autograd, everything else on the native kernels) vs the
+PyTorch spec model + autograd in fp32."""
+import copy
+
+import pytest
+import torch
+
+from batchai_retinanet_horovod_coco_b200 import models
+from test_gpu_engine import _cos, _inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def _model(name, K=80):
+    torch.manual_seed(0)
+    m = models.backbone(name).retinanet(K)
+    with torch.no_grad():
+        for sm in (m.regression_submodel, m.classification_submodel):
+            for c in list(sm.tower) + [sm.out]:
+                c.weight.normal_(0, 0.03)
+    return m
+
+
+@pytest.mark.parametrize("name", ["vgg16", "mobilenet224_0.5", "densenet121"])
+def test_hybrid_matches_autograd(name):
+    from batchai_retinanet_horovod_coco_b200.engine import create_trainer
+    from batchai_retinanet_horovod_coco_b200.engine.hybrid import HybridTrainer
+    from batchai_retinanet_horovod_coco_b200.engine.library import LibraryTrainer
+    from batchai_retinanet_horovod_coco_b200.utils import keras_h5
+    B, H, W = 2, 160, 224
+    model = _model(name)
+    ref_model = copy.deepcopy(model)
+    img, gt, cnt, hw = _inputs(B, H, W)
+
+    assert isinstance(create_trainer(copy.deepcopy(model), "cuda", batch=B, image_hw=(H, W)), HybridTrainer)
+    ht = HybridTrainer(model=model, device="cuda", batch=B, image_hw=(H, W), shape_bucket=1)   # exact shapes
+    loss_h, _ = ht.forward_loss(img, gt, cnt, hw)
+    torch.cuda.synchronize()
+    grads = ht.gradients_by_layer()
+
+    # batch-statistics BN on tiny maps amplifies bf16 rounding, so BN backbones are compared with the same
+    # autocast precision on the reference side (the backbone maths is then identical); VGG against fp32
+    lib = LibraryTrainer(model=ref_model, device="cuda", dtype=torch.float32 if name.startswith("vgg") else torch.bfloat16)
+    ref_model.train()
+    total, lc, lr_ = lib.loss(img.cuda(), gt.cuda(), cnt.cuda(), hw.cuda())
+    total.backward()
+    ref = torch.stack([total, lr_, lc]).detach()
+    rel = ((loss_h - ref).abs() / ref.abs().clamp(min=1e-6)).max().item()
+    assert rel < 5e-2, f"loss mismatch hybrid {loss_h.tolist()} vs ref {ref.tolist()}"
+
+    # heads + FPN come from the native kernels, backbone tensors from autograd into views of the flat bucket
+    bad, seen_backbone = [], 0
+    top = set(ref_model.fpn.keras_layers()) | set(ref_model.regression_submodel.keras_layers()) | \
+        set(ref_model.classification_submodel.keras_layers())
+    for lname, mod in ref_model.keras_layers().items():
+        if lname in top:
+            gw, gb = grads[lname]
+            if _cos(gw, mod.weight.grad) < 0.97:
+                bad.append((lname, round(_cos(gw, mod.weight.grad), 4)))
+            if _cos(gb, mod.bias.grad) < 0.97:
+                bad.append((lname + "/bias", round(_cos(gb, mod.bias.grad), 4)))
+    for wname, t in keras_h5.trainable_weight_list(ref_model):
+        if wname.split("/")[0] in top or wname.rsplit("/", 1)[0] in top:
+            continue
+        seen_backbone += 1
+        g = grads[wname][0]
+        assert g.shape == t.grad.shape
+        if t.grad.norm() > 1e-12 and _cos(g, t.grad) < 0.9:
+            bad.append((wname, round(_cos(g, t.grad), 4)))
+    assert seen_backbone > 10
+    assert len(bad) <= seen_backbone // 20, f"gradient mismatches: {bad[:20]} ({len(bad)} total)"
+
+
+def test_hybrid_train_predict_and_checkpoint(tmp_path):
+    from batchai_retinanet_horovod_coco_b200.engine import create_trainer
+    from batchai_retinanet_horovod_coco_b200.utils import keras_h5
+    B, H, W = 2, 128, 192
+    model = _model("mobilenet224_0.25", K=5)
+    tr = create_trainer(model, "cuda", lr=1e-4, clipnorm=0.0, batch=B, image_hw=(H, W))
+    img, gt, cnt, hw = _inputs(B, H, W)
+    gt[..., 4] = gt[..., 4] % 5
+    mm0 = model.backbone.conv1_bn.moving_mean.clone()
+    losses = [tr.train_step(img, gt, cnt, hw)[0].item() for _ in range(10)]
+    assert all(l == l for l in losses) and losses[-1] < losses[0], losses
+    assert not torch.equal(mm0, model.backbone.conv1_bn.moving_mean)       # trainable BN updates its statistics
+    b, s, l = tr.predict(img)
+    assert b.shape == (B, 300, 4)
+    # backbone parameters are views of the flat master buffer, Adam slots are exported under Keras names
+    prm = model.backbone.conv1.weight
+    assert prm.data_ptr() >= tr.P.data_ptr() and prm.data_ptr() < tr.P.data_ptr() + tr.P.numel() * 4
+    path = str(tmp_path / "snap.h5")
+    tr.save(path, epoch=1)
+    m2, state = keras_h5.load_full_model(path)
+    assert state["iterations"] == 10 and "conv1/kernel:0" in state["slots"] and "conv1_bn/gamma:0" in state["slots"]
+    assert torch.allclose(m2.backbone.conv1.weight.cpu(), prm.detach().cpu())
+    tr2 = create_trainer(m2, "cuda", lr=1e-4, clipnorm=0.0, batch=B, image_hw=(H, W))
+    tr2.load_optimizer_state(state)
+    a = tr.train_step(img, gt, cnt, hw)
+    b2 = tr2.train_step(img, gt, cnt, hw)
+    assert torch.allclose(a, b2, rtol=2e-2, atol=1e-3), (a, b2)

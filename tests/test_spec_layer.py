@@ -67,9 +67,13 @@ def test_freeze_backbone(r50):
 def test_backbone_factory():
     assert backbone("resnet101").retinanet(2).backbone_name == "resnet101"
     with pytest.raises(NotImplementedError):
-        backbone("vgg16")
+        backbone("inception")
     with pytest.raises(ValueError):
         backbone("resnet18")
+    with pytest.raises(ValueError):
+        backbone("vgg11")
+    with pytest.raises(ValueError):
+        backbone("mobilenet224_0.3")
 
 
 def test_generate_anchors_fixture():

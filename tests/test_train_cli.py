@@ -157,3 +157,24 @@ def test_two_rank_cpu_training_run(tmp_path):
     from batchai_retinanet_horovod_coco_b200.utils.keras_h5 import load_full_model
     _, st = load_full_model(str(snap / "checkpoint-03.h5"))
     assert st["iterations"] == 5 and st["epoch"] == 3
+
+
+@pytest.mark.timeout(600)
+def test_experimental_backbone_cli_run(tmp_path):
+    """`--backbone` other than ResNet trains through the same CLI (reference train.py:323-324 only warns)."""
+    import build_native
+    build_native.build()
+    root = write_coco_dataset(str(tmp_path / "coco"), num_images=2, image_hw=(96, 128), classes=3)
+    snap = tmp_path / "snapshots"
+    cmd = [sys.executable, os.path.join(ROOT, "train.py"), "--cpu", "--backbone", "mobilenet128_0.25", "--batch-size", "1",
+           "--image-min-side", "96", "--image-max-side", "128", "--snapshot-path", str(snap), "--steps", "2", "--epochs", "1",
+           "--lr", "1e-4", "coco", root]
+    env = dict(os.environ, OMP_NUM_THREADS="4", PYTHONPATH=ROOT)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=500, cwd=str(tmp_path), env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "experimental backbone" in r.stderr
+    assert "not found locally" in r.stderr          # ImageNet file for this backbone is looked up locally, then skipped
+    from batchai_retinanet_horovod_coco_b200.utils.keras_h5 import load_full_model
+    m, st = load_full_model(str(snap / "checkpoint-01.h5"))
+    assert m.backbone_name == "mobilenet128_0.25" and st["iterations"] == 2
+    assert "conv_dw_1/depthwise_kernel:0" in st["slots"] and "conv_pw_13_bn/gamma:0" in st["slots"]
