@@ -150,9 +150,8 @@ def check_args(parsed_args):
             parsed_args.multi_gpu, parsed_args.snapshot))
     if parsed_args.multi_gpu > 1 and not parsed_args.multi_gpu_force:
         raise ValueError("Multi-GPU support is experimental, use at own risk! Run with --multi-gpu-force if you wish to continue.")
-    if parsed_args.multi_gpu > 1:
-        raise ValueError("--multi-gpu (single-process towers, keras.utils.multi_gpu_model) has no B200 equivalent: "
-                         "use one process per GPU (launcher -np N), which is what this framework is built around.")
+    if parsed_args.multi_gpu > 1 and getattr(parsed_args, "cpu", False):
+        raise ValueError("--multi-gpu needs GPUs; drop --cpu or use the launcher (-np N) for CPU ranks.")
     if "resnet" not in parsed_args.backbone:
         warnings.warn("Using experimental backbone {}. Only resnet50 has been properly tested.".format(parsed_args.backbone))
     return parsed_args
@@ -276,8 +275,17 @@ def main(args=None):
     # Unlike the reference (which reloads a snapshot with a plain, un-distributed optimizer -- SURVEY
     # App. D item 1) the optimizer is always re-wrapped: create_trainer builds the distributed one.
     h, w = args.image_min_side, args.image_max_side
-    trainer = create_trainer(model, device, lr=args.lr, clipnorm=args.clipnorm, batch=args.batch_size, image_hw=(h, w),
-                             freeze_backbone=args.freeze_backbone, engine=args.engine)
+    if args.multi_gpu > 1:
+        # single-process towers (reference train.py:86-89): N native engines in one process, P2P allreduce
+        if hvd.size() > 1:
+            raise ValueError("--multi-gpu towers and multi-process ranks cannot be combined (each rank owns one GPU, "
+                             "reference train.py:71).")
+        from ..engine.multi_tower import MultiTowerTrainer
+        trainer = MultiTowerTrainer(model, args.multi_gpu, lr=args.lr, clipnorm=args.clipnorm, batch=args.batch_size,
+                                    image_hw=(h, w), freeze_backbone=args.freeze_backbone)
+    else:
+        trainer = create_trainer(model, device, lr=args.lr, clipnorm=args.clipnorm, batch=args.batch_size,
+                                 image_hw=(h, w), freeze_backbone=args.freeze_backbone, engine=args.engine)
     if state is not None:
         trainer.load_optimizer_state(state)
     callbacks = create_callbacks(model, model, prediction_model, validation_generator, args)

@@ -60,7 +60,7 @@ class ArHostArgs(C.Structure):
     _fields_ = [("bufs", C.c_void_p * 8), ("flags", C.c_void_p * 8), ("prescale", C.c_void_p * 8),
                 ("outs", C.c_void_p * 8), ("out", C.c_void_p), ("rank", C.c_int), ("world", C.c_int), ("offset", C.c_longlong),
                 ("count", C.c_longlong), ("postscale", C.c_float), ("epoch", C.c_uint32), ("algo", C.c_int),
-                ("max_blocks", C.c_int), ("has_prescale", C.c_int)]
+                ("max_blocks", C.c_int), ("has_prescale", C.c_int), ("external_sync", C.c_int)]
 
 
 def lib_path() -> str:
@@ -432,6 +432,11 @@ def ipc_open_handle(handle: bytes) -> int:
 
 def ipc_close_handle(ptr: int):
     _check(_load().b200_ipc_close_handle(C.c_void_p(ptr)), "ipc_close_handle")
+
+
+def enable_peer_access(device: int, world_local: int):
+    """cudaDeviceEnablePeerAccess from ``device`` (current) to devices 0..world_local-1."""
+    _check(_load().b200_enable_peer_access(int(device), int(world_local)), "enable_peer_access")
 
 
 class RawCudaBuffer:

@@ -41,6 +41,7 @@ class P2PComm:
         self._opened = []
         self.bucket = None
         self.prescale_local = None
+        self.external_sync = False   # LocalP2PComm orders ranks with events instead of in-kernel flags
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -68,15 +69,10 @@ class P2PComm:
         total = self.flag_bytes + SCALARS_BYTES + 8 * nfloats   # bucket + peer-writable result buffer
         with torch.cuda.device(self.device):
             self.base = native.ipc_alloc(total)
-            handle = native.ipc_get_handle(self.base) if self.world > 1 else b""
+            handle = self._export_region(self.base) if self.world > 1 else b""
             handles = self._gather(handle) if self.world > 1 else [handle]
             for r in range(self.world):
-                if r == self.rank:
-                    self.peer_base.append(self.base)
-                else:
-                    p = native.ipc_open_handle(handles[r])
-                    self._opened.append(p)
-                    self.peer_base.append(p)
+                self.peer_base.append(self.base if r == self.rank else self._import_region(handles[r]))
         raw = native.RawCudaBuffer(self.base, total).tensor(self.device)
         self._raw = raw
         off = self.flag_bytes
@@ -87,6 +83,21 @@ class P2PComm:
         torch.cuda.synchronize(self.device)
         self.barrier_host()
         return self.bucket
+
+    def _before_collective(self):
+        pass
+
+    def _after_collective(self):
+        pass
+
+    # how a region travels to the peers: CUDA IPC between processes (LocalP2PComm: plain pointers)
+    def _export_region(self, base: int) -> bytes:
+        return native.ipc_get_handle(base)
+
+    def _import_region(self, blob: bytes) -> int:
+        p = native.ipc_open_handle(blob)
+        self._opened.append(p)
+        return p
 
     def barrier_host(self):
         if self.world > 1:
@@ -109,6 +120,7 @@ class P2PComm:
         a.algo = algo
         a.max_blocks = 0
         a.has_prescale = int(has_prescale)
+        a.external_sync = int(self.external_sync)
         self.epoch = (self.epoch + 4) & 0x7FFFFFFF
         return a
 
@@ -119,7 +131,9 @@ class P2PComm:
         # results can be pushed into every rank's `result` buffer when `out` IS that buffer
         push = out.data_ptr() == self.result.data_ptr()
         a = self._args(out, 0, n4, 1.0 / self.world, prescale, algo, push=push)
+        self._before_collective()
         native.allreduce_host(a)
+        self._after_collective()
 
     def allreduce_sum_(self, t: torch.Tensor, average: bool = False):
         """Generic in-place allreduce of an arbitrary fp32 CUDA tensor, staged through the bucket."""
@@ -134,7 +148,9 @@ class P2PComm:
                 self.bucket[m:m4].zero_()
             tmp = torch.empty(m4, device=self.device, dtype=torch.float32)
             a = self._args(tmp, 0, m4, (1.0 / self.world) if average else 1.0, False, 0)
+            self._before_collective()
             native.allreduce_host(a)
+            self._after_collective()
             flat[done:done + m].copy_(tmp[:m])
             done += m
         return t
@@ -153,7 +169,9 @@ class P2PComm:
                 self.bucket[:m].copy_(flat[done:done + m])
             tmp = torch.empty(m4, device=self.device, dtype=torch.float32)
             a = self._args(tmp, 0, m4, 1.0, False, 0)
+            self._before_collective()
             native.broadcast_host(a, root)
+            self._after_collective()
             if self.rank != root:
                 flat[done:done + m].copy_(tmp[:m])
             done += m
@@ -168,3 +186,76 @@ class P2PComm:
             except Exception:
                 pass
         self._opened = []
+
+
+class LocalGroup:
+    """Control plane for ranks that are threads of ONE process (``--multi-gpu`` towers): a host barrier,
+    an all-gather of byte strings, and the per-rank CUDA events the ranks order their streams with."""
+
+    TIMEOUT_S = 120.0
+
+    def __init__(self, world: int):
+        import threading
+        self.world = world
+        self._barrier = threading.Barrier(world)
+        self._slots = [None] * world
+        self.ev_ready = [None] * world
+        self.ev_done = [None] * world
+
+    def wait(self):
+        self._barrier.wait(timeout=self.TIMEOUT_S)   # BrokenBarrierError if a tower died or is stuck
+
+    def abort(self):
+        self._barrier.abort()
+
+    def gather_fn(self, rank: int):
+        def gather(b: bytes):
+            self._slots[rank] = b
+            self.wait()
+            out = list(self._slots)
+            self.wait()
+            return out
+        return gather
+
+
+class LocalP2PComm(P2PComm):
+    """Same reduce kernels, ranks = GPUs driven by threads of one process.
+
+    * Regions are shared as raw device pointers after ``cudaDeviceEnablePeerAccess`` (a CUDA IPC handle
+      cannot be opened by the process that exported it).
+    * No in-kernel flag barriers: inside one process a kernel spinning on a peer can deadlock against an
+      implicitly synchronising runtime call (allocation, free) issued for that peer.  The ranks order their
+      streams with events instead: record "bucket ready" -> host barrier -> wait on every peer's event ->
+      flag-free one-shot reduce -> record "done" -> host barrier -> wait on every peer's "done" before the
+      bucket may be overwritten.
+    """
+
+    def __init__(self, rank: int, world: int, device, group: LocalGroup):
+        super().__init__(rank, world, device, group.gather_fn(rank))
+        self.group = group
+        self.external_sync = True
+        with torch.cuda.device(self.device):
+            native.enable_peer_access(self.device.index, world)
+            group.ev_ready[rank] = torch.cuda.Event()
+            group.ev_done[rank] = torch.cuda.Event()
+
+    def _export_region(self, base: int) -> bytes:
+        return int(base).to_bytes(8, "little")
+
+    def _import_region(self, blob: bytes) -> int:
+        return int.from_bytes(blob, "little")
+
+    def _sync(self, events):
+        stream = torch.cuda.current_stream(self.device)
+        events[self.rank].record(stream)
+        self.group.wait()                       # every rank has recorded
+        for r in range(self.world):
+            if r != self.rank:
+                stream.wait_event(events[r])
+        self.group.wait()                       # every rank has issued its waits: events may be re-recorded
+
+    def _before_collective(self):
+        self._sync(self.group.ev_ready)
+
+    def _after_collective(self):
+        self._sync(self.group.ev_done)

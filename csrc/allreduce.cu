@@ -32,6 +32,7 @@ struct ArParams {
   float postscale;
   uint32_t epoch;   // base flag value of this call; the call uses epoch+1 .. epoch+3
   int has_prescale;
+  int external_sync;  // no in-kernel flag barriers: the launching streams were ordered by the host
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -46,6 +47,7 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 // Block-level barrier across ranks: block b of every rank meets block b of every other rank.
 // Flag layout per rank: flags[block][peer].
 __device__ __forceinline__ void rank_barrier(const ArParams& p, uint32_t value) {
+  if (p.external_sync) return;
   __syncthreads();
   if (threadIdx.x < p.world) {
     const int peer = threadIdx.x;
@@ -252,6 +254,7 @@ static int fill(ArParams& p, const B200ArHostArgs* a) {
   p.postscale = a->postscale;
   p.epoch = a->epoch;
   p.has_prescale = a->has_prescale;
+  p.external_sync = a->external_sync;
   return 0;
 }
 
@@ -283,6 +286,7 @@ int b200_allreduce_host(const B200ArHostArgs* a, void* stream_) {
   const bool can_push = a->outs[0] != nullptr;
   // measured at 8 GPUs: push is never slower than one-shot (23 vs 25 us at 1 KB, 28 vs 61 us at 256 KB)
   if (algo == 0) algo = can_push ? 3 : ((bytes <= (128 << 10)) ? 1 : 2);
+  if (p.external_sync) algo = 1;   // the multi-phase algorithms need barriers between their phases
   if (algo == 3 && !can_push) return set_error(-1, "allreduce: push algorithm needs peer-mapped output buffers");
   const long long work = (algo == 1) ? n4 : (n4 + p.world - 1) / p.world;
   long long need = (work + kArThreads - 1) / kArThreads;

@@ -56,6 +56,14 @@ int num_sms() {
   return n;
 }
 
+static unsigned long long device_bit() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return 1ull << (dev & 63);
+}
+bool device_needs_setup(const std::atomic<unsigned long long>& mask) { return !(mask.load() & device_bit()); }
+void device_setup_done(std::atomic<unsigned long long>& mask) { mask.fetch_or(device_bit()); }
+
 }  // namespace b200
 
 extern "C" {

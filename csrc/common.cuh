@@ -45,4 +45,11 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const unsigned lo
 
 int num_sms();
 
+// Per-DEVICE one-time set-up (function attributes such as the dynamic shared-memory limit live in the
+// device's context, and one process may drive several GPUs: engine/multi_tower.py).  Usage:
+//   static std::atomic<unsigned long long> done{0};
+//   if (device_needs_setup(done)) { ...cudaFuncSetAttribute...; device_setup_done(done); }
+bool device_needs_setup(const std::atomic<unsigned long long>& mask);
+void device_setup_done(std::atomic<unsigned long long>& mask);
+
 }  // namespace b200

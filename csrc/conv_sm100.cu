@@ -427,13 +427,13 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   if ((a->ldi % 8) || (a->ldw % 8) || (a->ldo % 8)) return set_error(-1, "b200_conv: ld* must be multiples of 8");
 
   if (a->out_fp32) return set_error(-1, "b200_conv: fp32 output is not supported (bf16 activations only)");
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_set{0};   // per device
+  if (device_needs_setup(attr_set)) {
     B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr_set = true;
+    device_setup_done(attr_set);
   }
   const bool has_add = a->prob[0].add != nullptr, has_mask = a->prob[0].mask != nullptr;
   for (int i = 1; i < a->num_problems; ++i)

@@ -332,10 +332,10 @@ int b200_nms_sorted(const float* boxes, const int* cls_or_null, int n, float thr
   nms_mask_kernel<<<mgrid, 64, 0, stream>>>(boxes, cls_or_null, nullptr, n, 0, n, thr, mask_ws, words);
   int rc = check_launch("nms_mask_kernel");
   if (rc) return rc;
-  static bool attr = false;
-  if (!attr) {
+  static std::atomic<unsigned long long> attr{0};   // per device
+  if (device_needs_setup(attr)) {
     B200_CUDA_OK(cudaFuncSetAttribute(nms_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr = true;
+    device_setup_done(attr);
   }
   nms_scan_kernel<<<1, 128, words * sizeof(unsigned long long), stream>>>(mask_ws, nullptr, n, 0, n, words, n, boxes,
                                                                           nullptr, nullptr, nullptr, nullptr, nullptr,

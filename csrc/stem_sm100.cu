@@ -217,10 +217,10 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_conv_kernel(const StemPa
 extern "C" int b200_stem_conv(const void* x, const void* w_packed, const float* shift, void* y, int N, int H, int W,
                               void* stream) {
   using namespace b200;
-  static bool attr = false;
-  if (!attr) {
+  static std::atomic<unsigned long long> attr{0};   // per device
+  if (device_needs_setup(attr)) {
     B200_CUDA_OK(cudaFuncSetAttribute(stem_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
-    attr = true;
+    device_setup_done(attr);
   }
   StemParams p;
   p.x = static_cast<const __nv_bfloat16*>(x);
@@ -430,10 +430,10 @@ __global__ void __launch_bounds__(kSwThreads, 1) stem_wgrad_kernel(const __grid_
 extern "C" int b200_stem_wgrad(const void* x, const void* dy, const float* scale, float* dw, int N, int H, int W,
                                void* stream) {
   using namespace b200;
-  static bool attr = false;
-  if (!attr) {
+  static std::atomic<unsigned long long> attr{0};   // per device
+  if (device_needs_setup(attr)) {
     B200_CUDA_OK(cudaFuncSetAttribute(stem_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSwSmem));
-    attr = true;
+    device_setup_done(attr);
   }
   StemWgradParams p;
   memset(&p, 0, sizeof(p));

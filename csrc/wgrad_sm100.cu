@@ -270,10 +270,10 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
   if ((a->ldx % 8) || (a->ldy % 8)) return set_error(-1, "b200_wgrad: ld* must be multiples of 8");
   if (a->Cin % 64) return set_error(-1, "b200_wgrad: Cin must be a multiple of 64");
 
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_set{0};   // per device
+  if (device_needs_setup(attr_set)) {
     B200_CUDA_OK(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmemBytes));
-    attr_set = true;
+    device_setup_done(attr_set);
   }
 
   WgradParams p;

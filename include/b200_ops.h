@@ -208,6 +208,8 @@ typedef struct {
   int algo;                 /* 0 auto, 1 one-shot, 2 two-shot (pull), 3 fused reduce + push all-gather */
   int max_blocks;           /* <= 64; 0 = default */
   int has_prescale;
+  int external_sync;        /* 1: the caller orders the ranks with events (ranks = threads of one process); the
+                               kernel then contains no flag barrier and algo is forced to one-shot */
 } B200ArHostArgs;
 int b200_allreduce_host(const B200ArHostArgs* args, void* stream);
 int b200_broadcast_host(const B200ArHostArgs* args, int root, void* stream);

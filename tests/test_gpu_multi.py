@@ -34,3 +34,12 @@ def test_p2p_allreduce_and_broadcast():
 def test_data_parallel_step_matches_single_process():
     out = _run("dp_step.py", 2)
     assert "DP_OK" in out
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+def test_single_process_towers():
+    """--multi-gpu 2 (reference train.py:86-89): N engines in one process, same allreduce kernel over peer pointers."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "multi", "towers.py")], capture_output=True, text=True,
+                       timeout=420, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "TOWERS_OK" in r.stdout
