@@ -60,7 +60,8 @@ class ArHostArgs(C.Structure):
     _fields_ = [("bufs", C.c_void_p * 8), ("flags", C.c_void_p * 8), ("prescale", C.c_void_p * 8),
                 ("outs", C.c_void_p * 8), ("out", C.c_void_p), ("rank", C.c_int), ("world", C.c_int), ("offset", C.c_longlong),
                 ("count", C.c_longlong), ("postscale", C.c_float), ("epoch", C.c_uint32), ("algo", C.c_int),
-                ("max_blocks", C.c_int), ("has_prescale", C.c_int), ("external_sync", C.c_int)]
+                ("max_blocks", C.c_int), ("has_prescale", C.c_int), ("mc_buf", C.c_void_p), ("mc_out", C.c_void_p),
+                ("external_sync", C.c_int)]
 
 
 def lib_path() -> str:
@@ -432,6 +433,62 @@ def ipc_open_handle(handle: bytes) -> int:
 
 def ipc_close_handle(ptr: int):
     _check(_load().b200_ipc_close_handle(C.c_void_p(ptr)), "ipc_close_handle")
+
+
+# ---- VMM regions + NVLink multicast (csrc/vmm_multicast.cu) ----------------------------------------
+def vmm_supported(device: int):
+    """(vmm_with_posix_fd, multicast) capability of ``device``."""
+    mc = C.c_int(0)
+    ok = _load().b200_vmm_supported(int(device), C.byref(mc))
+    return bool(ok), bool(mc.value)
+
+
+def vmm_granularity(device: int, world: int) -> int:
+    g = C.c_longlong(0)
+    _check(_load().b200_vmm_granularity(int(device), int(world), C.byref(g)), "vmm_granularity")
+    return int(g.value)
+
+
+def vmm_create(device: int, nbytes: int):
+    """-> (handle, fd): physical allocation on ``device`` and a POSIX fd peers can import."""
+    h, fd = C.c_ulonglong(0), C.c_int(-1)
+    _check(_load().b200_vmm_create(int(device), C.c_longlong(nbytes), C.byref(h), C.byref(fd)), "vmm_create")
+    return int(h.value), int(fd.value)
+
+
+def vmm_import(fd: int) -> int:
+    h = C.c_ulonglong(0)
+    _check(_load().b200_vmm_import(int(fd), C.byref(h)), "vmm_import")
+    return int(h.value)
+
+
+def vmm_map(handle: int, nbytes: int, device: int, alignment: int) -> int:
+    p = C.c_void_p()
+    _check(_load().b200_vmm_map(C.c_ulonglong(handle), C.c_longlong(nbytes), int(device), C.c_longlong(alignment),
+                                C.byref(p)), "vmm_map")
+    return int(p.value)
+
+
+def vmm_unmap(ptr: int, nbytes: int):
+    _check(_load().b200_vmm_unmap(C.c_void_p(ptr), C.c_longlong(nbytes)), "vmm_unmap")
+
+
+def vmm_release(handle: int):
+    _check(_load().b200_vmm_release(C.c_ulonglong(handle)), "vmm_release")
+
+
+def mc_create(world: int, nbytes: int):
+    h, fd = C.c_ulonglong(0), C.c_int(-1)
+    _check(_load().b200_mc_create(int(world), C.c_longlong(nbytes), C.byref(h), C.byref(fd)), "mc_create")
+    return int(h.value), int(fd.value)
+
+
+def mc_add_device(mc: int, device: int):
+    _check(_load().b200_mc_add_device(C.c_ulonglong(mc), int(device)), "mc_add_device")
+
+
+def mc_bind(mc: int, mem: int, nbytes: int):
+    _check(_load().b200_mc_bind(C.c_ulonglong(mc), C.c_ulonglong(mem), C.c_longlong(nbytes)), "mc_bind")
 
 
 def enable_peer_access(device: int, world_local: int):

@@ -17,6 +17,10 @@ IPC handles once, and for the rendezvous itself.
 from __future__ import annotations
 
 import ctypes as C
+import os
+import socket
+import threading
+import uuid
 
 import torch
 
@@ -42,6 +46,9 @@ class P2PComm:
         self.bucket = None
         self.prescale_local = None
         self.external_sync = False   # LocalP2PComm orders ranks with events instead of in-kernel flags
+        self.mc_base = 0             # multicast (NVLS) address of the region, 0 when not available
+        self.region_bytes = 0
+        self._vmm = None             # handles to release on close
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -68,11 +75,8 @@ class P2PComm:
         self.bucket_elems = nfloats
         total = self.flag_bytes + SCALARS_BYTES + 8 * nfloats   # bucket + peer-writable result buffer
         with torch.cuda.device(self.device):
-            self.base = native.ipc_alloc(total)
-            handle = self._export_region(self.base) if self.world > 1 else b""
-            handles = self._gather(handle) if self.world > 1 else [handle]
-            for r in range(self.world):
-                self.peer_base.append(self.base if r == self.rank else self._import_region(handles[r]))
+            if not self._alloc_region_vmm(total):
+                self._alloc_region_ipc(total)
         raw = native.RawCudaBuffer(self.base, total).tensor(self.device)
         self._raw = raw
         off = self.flag_bytes
@@ -83,6 +87,130 @@ class P2PComm:
         torch.cuda.synchronize(self.device)
         self.barrier_host()
         return self.bucket
+
+    # ------------------------------------------------------------------ region allocation
+    def _alloc_region_ipc(self, total: int):
+        """cudaMalloc + CUDA IPC handles (no multicast address)."""
+        self.region_bytes = total
+        self.base = native.ipc_alloc(total)
+        handle = self._export_region(self.base) if self.world > 1 else b""
+        handles = self._gather(handle) if self.world > 1 else [handle]
+        for r in range(self.world):
+            self.peer_base.append(self.base if r == self.rank else self._import_region(handles[r]))
+
+    def _nvls_wanted(self) -> bool:
+        return self.world > 1 and not self.external_sync and os.environ.get("B200_P2P_NVLS", "1") != "0"
+
+    def _alloc_region_vmm(self, total: int) -> bool:
+        """VMM allocation shared through POSIX fds, every peer mapped unicast, plus an NVSwitch multicast
+        mapping of the same memory (``mc_base``) for the NVLS allreduce.  Returns False (after agreeing with
+        every rank) when the box does not offer it, in which case the CUDA IPC path is used."""
+        if not self._nvls_wanted():
+            return False
+        dev = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        vmm, mc = native.vmm_supported(dev)
+        if not all(f == b"1" for f in self._gather(b"1" if (vmm and mc) else b"0")):
+            return False
+        state = {"maps": [], "handles": []}
+        err = None
+        size = mem = mc_handle = base = 0
+        peer_base = []
+        try:
+            gran = native.vmm_granularity(dev, self.world)
+            size = -(-total // gran) * gran
+            mem, mem_fd = native.vmm_create(dev, size)
+            state["handles"].append(mem)
+            base = native.vmm_map(mem, size, dev, gran)
+            state["maps"].append(base)
+            native.RawCudaBuffer(base, size).tensor(self.device).zero_()
+            torch.cuda.synchronize(self.device)
+            fds = [mem_fd]
+            if self.rank == 0:
+                mc_handle, mc_fd = native.mc_create(self.world, size)
+                state["handles"].append(mc_handle)
+                fds.append(mc_fd)
+            got = self._exchange_fds(fds)               # {peer rank: [fds]}
+            peer_base = [0] * self.world
+            for r in range(self.world):
+                if r == self.rank:
+                    peer_base[r] = base
+                    continue
+                h = native.vmm_import(got[r][0])
+                state["handles"].append(h)
+                peer_base[r] = native.vmm_map(h, size, dev, gran)
+                state["maps"].append(peer_base[r])
+            if self.rank != 0:
+                mc_handle = native.vmm_import(got[0][1])
+                state["handles"].append(mc_handle)
+            for fl in list(got.values()) + [fds]:
+                for fd in fl:
+                    os.close(fd)
+            native.mc_add_device(mc_handle, dev)
+        except Exception as e:  # noqa: BLE001 - any failure must be agreed on by all ranks before falling back
+            err = e
+        # every device must be added before anyone binds; a rank that failed makes all ranks fall back
+        if not all(f == b"1" for f in self._gather(b"0" if err else b"1")):
+            self._release_vmm(state, size)
+            if err is not None and os.environ.get("B200_P2P_NVLS") == "1":
+                raise err
+            return False
+        try:
+            native.mc_bind(mc_handle, mem, size)
+        except Exception as e:  # noqa: BLE001
+            err = e
+        if not all(f == b"1" for f in self._gather(b"0" if err else b"1")):
+            raise RuntimeError(f"NVLS multicast bind failed on some rank ({err}); set B200_P2P_NVLS=0 to use CUDA IPC")
+        mc_base = native.vmm_map(mc_handle, size, dev, gran)
+        state["maps"].append(mc_base)
+        self.base, self.peer_base, self.mc_base, self.region_bytes = base, peer_base, mc_base, size
+        self._vmm = (state, size)
+        self._gather(b"x")
+        return True
+
+    def _release_vmm(self, state, size):
+        for ptr in state["maps"]:
+            try:
+                native.vmm_unmap(ptr, size)
+            except Exception:
+                pass
+        for h in state["handles"]:
+            try:
+                native.vmm_release(h)
+            except Exception:
+                pass
+
+    def _exchange_fds(self, fds):
+        """Give ``fds`` to every peer and receive theirs (SCM_RIGHTS over abstract Unix sockets; the names travel
+        over the control plane).  Returns {peer rank: [fd, ...]} with this process's own copies."""
+        name = f"\0b200p2p-{uuid.uuid4().hex}-{self.rank}"
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        srv.bind(name)
+        srv.listen(self.world)
+        srv.settimeout(60)
+        names = [n.decode("latin1") for n in self._gather(name.encode("latin1"))]
+
+        def serve():
+            for _ in range(self.world - 1):
+                conn, _ = srv.accept()
+                with conn:
+                    conn.recv(1)
+                    socket.send_fds(conn, [b"f"], list(fds))
+
+        t = threading.Thread(target=serve, daemon=True)
+        t.start()
+        got = {}
+        for r in range(self.world):
+            if r == self.rank:
+                continue
+            with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as c:
+                c.settimeout(60)
+                c.connect(names[r])
+                c.send(b"r")
+                _, rfds, _, _ = socket.recv_fds(c, 16, 4)
+                got[r] = list(rfds)
+        t.join(timeout=60)
+        srv.close()
+        return got
 
     def _before_collective(self):
         pass
@@ -112,6 +240,9 @@ class P2PComm:
             a.flags[r] = self.peer_base[r]
             a.prescale[r] = self.peer_base[r] + self.flag_bytes
             a.outs[r] = (self.peer_base[r] + self.flag_bytes + SCALARS_BYTES + 4 * self.bucket_elems) if push else 0
+        if push and self.mc_base:
+            a.mc_buf = self.mc_base + self.flag_bytes + SCALARS_BYTES
+            a.mc_out = self.mc_base + self.flag_bytes + SCALARS_BYTES + 4 * self.bucket_elems
         a.out = out.data_ptr()
         a.rank, a.world = self.rank, self.world
         a.offset, a.count = offset, count
@@ -167,8 +298,9 @@ class P2PComm:
             m4 = (m + 3) // 4 * 4
             if self.rank == root:
                 self.bucket[:m].copy_(flat[done:done + m])
-            tmp = torch.empty(m4, device=self.device, dtype=torch.float32)
-            a = self._args(tmp, 0, m4, 1.0, False, 0)
+            use_mc = bool(self.mc_base)      # through the switch: one multicast store reaches every result buffer
+            tmp = self.result if use_mc else torch.empty(m4, device=self.device, dtype=torch.float32)
+            a = self._args(tmp, 0, m4, 1.0, False, 4 if use_mc else 0, push=use_mc)
             self._before_collective()
             native.broadcast_host(a, root)
             self._after_collective()
@@ -186,6 +318,10 @@ class P2PComm:
             except Exception:
                 pass
         self._opened = []
+        if self._vmm is not None:
+            self.bucket = self.result = self.prescale_local = self._raw = None
+            self._release_vmm(*self._vmm)
+            self._vmm = None
 
 
 class LocalGroup:

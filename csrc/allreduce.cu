@@ -31,6 +31,8 @@ struct ArParams {
   long long offset, count;
   float postscale;
   uint32_t epoch;   // base flag value of this call; the call uses epoch+1 .. epoch+3
+  const float* mc_buf;  // multicast address of the bucket (NVLS), or null
+  float* mc_out;        // multicast address of the result buffer (NVLS), or null
   int has_prescale;
   int external_sync;  // no in-kernel flag barriers: the launching streams were ordered by the host
 };
@@ -202,6 +204,85 @@ __global__ void __launch_bounds__(kArThreads) allreduce_push_kernel(const ArPara
   rank_barrier(p, p.epoch + 2);
 }
 
+
+// ---- NVLS: the NVSwitch reduces.  multimem.ld_reduce on the multicast address returns the sum of the
+// same offset in EVERY rank's bucket (added inside the switch); multimem.st writes one value into every
+// rank's result buffer.  Each rank handles 1/N of the bucket, so a GPU sends and receives about S bytes
+// instead of 2 (N-1)/N S with unicast reduce-scatter + all-gather.  The switch cannot weight its inputs, so
+// the per-rank clip factor is applied to the local bucket in place before the first barrier.
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+
+template <int kWorld>
+__global__ void __launch_bounds__(kArThreads) allreduce_nvls_kernel(const ArParams p) {
+  const long long n4 = p.count >> 2;
+  const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  if (p.has_prescale) {
+    const float s = *p.prescale[p.rank];
+    if (s != 1.f) {
+      float4* mine = reinterpret_cast<float4*>(p.bufs[p.rank] + p.offset);
+      for (long long i = tid; i < n4; i += nthreads) {
+        float4 v = mine[i];
+        v.x *= s; v.y *= s; v.z *= s; v.w *= s;
+        mine[i] = v;
+      }
+      __threadfence_system();
+    }
+  }
+  rank_barrier(p, p.epoch + 1);
+  const long long per = (n4 + kWorld - 1) / kWorld;
+  const long long lo = p.rank * per;
+  const long long hi = lo + per < n4 ? lo + per : n4;
+  const float* in = p.mc_buf + p.offset;
+  float* out = p.mc_out + p.offset;
+  constexpr int kU = 4;
+  long long i = lo + tid;
+  for (; i + (kU - 1) * nthreads < hi; i += kU * nthreads) {
+    float4 v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) v[u] = multimem_ld_reduce_add(in + (i + u * nthreads) * 4);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      v[u].x *= p.postscale; v[u].y *= p.postscale; v[u].z *= p.postscale; v[u].w *= p.postscale;
+      multimem_st(out + (i + u * nthreads) * 4, v[u]);
+    }
+  }
+  for (; i < hi; i += nthreads) {
+    float4 v = multimem_ld_reduce_add(in + i * 4);
+    v.x *= p.postscale; v.y *= p.postscale; v.z *= p.postscale; v.w *= p.postscale;
+    multimem_st(out + i * 4, v);
+  }
+  __threadfence_system();
+  rank_barrier(p, p.epoch + 2);
+}
+
+// Broadcast through the switch: the root stores once, every rank's result buffer receives it.
+template <int kWorld>
+__global__ void __launch_bounds__(kArThreads) broadcast_nvls_kernel(const ArParams p, int root) {
+  rank_barrier(p, p.epoch + 1);
+  if (p.rank == root) {
+    const long long n4 = p.count >> 2;
+    const float4* src = reinterpret_cast<const float4*>(p.bufs[root] + p.offset);
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+         i += static_cast<long long>(gridDim.x) * blockDim.x)
+      multimem_st(p.mc_out + p.offset + i * 4, src[i]);
+    __threadfence_system();
+  }
+  rank_barrier(p, p.epoch + 2);
+}
+
 template <int kWorld>
 __global__ void __launch_bounds__(kArThreads) broadcast_kernel(const ArParams p, int root) {
   rank_barrier(p, p.epoch + 1);
@@ -254,6 +335,8 @@ static int fill(ArParams& p, const B200ArHostArgs* a) {
   p.postscale = a->postscale;
   p.epoch = a->epoch;
   p.has_prescale = a->has_prescale;
+  p.mc_buf = static_cast<const float*>(a->mc_buf);
+  p.mc_out = static_cast<float*>(a->mc_out);
   p.external_sync = a->external_sync;
   return 0;
 }
@@ -285,7 +368,12 @@ int b200_allreduce_host(const B200ArHostArgs* a, void* stream_) {
   int algo = a->algo;
   const bool can_push = a->outs[0] != nullptr;
   // measured at 8 GPUs: push is never slower than one-shot (23 vs 25 us at 1 KB, 28 vs 61 us at 256 KB)
-  if (algo == 0) algo = can_push ? 3 : ((bytes <= (128 << 10)) ? 1 : 2);
+  const bool can_nvls = p.mc_buf != nullptr && p.mc_out != nullptr && !p.external_sync;
+  static long long nvls_min = -1;
+  if (nvls_min < 0) { const char* e = getenv("B200_AR_NVLS_MIN"); nvls_min = e ? atoll(e) : (1ll << 20); }
+  // NVLS moves S bytes per direction per GPU, unicast push 2(N-1)/N * S / 2: no gain at N = 2 (measured 0.6x)
+  if (algo == 0) algo = (can_nvls && p.world >= 4 && bytes >= nvls_min) ? 4 : (can_push ? 3 : ((bytes <= (128 << 10)) ? 1 : 2));
+  if (algo == 4 && !can_nvls) return set_error(-1, "allreduce: NVLS algorithm needs multicast addresses");
   if (p.external_sync) algo = 1;   // the multi-phase algorithms need barriers between their phases
   if (algo == 3 && !can_push) return set_error(-1, "allreduce: push algorithm needs peer-mapped output buffers");
   const long long work = (algo == 1) ? n4 : (n4 + p.world - 1) / p.world;
@@ -297,6 +385,8 @@ int b200_allreduce_host(const B200ArHostArgs* a, void* stream_) {
       allreduce_oneshot_kernel<W><<<blocks, kArThreads, 0, stream>>>(p);                         \
     else if (algo == 3)                                                                          \
       allreduce_push_kernel<W><<<blocks, kArThreads, 0, stream>>>(p);                            \
+    else if (algo == 4)                                                                          \
+      allreduce_nvls_kernel<W><<<blocks, kArThreads, 0, stream>>>(p);                            \
     else                                                                                         \
       allreduce_twoshot_kernel<W><<<blocks, kArThreads, 0, stream>>>(p);                         \
     break;
@@ -322,6 +412,17 @@ int b200_broadcast_host(const B200ArHostArgs* a, int root, void* stream_) {
   if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
   long long need = (n4 + kArThreads - 1) / kArThreads;
   if (need < blocks) blocks = static_cast<int>(need < 1 ? 1 : need);
+  if (a->algo == 4) {
+    // through the switch: the result lands in every rank's `result` buffer (mc_out), the root's included
+    if (!p.mc_out || p.external_sync) return set_error(-1, "broadcast: NVLS needs a multicast result address");
+    switch (p.world) {
+      case 2: broadcast_nvls_kernel<2><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+      case 4: broadcast_nvls_kernel<4><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+      case 8: broadcast_nvls_kernel<8><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+      default: return set_error(-1, "broadcast: world size %d not instantiated", p.world);
+    }
+    return check_launch("broadcast_nvls_kernel");
+  }
   switch (p.world) {
     case 2: broadcast_kernel<2><<<blocks, kArThreads, 0, stream>>>(p, root); break;
     case 4: broadcast_kernel<4><<<blocks, kArThreads, 0, stream>>>(p, root); break;

@@ -205,9 +205,12 @@ typedef struct {
   long long offset, count;  /* element range of the bucket, multiples of 4 */
   float postscale;          /* e.g. 1/world */
   uint32_t epoch;           /* flag base; advance by 4 per call, same on every rank */
-  int algo;                 /* 0 auto, 1 one-shot, 2 two-shot (pull), 3 fused reduce + push all-gather */
+  int algo;                 /* 0 auto, 1 one-shot, 2 two-shot (pull), 3 fused reduce + push all-gather,
+                               4 NVLS: in-switch reduce (multimem.ld_reduce) + multicast store (needs mc_buf/mc_out) */
   int max_blocks;           /* <= 64; 0 = default */
   int has_prescale;
+  void* mc_buf;             /* multicast (NVLS) address of the bucket, or null */
+  void* mc_out;             /* multicast (NVLS) address of the result buffer, or null */
   int external_sync;        /* 1: the caller orders the ranks with events (ranks = threads of one process); the
                                kernel then contains no flag barrier and algo is forced to one-shot */
 } B200ArHostArgs;
@@ -221,6 +224,20 @@ int b200_ipc_get_handle(void* ptr, void* handle64);
 int b200_ipc_open_handle(const void* handle64, void** ptr);
 int b200_ipc_close_handle(void* ptr);
 int b200_enable_peer_access(int device, int world_local);
+
+/* ---- VMM + NVLink multicast set-up (csrc/vmm_multicast.cu): symmetric regions that peers map through a
+ * POSIX fd and that are bound to an NVSwitch multicast object for the NVLS allreduce (algo 4).  The
+ * reference's stack reaches NVLS only through NCCL, if at all. */
+int b200_vmm_supported(int device, int* multicast);
+int b200_vmm_granularity(int device, int world, long long* bytes);
+int b200_vmm_create(int device, long long bytes, unsigned long long* handle, int* fd);
+int b200_vmm_import(int fd, unsigned long long* handle);
+int b200_vmm_map(unsigned long long handle, long long bytes, int device, long long alignment, void** ptr);
+int b200_vmm_unmap(void* ptr, long long bytes);
+int b200_vmm_release(unsigned long long handle);
+int b200_mc_create(int world, long long bytes, unsigned long long* handle, int* fd);
+int b200_mc_add_device(unsigned long long mc, int device);
+int b200_mc_bind(unsigned long long mc, unsigned long long mem, long long bytes);
 
 #ifdef __cplusplus
 }

@@ -55,13 +55,21 @@ while size <= MAXB:
         dst = comm.result if algo == 3 else out
         ms = timeit(lambda: comm.allreduce_avg(bucket, dst, n, prescale=True, algo=algo), iters)
         row[name + "_us"] = ms * 1e3
+    if comm.mc_base:
+        # NVLS: in-switch reduce + multicast store; `nvls_scaled` also pays the local in-place clip-factor pass
+        row["nvls_us"] = timeit(lambda: comm.allreduce_avg(bucket, comm.result, n, prescale=True, algo=4), iters) * 1e3
+        comm.prescale_local.fill_(0.999)
+        row["nvls_scaled_us"] = timeit(lambda: comm.allreduce_avg(bucket, comm.result, n, prescale=True, algo=4), iters) * 1e3
+        comm.prescale_local.fill_(1.0)
+        bucket.normal_()
     best = min(v for k, v in row.items() if k.endswith("_us"))
     ms_n = timeit(lambda: dist.all_reduce(nccl_buf[:n]), iters)
     row["nccl_us"] = ms_n * 1e3
     row["p2p_algbw_GBs"] = size / best / 1e3
     row["p2p_busbw_GBs"] = row["p2p_algbw_GBs"] * 2 * (world - 1) / world
     row["nccl_busbw_GBs"] = size / (ms_n * 1e3) / 1e3 * 2 * (world - 1) / world
-    roof_us = (world - 1) / world * size / LINK * 1e6   # per direction: reads in, pushes out
+    # per direction per GPU: unicast reduce + push moves (N-1)/N * S in and out; with NVLS the floor is S / LINK
+    roof_us = (world - 1) / world * size / LINK * 1e6
     row["frac_of_nvlink_roofline"] = roof_us / best
     row["speedup_vs_nccl"] = ms_n * 1e3 / best
     if rank == 0:

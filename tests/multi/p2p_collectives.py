@@ -10,16 +10,21 @@ dist.init_process_group("nccl", device_id=dev)
 comm = P2PComm.from_torch_distributed(dev)
 N = 6_000_000
 bucket = comm.symmetric_bucket(N)
-for algo, n in ((1, 1000), (1, 100_000), (2, 100_000), (2, N), (0, 4096), (0, N), (3, 100_000), (3, N)):
+cases = [(1, 1000), (1, 100_000), (2, 100_000), (2, N), (0, 4096), (0, N), (3, 100_000), (3, N)]
+if rank == 0:
+    print("P2P_REGION", "vmm+multicast" if comm.mc_base else "cuda-ipc")
+if comm.mc_base:      # NVLS: in-switch reduce + multicast store (algo 4), and the auto choice with a shared result buffer
+    cases += [(4, 1000), (4, 100_000), (4, N), (-1, N)]
+for algo, n in cases:
     g = torch.Generator(device=dev).manual_seed(100 + rank)
     x = torch.randn(N, device=dev, generator=g)
     bucket.copy_(x)
     pre = 0.5 + rank
     comm.prescale_local.fill_(pre)
-    out = comm.result if algo == 3 else torch.zeros(N, device=dev)
+    out = comm.result if algo in (3, 4, -1) else torch.zeros(N, device=dev)
     out.zero_()
     torch.cuda.synchronize(); dist.barrier()
-    comm.allreduce_avg(bucket, out, n, prescale=True, algo=algo)
+    comm.allreduce_avg(bucket, out, n, prescale=True, algo=max(algo, 0))
     torch.cuda.synchronize()
     ref = x * pre
     dist.all_reduce(ref)
@@ -37,7 +42,7 @@ assert abs(t[0].item() - world * (world + 1) / 2) < 1e-5
 # bandwidth (device timed, max over ranks)
 for nbytes in (1 << 12, 1 << 16, 1 << 20, 1 << 24, N * 4):
     n = nbytes // 4
-    out = torch.zeros(N, device=dev)
+    out = comm.result          # shared result buffer: lets the auto choice use push / NVLS
     for _ in range(3):
         comm.allreduce_avg(bucket, out, n, prescale=False)
     torch.cuda.synchronize(); dist.barrier()
