@@ -56,6 +56,15 @@ int num_sms() {
   return n;
 }
 
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("B200_PDL");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
+
 static unsigned long long device_bit() {
   int dev = 0;
   cudaGetDevice(&dev);

@@ -6,6 +6,8 @@
 #include <stdio.h>
 
 #include <atomic>
+#include <utility>
+#include <cstdlib>
 
 namespace b200 {
 
@@ -49,6 +51,24 @@ int num_sms();
 // device's context, and one process may drive several GPUs: engine/multi_tower.py).  Usage:
 //   static std::atomic<unsigned long long> done{0};
 //   if (device_needs_setup(done)) { ...cudaFuncSetAttribute...; device_setup_done(done); }
+// Launch with the programmatic-dependent-launch attribute (see pdl_wait in ptx_sm100.cuh); B200_PDL=0 turns it off.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 bool device_needs_setup(const std::atomic<unsigned long long>& mask);
 void device_setup_done(std::atomic<unsigned long long>& mask);
 

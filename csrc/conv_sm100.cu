@@ -133,6 +133,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
+  // set-up done: let the next kernel start its own set-up, then wait for the previous kernel's results
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -555,9 +558,9 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
 
   const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles;
   const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
-  if (has_add && has_mask) conv_igemm_kernel<true, true><<<grid, kConvThreads, kSmemBytes, stream>>>(p);
-  else if (has_add) conv_igemm_kernel<true, false><<<grid, kConvThreads, kSmemBytes, stream>>>(p);
-  else if (has_mask) conv_igemm_kernel<false, true><<<grid, kConvThreads, kSmemBytes, stream>>>(p);
-  else conv_igemm_kernel<false, false><<<grid, kConvThreads, kSmemBytes, stream>>>(p);
+  if (has_add && has_mask) launch_pdl(conv_igemm_kernel<true, true>, grid, kConvThreads, kSmemBytes, stream, p);
+  else if (has_add) launch_pdl(conv_igemm_kernel<true, false>, grid, kConvThreads, kSmemBytes, stream, p);
+  else if (has_mask) launch_pdl(conv_igemm_kernel<false, true>, grid, kConvThreads, kSmemBytes, stream, p);
+  else launch_pdl(conv_igemm_kernel<false, false>, grid, kConvThreads, kSmemBytes, stream, p);
   return check_launch("conv_igemm_kernel");
 }

@@ -270,6 +270,8 @@ struct ColsumArgs {
 };
 __global__ void __launch_bounds__(256) colsum_kernel(ColsumArgs a, int cols, int ld, float* __restrict__ out) {
   __shared__ float part[8][32][8];
+  pdl_launch_dependents();   // sits between wgrad and dgrad of every biased layer: keep the dependent-launch chain
+  pdl_wait();
   int pi = 0;
 #pragma unroll
   for (int i = 1; i < 5; ++i)
@@ -443,7 +445,7 @@ int b200_colsum_multi(const void* const* xs, const long long* rows, int n, int c
   a.n = n;
   if (blocks == 0) return 0;
   dim3 grid(static_cast<unsigned>(blocks), (cols + 255) / 256);
-  colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a, cols, ld, out_accum);
+  launch_pdl(colsum_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream), a, cols, ld, out_accum);
   return check_launch("colsum");
 }
 

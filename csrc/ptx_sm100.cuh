@@ -135,4 +135,12 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
 
+
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute may
+// start (and run its set-up: barrier init, TMEM alloc, descriptor prefetch) while the previous kernel in the
+// stream is still draining; pdl_wait() blocks until that kernel has completed and its writes are visible.
+// Every global-memory access must come after pdl_wait().  pdl_launch_dependents() lets the NEXT kernel do the same.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 }  // namespace b200

@@ -129,6 +129,8 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
+  pdl_launch_dependents();   // set-up done: the next kernel may start its own; then wait for our inputs
+  pdl_wait();
 
   if (pt_begin < pt_end) {
     if (warp == 0) {
@@ -363,7 +365,7 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
   const long long grid = units * p.ksplit;
   if (grid > 0x7fffffffLL) return set_error(-1, "b200_wgrad: grid too large");
 
-  wgrad_kernel<<<static_cast<unsigned>(grid), kWThreads, kWSmemBytes, stream>>>(p);
+  launch_pdl(wgrad_kernel, static_cast<unsigned>(grid), kWThreads, kWSmemBytes, stream, p);
   int rc = check_launch("wgrad_kernel");
   if (rc) return rc;
   if (a->dbias) {
