@@ -31,6 +31,7 @@ class HybridTrainer(NativeTrainer):
         self.blocks = []
         self.bb = self.model.backbone.to(self.device)
         self._infer = False
+        self.use_graph = False    # the autograd backbone is not captured
         self._extra = []          # (param, offset, numel) in the flat buffers
         self._extra_bound = False
         return []

@@ -26,6 +26,8 @@ checkpoints: ``load_from_model`` / ``store_to_model`` convert between the two pa
 from __future__ import annotations
 
 import math
+import os
+import warnings
 
 import torch
 import torch.nn.functional as F
@@ -82,7 +84,7 @@ class NativeTrainer:
     def __init__(self, backbone: str = "resnet50", num_classes: int = 80, device="cuda", batch: int = 8,
                  image_hw=(800, 1333), lr: float = 1e-5, clipnorm: float = 0.001, distributed: bool = False,
                  model: RetinaNet | None = None, freeze_backbone: bool = False, comm=None, shape_bucket: int = 1,
-                 max_plans: int = 4):
+                 max_plans: int = 4, use_graph: bool | None = None):
         native.require()
         self.device = torch.device(device)
         self.num_classes = num_classes
@@ -95,6 +97,13 @@ class NativeTrainer:
         # sizes are rounded up to `shape_bucket` and only the `max_plans` most recent buffer plans are kept.
         self.shape_bucket = max(1, int(shape_bucket))
         self.max_plans = max(1, int(max_plans))
+        # Whole-step CUDA graph per plan: at small per-GPU batches (the reference's default --batch-size is 1) the
+        # ~270 launches of a step cost more host time than GPU time.  B200_GRAPH=0 disables it.
+        if use_graph is None:
+            use_graph = os.environ.get("B200_GRAPH", "1") != "0"
+        self.use_graph = bool(use_graph)
+        self.graph_warmup = 2        # eager steps on a plan before it is captured
+        self.graph_gt_cap = 128      # ground-truth boxes per image the captured step can take
         self.model = model if model is not None else RetinaNet(num_classes, backbone)
         if freeze_backbone:
             self.model.freeze_backbone()
@@ -218,6 +227,9 @@ class NativeTrainer:
         self.npos = torch.zeros(1, dtype=torch.int32, device=dev)
         self.ones64 = torch.ones(64, device=dev)
         self.zeros64 = torch.zeros(64, device=dev)
+        self.lr_dev = torch.zeros(1, device=dev)          # bias-corrected Adam step size of the current step
+        self.loss_out = torch.zeros(3, device=dev)        # [loss, regression_loss, classification_loss]
+        self.stem_wp = torch.zeros(64, 256, device=dev, dtype=BF16)
         self._bind_extra()
 
     # ------------------------------------------------------------------ parameter import / export
@@ -232,6 +244,7 @@ class NativeTrainer:
                 s, t = c.bn.scale_shift()
                 c.scale.copy_(s.to(self.device))
                 c.shift.copy_(t.to(self.device))
+        self.__dict__.pop("_stem_idx", None)      # the packed-stem helper caches the BN scale
         self._refresh_weights()
 
     @torch.no_grad()
@@ -260,7 +273,7 @@ class NativeTrainer:
             idx = ((r * 7 + sx).view(1, 256) * 64 + co) * 3 + c.view(1, 256)
             self._stem_idx = torch.where(ok.view(1, 256), idx, torch.zeros_like(idx))
             self._stem_ok = ok.view(1, 256).float() * s.scale.view(64, 1)
-        self.stem_wp = (s.wview(self.P).reshape(-1)[self._stem_idx] * self._stem_ok).to(BF16)
+        self.stem_wp.copy_(s.wview(self.P).reshape(-1)[self._stem_idx] * self._stem_ok)   # in place: address is stable
 
     def optimizer_state(self):
         """Adam slots as {keras layer name: {'kernel': (m, v), 'bias': (m, v)}} views + iterations."""
@@ -573,21 +586,25 @@ class NativeTrainer:
         self.iterations, self.lr = int(it[0].item()), float(it[1].item())
         self._refresh_weights()
 
-    def _optimizer_step(self):
-        n = self.n_train
+    def _begin_step(self):
+        """Host-side per-step scalars, written to device memory OUTSIDE any captured graph."""
         self.iterations += 1
         t = self.iterations
-        lr_t = self.lr * math.sqrt(1.0 - self.beta2 ** t) / (1.0 - self.beta1 ** t)
+        self.lr_dev.fill_(self.lr * math.sqrt(1.0 - self.beta2 ** t) / (1.0 - self.beta1 ** t))
+
+    def _optimizer_step(self):
+        n = self.n_train
         native.sumsq(self.G[:n], self.scal[0:1])
         if self.comm is not None and self.comm.world > 1:
             # the clip factor lives in peer-visible memory: peers apply it while reading my bucket
             native.clip_scale(self.scal[0:1], self.clipnorm, self.comm.prescale_local)
             self.comm.allreduce_avg(self.G, self.Gavg, n, prescale=True)
-            native.adam(self.P[:n], self.Gavg[:n], self.M[:n], self.V[:n], None, lr_t, self.beta1, self.beta2, self.eps)
+            native.adam(self.P[:n], self.Gavg[:n], self.M[:n], self.V[:n], None, self.lr_dev, self.beta1, self.beta2,
+                        self.eps)
         else:
             native.clip_scale(self.scal[0:1], self.clipnorm, self.scal[1:2])
-            native.adam(self.P[:n], self.G[:n], self.M[:n], self.V[:n], self.scal[1:2], lr_t, self.beta1, self.beta2,
-                        self.eps)
+            native.adam(self.P[:n], self.G[:n], self.M[:n], self.V[:n], self.scal[1:2], self.lr_dev, self.beta1,
+                        self.beta2, self.eps)
         self._refresh_weights()
 
     def _mark(self, name):
@@ -633,13 +650,29 @@ class NativeTrainer:
         img_hw int32 [B,2] un-padded sizes.  Returns a device tensor [loss, regression_loss,
         classification_loss] (the Keras metric names of reference train.py:99-102)."""
         dev = self.device
+        B, H, W = images_u8.shape[:3]
+        b = self.shape_bucket
+        p = self._plan(B, -(-H // b) * b, -(-W // b) * b)
+        self._begin_step()
+        if "graph" in p and self._graph_usable(p, gt):
+            # steady state: inputs go straight (H2D when they are on the host) into the graph's static buffers
+            self._load_static(p, images_u8, gt, gt_count, img_hw)
+            p["graph"].replay()
+            native.add_launch_count(p["graph_kernels"])
+            return self.loss_out.clone()
         images_u8 = images_u8.to(dev, non_blocking=True)
         gt = gt.to(dev, torch.float32, non_blocking=True)
         gt_count = gt_count.to(dev, torch.int32, non_blocking=True)
         img_hw = img_hw.to(dev, torch.int32, non_blocking=True)
         images_u8 = self._bucket(images_u8)
-        B, H, W, _ = images_u8.shape
-        p = self._plan(B, H, W)
+        if self._graph_usable(p, gt):
+            self._graph_step(p, images_u8, gt, gt_count, img_hw)
+        else:
+            self._step_body(p, images_u8, gt, gt_count, img_hw)
+        return self.loss_out.clone()
+
+    def _step_body(self, p, images_u8, gt, gt_count, img_hw):
+        """Everything of a step that runs on the device, in stream order (this is what a graph captures)."""
         self.G.zero_()
         self._mark("h2d+zero")
         self._forward(p, images_u8, img_hw)
@@ -650,7 +683,52 @@ class NativeTrainer:
         self._mark("backward")
         self._optimizer_step()
         self._mark("optimizer")
-        return torch.stack([self.scal[2] + self.scal[3], self.scal[2], self.scal[3]])
+        torch.stack([self.scal[2] + self.scal[3], self.scal[2], self.scal[3]], out=self.loss_out)
+
+    # ------------------------------------------------------------------ whole-step CUDA graph
+    def _graph_usable(self, p, gt) -> bool:
+        if not self.use_graph or self._prof is not None or p.get("graph_failed"):
+            return False
+        if self.comm is not None and getattr(self.comm, "external_sync", False):
+            return False                     # in-process towers order their streams with host barriers
+        return gt.shape[1] <= self.graph_gt_cap
+
+    def _load_static(self, p, images_u8, gt, gt_count, img_hw):
+        dst = p["in_img"]
+        H, W = images_u8.shape[1:3]
+        if (H, W) != tuple(dst.shape[1:3]):          # bucket padding: colour that preprocesses to zero
+            dst[..., 0], dst[..., 1], dst[..., 2] = self._pad_bgr()
+        dst[:, :H, :W].copy_(images_u8, non_blocking=True)
+        p["in_gt"][:, :gt.shape[1]].copy_(gt, non_blocking=True)
+        p["in_cnt"].copy_(gt_count, non_blocking=True)
+        p["in_hw"].copy_(img_hw, non_blocking=True)
+
+    def _graph_step(self, p, images_u8, gt, gt_count, img_hw):
+        """Warm-up (eager) steps of a plan, then capture + first replay.  Inputs are on the device, bucketed."""
+        p["graph_warm"] = p.get("graph_warm", 0) + 1
+        if p["graph_warm"] <= self.graph_warmup:
+            self._step_body(p, images_u8, gt, gt_count, img_hw)
+            return
+        B = images_u8.shape[0]
+        p["in_img"] = torch.empty_like(images_u8)
+        p["in_gt"] = torch.zeros(B, self.graph_gt_cap, 5, device=self.device)
+        p["in_cnt"] = torch.zeros(B, dtype=torch.int32, device=self.device)
+        p["in_hw"] = torch.zeros(B, 2, dtype=torch.int32, device=self.device)
+        self._load_static(p, images_u8, gt, gt_count, img_hw)
+        try:
+            torch.cuda.synchronize(self.device)
+            k0 = native.launch_count()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._step_body(p, p["in_img"], p["in_gt"], p["in_cnt"], p["in_hw"])
+            p["graph_kernels"] = native.launch_count() - k0     # capture counted them once: that is the first replay
+        except Exception as e:  # noqa: BLE001 - capture is an optimisation: fall back to eager launches
+            warnings.warn(f"CUDA-graph capture of the training step failed ({e}); continuing with eager launches")
+            p["graph_failed"] = True
+            self._step_body(p, images_u8, gt, gt_count, img_hw)
+            return
+        p["graph"] = g
+        g.replay()
 
     @torch.no_grad()
     def forward_loss(self, images_u8, gt, gt_count, img_hw):

@@ -60,7 +60,7 @@ class ArHostArgs(C.Structure):
     _fields_ = [("bufs", C.c_void_p * 8), ("flags", C.c_void_p * 8), ("prescale", C.c_void_p * 8),
                 ("outs", C.c_void_p * 8), ("out", C.c_void_p), ("rank", C.c_int), ("world", C.c_int), ("offset", C.c_longlong),
                 ("count", C.c_longlong), ("postscale", C.c_float), ("epoch", C.c_uint32), ("algo", C.c_int),
-                ("max_blocks", C.c_int), ("has_prescale", C.c_int), ("mc_buf", C.c_void_p), ("mc_out", C.c_void_p),
+                ("max_blocks", C.c_int), ("has_prescale", C.c_int), ("epoch_ptr", C.c_void_p), ("mc_buf", C.c_void_p), ("mc_out", C.c_void_p),
                 ("external_sync", C.c_int)]
 
 
@@ -114,6 +114,11 @@ def _ptr(t) -> C.c_void_p:
 
 def launch_count() -> int:
     return int(_load().b200_launch_count())
+
+
+def add_launch_count(n: int):
+    """Report kernels executed through a CUDA-graph replay (they bypass the launch wrappers)."""
+    _load().b200_add_launch_count(C.c_longlong(int(n)))
 
 
 def reset_launch_count():
@@ -323,6 +328,11 @@ def clip_scale(sumsq_t, clipnorm, scale):
 
 
 def adam(p, g, m, v, grad_scale, lr_t, beta1, beta2, eps):
+    """``lr_t`` may be a float or a 1-element fp32 device tensor (read on the device: CUDA-graph friendly)."""
+    if isinstance(lr_t, torch.Tensor):
+        _check(_load().b200_adam_devlr(_ptr(p), _ptr(g), _ptr(m), _ptr(v), C.c_longlong(p.numel()), _ptr(grad_scale),
+                                       _ptr(lr_t), C.c_float(beta1), C.c_float(beta2), C.c_float(eps), _stream()), "adam")
+        return
     _check(_load().b200_adam(_ptr(p), _ptr(g), _ptr(m), _ptr(v), C.c_longlong(p.numel()), _ptr(grad_scale),
                              C.c_float(lr_t), C.c_float(beta1), C.c_float(beta2), C.c_float(eps), _stream()), "adam")
 

@@ -248,6 +248,9 @@ class P2PComm:
         a.offset, a.count = offset, count
         a.postscale = postscale
         a.epoch = self.epoch
+        # the flag epoch lives in device memory (scalars + 64) and is bumped on the device after every collective,
+        # so a captured CUDA graph of a training step replays with fresh flag values
+        a.epoch_ptr = 0 if self.external_sync else self.base + self.flag_bytes + 64
         a.algo = algo
         a.max_blocks = 0
         a.has_prescale = int(has_prescale)

@@ -31,6 +31,7 @@ struct ArParams {
   long long offset, count;
   float postscale;
   uint32_t epoch;   // base flag value of this call; the call uses epoch+1 .. epoch+3
+  const uint32_t* epoch_ptr;  // device-resident epoch (CUDA-graph replay), or null
   const float* mc_buf;  // multicast address of the bucket (NVLS), or null
   float* mc_out;        // multicast address of the result buffer (NVLS), or null
   int has_prescale;
@@ -48,6 +49,12 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 
 // Block-level barrier across ranks: block b of every rank meets block b of every other rank.
 // Flag layout per rank: flags[block][peer].
+// Base flag value of this call: a kernel argument, or read from device memory so that a captured graph of the
+// collective sees a fresh epoch at every replay (a one-thread kernel bumps the counter after each collective).
+__device__ __forceinline__ uint32_t ar_epoch(const ArParams& p) { return p.epoch_ptr ? *p.epoch_ptr : p.epoch; }
+
+__global__ void epoch_bump_kernel(uint32_t* e) { *e = (*e + 4u) & 0x7fffffffu; }
+
 __device__ __forceinline__ void rank_barrier(const ArParams& p, uint32_t value) {
   if (p.external_sync) return;
   __syncthreads();
@@ -75,7 +82,7 @@ __device__ __forceinline__ float4 ld_peer(const float* p) {
 
 template <int kWorld>
 __global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(const ArParams p) {
-  rank_barrier(p, p.epoch + 1);
+  rank_barrier(p, ar_epoch(p) + 1);
   float pre[kWorld];
 #pragma unroll
   for (int r = 0; r < kWorld; ++r) pre[r] = p.has_prescale ? *p.prescale[r] : 1.f;
@@ -94,12 +101,12 @@ __global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(const ArP
     acc.x *= p.postscale; acc.y *= p.postscale; acc.z *= p.postscale; acc.w *= p.postscale;
     reinterpret_cast<float4*>(p.out + p.offset)[i] = acc;
   }
-  rank_barrier(p, p.epoch + 2);
+  rank_barrier(p, ar_epoch(p) + 2);
 }
 
 template <int kWorld>
 __global__ void __launch_bounds__(kArThreads) allreduce_twoshot_kernel(const ArParams p) {
-  rank_barrier(p, p.epoch + 1);
+  rank_barrier(p, ar_epoch(p) + 1);
   float pre[kWorld];
 #pragma unroll
   for (int r = 0; r < kWorld; ++r) pre[r] = p.has_prescale ? *p.prescale[r] : 1.f;
@@ -138,7 +145,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_twoshot_kernel(const ArP
     }
   }
   __threadfence_system();
-  rank_barrier(p, p.epoch + 2);
+  rank_barrier(p, ar_epoch(p) + 2);
   // phase 2: all-gather the reduced slices (4 loads in flight per thread per peer slice)
 #pragma unroll
   for (int r = 0; r < kWorld; ++r) {
@@ -155,7 +162,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_twoshot_kernel(const ArP
         if (i0 + u * stride < s1) reinterpret_cast<float4*>(p.out + p.offset)[i0 + u * stride] = v[u];
     }
   }
-  rank_barrier(p, p.epoch + 3);
+  rank_barrier(p, ar_epoch(p) + 3);
 }
 
 // Fused reduce-scatter + all-gather, push flavour: each rank reduces its 1/N slice from all peers
@@ -164,7 +171,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_twoshot_kernel(const ArP
 // is no second phase and no intermediate copy in the bucket.
 template <int kWorld>
 __global__ void __launch_bounds__(kArThreads) allreduce_push_kernel(const ArParams p) {
-  rank_barrier(p, p.epoch + 1);
+  rank_barrier(p, ar_epoch(p) + 1);
   float pre[kWorld];
 #pragma unroll
   for (int r = 0; r < kWorld; ++r) pre[r] = p.has_prescale ? *p.prescale[r] : 1.f;
@@ -201,7 +208,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_push_kernel(const ArPara
     }
   }
   __threadfence_system();
-  rank_barrier(p, p.epoch + 2);
+  rank_barrier(p, ar_epoch(p) + 2);
 }
 
 
@@ -241,7 +248,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_nvls_kernel(const ArPara
       __threadfence_system();
     }
   }
-  rank_barrier(p, p.epoch + 1);
+  rank_barrier(p, ar_epoch(p) + 1);
   const long long per = (n4 + kWorld - 1) / kWorld;
   const long long lo = p.rank * per;
   const long long hi = lo + per < n4 ? lo + per : n4;
@@ -265,13 +272,13 @@ __global__ void __launch_bounds__(kArThreads) allreduce_nvls_kernel(const ArPara
     multimem_st(out + i * 4, v);
   }
   __threadfence_system();
-  rank_barrier(p, p.epoch + 2);
+  rank_barrier(p, ar_epoch(p) + 2);
 }
 
 // Broadcast through the switch: the root stores once, every rank's result buffer receives it.
 template <int kWorld>
 __global__ void __launch_bounds__(kArThreads) broadcast_nvls_kernel(const ArParams p, int root) {
-  rank_barrier(p, p.epoch + 1);
+  rank_barrier(p, ar_epoch(p) + 1);
   if (p.rank == root) {
     const long long n4 = p.count >> 2;
     const float4* src = reinterpret_cast<const float4*>(p.bufs[root] + p.offset);
@@ -280,12 +287,12 @@ __global__ void __launch_bounds__(kArThreads) broadcast_nvls_kernel(const ArPara
       multimem_st(p.mc_out + p.offset + i * 4, src[i]);
     __threadfence_system();
   }
-  rank_barrier(p, p.epoch + 2);
+  rank_barrier(p, ar_epoch(p) + 2);
 }
 
 template <int kWorld>
 __global__ void __launch_bounds__(kArThreads) broadcast_kernel(const ArParams p, int root) {
-  rank_barrier(p, p.epoch + 1);
+  rank_barrier(p, ar_epoch(p) + 1);
   if (p.rank != root) {
     const long long n4 = p.count >> 2;
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
@@ -294,7 +301,7 @@ __global__ void __launch_bounds__(kArThreads) broadcast_kernel(const ArParams p,
       reinterpret_cast<float4*>(p.out + p.offset)[i] = v;
     }
   }
-  rank_barrier(p, p.epoch + 2);
+  rank_barrier(p, ar_epoch(p) + 2);
 }
 
 __global__ void scale_copy_kernel(const float* __restrict__ in, float* __restrict__ out, long long n4,
@@ -335,6 +342,7 @@ static int fill(ArParams& p, const B200ArHostArgs* a) {
   p.postscale = a->postscale;
   p.epoch = a->epoch;
   p.has_prescale = a->has_prescale;
+  p.epoch_ptr = a->epoch_ptr;
   p.mc_buf = static_cast<const float*>(a->mc_buf);
   p.mc_out = static_cast<float*>(a->mc_out);
   p.external_sync = a->external_sync;
@@ -398,6 +406,7 @@ int b200_allreduce_host(const B200ArHostArgs* a, void* stream_) {
       return set_error(-1, "allreduce: world size %d not instantiated (1, 2, 4, 8)", p.world);
   }
 #undef B200_AR_LAUNCH
+  if (a->epoch_ptr) epoch_bump_kernel<<<1, 1, 0, stream>>>(a->epoch_ptr);
   return check_launch("allreduce_kernel");
 }
 
@@ -421,6 +430,7 @@ int b200_broadcast_host(const B200ArHostArgs* a, int root, void* stream_) {
       case 8: broadcast_nvls_kernel<8><<<blocks, kArThreads, 0, stream>>>(p, root); break;
       default: return set_error(-1, "broadcast: world size %d not instantiated", p.world);
     }
+    if (a->epoch_ptr) epoch_bump_kernel<<<1, 1, 0, stream>>>(a->epoch_ptr);
     return check_launch("broadcast_nvls_kernel");
   }
   switch (p.world) {
@@ -429,6 +439,7 @@ int b200_broadcast_host(const B200ArHostArgs* a, int root, void* stream_) {
     case 8: broadcast_kernel<8><<<blocks, kArThreads, 0, stream>>>(p, root); break;
     default: return set_error(-1, "broadcast: world size %d not instantiated", p.world);
   }
+  if (a->epoch_ptr) epoch_bump_kernel<<<1, 1, 0, stream>>>(a->epoch_ptr);
   return check_launch("broadcast_kernel");
 }
 

@@ -80,4 +80,7 @@ const char* b200_last_error(void) { return b200::g_last_error; }
 int b200_ops_abi_version(void) { return 1; }
 long long b200_launch_count(void) { return b200::g_launch_count.load(); }
 void b200_reset_launch_count(void) { b200::g_launch_count.store(0); }
+/* Kernels executed by replaying a captured CUDA graph never pass through the launch wrappers: the owner of the
+ * graph reports them here (count taken while the graph was captured). */
+void b200_add_launch_count(long long n) { b200::g_launch_count.fetch_add(n); }
 }

@@ -40,9 +40,10 @@ __global__ void clip_scale_kernel(const float* __restrict__ sumsq, float clipnor
 }
 
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                            float* __restrict__ v, long long n, const float* __restrict__ grad_scale, float lr_t,
-                            float b1, float b2, float eps) {
+                            float* __restrict__ v, long long n, const float* __restrict__ grad_scale, float lr_host,
+                            float b1, float b2, float eps, const float* __restrict__ lr_dev) {
   const float gs = grad_scale ? *grad_scale : 1.f;
+  const float lr_t = lr_dev ? *lr_dev : lr_host;   // device copy: the value can change between CUDA-graph replays
   const long long n4 = n >> 2;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -95,8 +96,8 @@ int b200_clip_scale(const float* sumsq, float clipnorm, float* scale, void* stre
   return check_launch("clip_scale_kernel");
 }
 
-int b200_adam(float* p, const float* g, float* m, float* v, long long n, const float* grad_scale, float lr_t,
-              float beta1, float beta2, float eps, void* stream) {
+static int adam_launch(float* p, const float* g, float* m, float* v, long long n, const float* grad_scale, float lr_t,
+                       float beta1, float beta2, float eps, const float* lr_dev, void* stream) {
   if ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
        reinterpret_cast<uintptr_t>(v)) & 15)
     return set_error(-1, "adam: buffers must be 16-byte aligned");
@@ -105,8 +106,20 @@ int b200_adam(float* p, const float* g, float* m, float* v, long long n, const f
   if (gr > cap) gr = cap;
   if (gr < 1) gr = 1;
   adam_kernel<<<static_cast<unsigned>(gr), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, v, n, grad_scale, lr_t,
-                                                                                       beta1, beta2, eps);
+                                                                                       beta1, beta2, eps, lr_dev);
   return check_launch("adam_kernel");
+}
+
+int b200_adam(float* p, const float* g, float* m, float* v, long long n, const float* grad_scale, float lr_t,
+              float beta1, float beta2, float eps, void* stream) {
+  return adam_launch(p, g, m, v, n, grad_scale, lr_t, beta1, beta2, eps, nullptr, stream);
+}
+
+/* Same update with the bias-corrected learning rate read from device memory (for CUDA-graph replay). */
+int b200_adam_devlr(float* p, const float* g, float* m, float* v, long long n, const float* grad_scale,
+                    const float* lr_t_dev, float beta1, float beta2, float eps, void* stream) {
+  if (!lr_t_dev) return set_error(-1, "adam: lr_t_dev is null");
+  return adam_launch(p, g, m, v, n, grad_scale, 0.f, beta1, beta2, eps, lr_t_dev, stream);
 }
 
 }  // extern "C"

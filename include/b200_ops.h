@@ -22,6 +22,7 @@ int b200_ops_abi_version(void);
 /* Number of kernel launches issued by this library in this process (bench.py gpu_launches). */
 long long b200_launch_count(void);
 void b200_reset_launch_count(void);
+void b200_add_launch_count(long long n); /* kernels run by a CUDA-graph replay (counted at capture time) */
 
 /* ------------------------------------------------------------------ convolution (tcgen05)
  * Implicit-GEMM convolution on the 5th-gen tensor cores: TMA tiled loads (zero-filled halos)
@@ -165,6 +166,9 @@ int b200_sumsq(const float* x, long long n, float* out, void* stream);
  * m,v update; p -= lr_t * m / (sqrt(v) + eps) with lr_t = lr*sqrt(1-b2^t)/(1-b1^t). */
 int b200_adam(float* p, const float* g, float* m, float* v, long long n, const float* grad_scale, float lr_t,
               float beta1, float beta2, float eps, void* stream);
+/* Same update, bias-corrected learning rate read from device memory (a captured CUDA graph replays with new values). */
+int b200_adam_devlr(float* p, const float* g, float* m, float* v, long long n, const float* grad_scale,
+                    const float* lr_t_dev, float beta1, float beta2, float eps, void* stream);
 /* clip factor: scale[0] = (norm >= clip) ? clip / norm : 1 with norm = sqrt(sumsq[0]). */
 int b200_clip_scale(const float* sumsq, float clipnorm, float* scale, void* stream);
 
@@ -209,6 +213,8 @@ typedef struct {
                                4 NVLS: in-switch reduce (multimem.ld_reduce) + multicast store (needs mc_buf/mc_out) */
   int max_blocks;           /* <= 64; 0 = default */
   int has_prescale;
+  unsigned int* epoch_ptr;  /* device counter holding the flag epoch (bumped by 4 after the call); null: use `epoch`.
+                               With it a captured CUDA graph of the collective can be replayed. */
   void* mc_buf;             /* multicast (NVLS) address of the bucket, or null */
   void* mc_out;             /* multicast (NVLS) address of the result buffer, or null */
   int external_sync;        /* 1: the caller orders the ranks with events (ranks = threads of one process); the
