@@ -66,6 +66,7 @@ class LibraryTrainer:
         self.num_classes = num_classes
         self.clipnorm = clipnorm
         self.model = (model or RetinaNet(num_classes, backbone)).to(self.device)
+        self.num_classes = self.model.num_classes
         if freeze_backbone:
             self.model.freeze_backbone()
         if self.device.type == "cuda":

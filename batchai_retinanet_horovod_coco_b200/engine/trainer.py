@@ -105,6 +105,7 @@ class NativeTrainer:
         self.graph_warmup = 2        # eager steps on a plan before it is captured
         self.graph_gt_cap = 128      # ground-truth boxes per image the captured step can take
         self.model = model if model is not None else RetinaNet(num_classes, backbone)
+        self.num_classes = self.model.num_classes      # a model that is passed in decides, not the default argument
         if freeze_backbone:
             self.model.freeze_backbone()
         self.backbone_name = self.model.backbone_name

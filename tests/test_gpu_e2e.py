@@ -1,0 +1,33 @@
+"""End-to-end learning check on the GPU engines: overfit eight synthetic images, then run the prediction graph and
+the VOC-style evaluator on them.  Ties together target assignment, focal / smooth-L1, the hand-written backward,
+Adam, box decoding, NMS and evaluation; it is the test that caught the engine ignoring a passed-in model's class
+count (anything but 80 classes trained the wrong logits)."""
+import pytest
+import torch
+
+from batchai_retinanet_horovod_coco_b200 import models
+from batchai_retinanet_horovod_coco_b200.preprocessing.synthetic import SyntheticGenerator
+from batchai_retinanet_horovod_coco_b200.utils.eval import evaluate, mean_ap
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("backbone,steps", [("resnet50", 300), ("vgg16", 300)])
+def test_overfit_then_detect(backbone, steps):
+    from batchai_retinanet_horovod_coco_b200.engine import create_trainer
+    torch.manual_seed(0)
+    gen = SyntheticGenerator(num_images=8, image_hw=(256, 320), classes=3, boxes_per_image=3, seed=3, batch_size=8,
+                             image_min_side=256, image_max_side=320, shuffle_groups=False)
+    model = models.backbone(backbone).retinanet(gen.num_classes())
+    tr = create_trainer(model, "cuda", lr=1e-4, clipnorm=0.0, batch=8, image_hw=(256, 320))
+    assert tr.num_classes == 3
+    first = None
+    for s in range(steps):
+        loss = tr.train_step(*gen.next_compact(pin=True))
+        if s == 0:
+            first = loss.tolist()
+    last = loss.tolist()
+    assert 0.9 < first[2] < 1.4, first          # focal loss at the 0.01 prior starts near 1.1 whatever the class count
+    assert last[0] < 0.1 * first[0], (first, last)
+    aps = evaluate(gen, lambda x: tr.predict(x), iou_threshold=0.5, score_threshold=0.05, max_detections=100)
+    assert mean_ap(aps) > 0.9, aps
