@@ -12,14 +12,15 @@ from batchai_retinanet_horovod_coco_b200.utils.eval import evaluate, mean_ap
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("backbone,steps", [("resnet50", 300), ("vgg16", 300)])
-def test_overfit_then_detect(backbone, steps):
+@pytest.mark.parametrize("backbone,steps,hw", [("resnet50", 300, (256, 320)), ("vgg16", 300, (256, 320)),
+                                               ("resnet50", 300, (250, 310))])   # last: padded up to the 64-px shape bucket
+def test_overfit_then_detect(backbone, steps, hw):
     from batchai_retinanet_horovod_coco_b200.engine import create_trainer
     torch.manual_seed(0)
-    gen = SyntheticGenerator(num_images=8, image_hw=(256, 320), classes=3, boxes_per_image=3, seed=3, batch_size=8,
-                             image_min_side=256, image_max_side=320, shuffle_groups=False)
+    gen = SyntheticGenerator(num_images=8, image_hw=hw, classes=3, boxes_per_image=3, seed=3, batch_size=8,
+                             image_min_side=hw[0], image_max_side=hw[1], shuffle_groups=False)
     model = models.backbone(backbone).retinanet(gen.num_classes())
-    tr = create_trainer(model, "cuda", lr=1e-4, clipnorm=0.0, batch=8, image_hw=(256, 320))
+    tr = create_trainer(model, "cuda", lr=1e-4, clipnorm=0.0, batch=8, image_hw=hw)
     assert tr.num_classes == 3
     first = None
     for s in range(steps):

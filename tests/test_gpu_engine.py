@@ -141,3 +141,20 @@ def test_graph_replay_matches_eager_steps():
         assert torch.allclose(x, y, rtol=1e-4 if i < 4 else 1e-2, atol=1e-4), (i, la, lb)
     torch.cuda.synchronize()
     assert (a.P - b.P).abs().max().item() < 5e-4 and (a.P != 0).any()
+
+
+def test_freeze_backbone_trains_only_fpn_and_heads():
+    """--freeze-backbone (reference train.py:82,375): 36 trainable tensors, backbone weights never move."""
+    from batchai_retinanet_horovod_coco_b200.engine.trainer import NativeTrainer
+    torch.manual_seed(0)
+    B, H, W = 2, 160, 224
+    nt = NativeTrainer("resnet50", 80, device="cuda", batch=B, image_hw=(H, W), lr=1e-4, clipnorm=0.0, freeze_backbone=True)
+    assert sum(1 for c in nt.convs if c.trainable) == 18 and not nt.stem.trainable       # 18 convs = 36 tensors
+    assert nt.n_train < 15_000_000 < nt.n_params
+    frozen0 = nt.P[nt.n_train:].clone()
+    head0 = nt.P[:nt.n_train].clone()
+    img, gt, cnt, hw = _inputs(B, H, W)
+    losses = [nt.train_step(img, gt, cnt, hw)[0].item() for _ in range(6)]
+    assert losses[-1] < losses[0], losses
+    assert torch.equal(nt.P[nt.n_train:], frozen0)
+    assert not torch.equal(nt.P[:nt.n_train], head0)
