@@ -209,6 +209,10 @@ def parse_args(args):
     parser.add_argument("--image-max-side", help="Rescale the image if the largest side is larger than max_side.", type=int, default=1333)
     # ---- extensions (not in the reference) ----
     parser.add_argument("--cpu", help="(extension) force the CPU spec engine.", action="store_true")
+    parser.add_argument("--workers", help="(extension) background threads producing batches (Keras fit_generator "
+                        "uses 1); 0 loads in the training thread.", type=int, default=min(8, os.cpu_count() or 1))
+    parser.add_argument("--max-queue-size", help="(extension) batches kept ready ahead of the training step "
+                        "(Keras default 10).", type=int, default=10)
     parser.add_argument("--engine", help="(extension) auto | native | spec", default="auto")
     parser.add_argument("--lr", help="(extension) Adam learning rate (reference hard-codes 1e-5).", type=float, default=1e-5)
     parser.add_argument("--clipnorm", help="(extension) global-norm clip (reference hard-codes 0.001).", type=float, default=0.001)
@@ -217,8 +221,11 @@ def parse_args(args):
     return check_args(parser.parse_args(args))
 
 
-def fit_generator(trainer, generator, steps_per_epoch, epochs, callbacks, initial_epoch=0, verbose=1):
-    """Keras ``fit_generator`` over the compact batches (reference train.py:444-450)."""
+def fit_generator(trainer, generator, steps_per_epoch, epochs, callbacks, initial_epoch=0, verbose=1, workers=1,
+                  max_queue_size=10):
+    """Keras ``fit_generator`` over the compact batches (reference train.py:444-450): batches are produced ahead of
+    the training step by ``workers`` background threads into a queue of ``max_queue_size`` (Keras defaults 1 / 10)."""
+    from ..preprocessing.prefetch import BatchPrefetcher
     params = {"epochs": epochs, "steps": steps_per_epoch, "verbose": verbose}
     cbs = list(callbacks)
     if verbose and hvd.rank() == 0:
@@ -227,11 +234,12 @@ def fit_generator(trainer, generator, steps_per_epoch, epochs, callbacks, initia
     history = []
     cl.on_train_begin({})
     pin = trainer.device.type == "cuda"
+    batches = BatchPrefetcher(generator, workers=workers, max_queue_size=max_queue_size, pin=pin)
     for epoch in range(initial_epoch, epochs):
         cl.on_epoch_begin(epoch, {})
         sums = torch.zeros(3, device=trainer.device)
         for step in range(steps_per_epoch):
-            batch = generator.next_compact(pin=pin)
+            batch = batches.next()
             out = trainer.train_step(*batch)
             sums += out.detach().to(sums.device)
             if verbose and ((step + 1) % max(1, steps_per_epoch // 10) == 0 or step + 1 == steps_per_epoch):
@@ -241,6 +249,7 @@ def fit_generator(trainer, generator, steps_per_epoch, epochs, callbacks, initia
         logs = {"loss": m[0], "regression_loss": m[1], "classification_loss": m[2]}
         cl.on_epoch_end(epoch, logs)
         history.append(logs)
+    batches.close()
     cl.on_train_end({})
     return history
 
@@ -290,7 +299,8 @@ def main(args=None):
         trainer.load_optimizer_state(state)
     callbacks = create_callbacks(model, model, prediction_model, validation_generator, args)
     history = fit_generator(trainer, train_generator, steps_per_epoch=args.steps, epochs=args.epochs, callbacks=callbacks,
-                            initial_epoch=initial_epoch, verbose=1)
+                            initial_epoch=initial_epoch, verbose=1, workers=args.workers,
+                            max_queue_size=args.max_queue_size)
     if args.timeline:
         hvd.timeline_stop()
     return history

@@ -95,7 +95,9 @@ class Generator:
 
     def random_transform_group_entry(self, image, annotations):
         if self.transform_generator:
-            transform = adjust_transform_for_image(next(self.transform_generator), image,
+            with self.lock:      # Python generators are not re-entrant; prefetch workers share this one
+                matrix = next(self.transform_generator)
+            transform = adjust_transform_for_image(matrix, image,
                                                    self.transform_parameters.relative_translation)
             image = apply_transform(transform, image, self.transform_parameters)
             annotations = annotations.copy()

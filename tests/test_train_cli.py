@@ -178,3 +178,30 @@ def test_experimental_backbone_cli_run(tmp_path):
     m, st = load_full_model(str(snap / "checkpoint-01.h5"))
     assert m.backbone_name == "mobilenet128_0.25" and st["iterations"] == 2
     assert "conv_dw_1/depthwise_kernel:0" in st["slots"] and "conv_pw_13_bn/gamma:0" in st["slots"]
+
+
+def test_batch_prefetcher_order_coverage_and_errors():
+    from batchai_retinanet_horovod_coco_b200.preprocessing.prefetch import BatchPrefetcher
+    from batchai_retinanet_horovod_coco_b200.preprocessing.synthetic import SyntheticGenerator
+    from batchai_retinanet_horovod_coco_b200.utils.transform import random_transform_generator
+    mk = lambda: SyntheticGenerator(num_images=12, image_hw=(64, 96), classes=3, batch_size=2, shuffle_groups=False,
+                                    image_min_side=64, image_max_side=96)
+    ref = mk()
+    want = [ref.next_compact()[1] for _ in range(6)]
+    with BatchPrefetcher(mk(), workers=1, max_queue_size=3) as pf:              # one worker: the generator's own order
+        got = [pf.next()[1] for _ in range(6)]
+    assert all(torch.equal(a, b) for a, b in zip(want, got))
+    g = mk()
+    g.transform_generator = random_transform_generator(flip_x_chance=0.5)       # shared, not re-entrant: must be locked
+    with BatchPrefetcher(g, workers=4, max_queue_size=4) as pf:                 # several workers: every group, any order
+        got = [pf.next() for _ in range(12)]
+    assert all(b[0].dtype == torch.uint8 and b[0].shape == (2, 64, 96, 3) for b in got)
+    with BatchPrefetcher(mk(), workers=0) as pf:                                # synchronous mode
+        assert torch.equal(pf.next()[1], want[0])
+
+    class Broken(SyntheticGenerator):
+        def load_image(self, i):
+            raise OSError("unreadable image")
+    with pytest.raises(OSError, match="unreadable"):
+        with BatchPrefetcher(Broken(num_images=4, image_hw=(32, 32), classes=2, batch_size=2), workers=2) as pf:
+            pf.next()
