@@ -80,6 +80,24 @@ class Conv:
         return flat[self.b_off:self.b_off + self.cout]
 
 
+class StepHandle:
+    """Result of ``train_step_async``.  ``loss`` is a device tensor (stream-ordered, always valid);
+    ``loss_cpu()`` returns the same triple from pinned host memory after waiting only for the forward half of the
+    step -- call it before issuing the next step (a later call falls back to the device tensor)."""
+
+    def __init__(self, trainer):
+        self._t = trainer
+        self._step = trainer._steps_issued
+        self.loss = trainer.loss_out.clone()
+
+    def loss_cpu(self) -> torch.Tensor:
+        t = self._t
+        if t._steps_issued != self._step:
+            return self.loss.cpu()
+        t._ev_front.synchronize()
+        return t.loss_host.clone()
+
+
 class NativeTrainer:
     def __init__(self, backbone: str = "resnet50", num_classes: int = 80, device="cuda", batch: int = 8,
                  image_hw=(800, 1333), lr: float = 1e-5, clipnorm: float = 0.001, distributed: bool = False,
@@ -230,6 +248,11 @@ class NativeTrainer:
         self.zeros64 = torch.zeros(64, device=dev)
         self.lr_dev = torch.zeros(1, device=dev)          # bias-corrected Adam step size of the current step
         self.loss_out = torch.zeros(3, device=dev)        # [loss, regression_loss, classification_loss]
+        self.loss_host = torch.zeros(3).pin_memory()      # the same triple, copied out right after the loss kernels
+        self._ev_front = torch.cuda.Event()               # forward + losses of the latest step are done
+        self._ev_h2d = torch.cuda.Event()
+        self._copy_stream = torch.cuda.Stream(device=dev)
+        self._steps_issued = 0
         self.stem_wp = torch.zeros(64, 256, device=dev, dtype=BF16)
         self._bind_extra()
 
@@ -590,6 +613,7 @@ class NativeTrainer:
     def _begin_step(self):
         """Host-side per-step scalars, written to device memory OUTSIDE any captured graph."""
         self.iterations += 1
+        self._steps_issued += 1
         t = self.iterations
         self.lr_dev.fill_(self.lr * math.sqrt(1.0 - self.beta2 ** t) / (1.0 - self.beta1 ** t))
 
@@ -650,17 +674,28 @@ class NativeTrainer:
         images uint8 [B,H,W,3] BGR, gt fp32 [B,G,5] (x1,y1,x2,y2,label), gt_count int32 [B],
         img_hw int32 [B,2] un-padded sizes.  Returns a device tensor [loss, regression_loss,
         classification_loss] (the Keras metric names of reference train.py:99-102)."""
+        return self.train_step_async(images_u8, gt, gt_count, img_hw).loss
+
+    def train_step_async(self, images_u8, gt, gt_count, img_hw) -> "StepHandle":
+        """Same step, returning a handle: ``handle.loss`` is the device tensor ``train_step`` returns,
+        ``handle.loss_cpu()`` the same three numbers on the host, available as soon as the forward pass and
+        the losses are done -- backward, allreduce and Adam keep running, and the next call's host-to-device
+        copy of its inputs overlaps them (it only waits for this step to have consumed its inputs)."""
         dev = self.device
         B, H, W = images_u8.shape[:3]
         b = self.shape_bucket
         p = self._plan(B, -(-H // b) * b, -(-W // b) * b)
         self._begin_step()
+        main = torch.cuda.current_stream(dev)
         if "graph" in p and self._graph_usable(p, gt):
             # steady state: inputs go straight (H2D when they are on the host) into the graph's static buffers
             self._load_static(p, images_u8, gt, gt_count, img_hw)
-            p["graph"].replay()
+            ga, gb = p["graph"]
+            ga.replay()
+            self._ev_front.record(main)
+            gb.replay()
             native.add_launch_count(p["graph_kernels"])
-            return self.loss_out.clone()
+            return StepHandle(self)
         images_u8 = images_u8.to(dev, non_blocking=True)
         gt = gt.to(dev, torch.float32, non_blocking=True)
         gt_count = gt_count.to(dev, torch.int32, non_blocking=True)
@@ -670,23 +705,32 @@ class NativeTrainer:
             self._graph_step(p, images_u8, gt, gt_count, img_hw)
         else:
             self._step_body(p, images_u8, gt, gt_count, img_hw)
-        return self.loss_out.clone()
+        return StepHandle(self)
 
-    def _step_body(self, p, images_u8, gt, gt_count, img_hw):
-        """Everything of a step that runs on the device, in stream order (this is what a graph captures)."""
+    def _step_front(self, p, images_u8, gt, gt_count, img_hw):
+        """Forward + losses; the loss triple is final here and goes to pinned host memory."""
         self.G.zero_()
         self._mark("h2d+zero")
         self._forward(p, images_u8, img_hw)
         self._mark("forward")
         self._losses(p, gt, gt_count, img_hw)
+        torch.stack([self.scal[2] + self.scal[3], self.scal[2], self.scal[3]], out=self.loss_out)
+        self.loss_host.copy_(self.loss_out, non_blocking=True)
         self._mark("losses")
+
+    def _step_back(self, p):
         self._backward(p)
         self._mark("backward")
         self._optimizer_step()
         self._mark("optimizer")
-        torch.stack([self.scal[2] + self.scal[3], self.scal[2], self.scal[3]], out=self.loss_out)
 
-    # ------------------------------------------------------------------ whole-step CUDA graph
+    def _step_body(self, p, images_u8, gt, gt_count, img_hw):
+        """A whole step with plain launches, in stream order."""
+        self._step_front(p, images_u8, gt, gt_count, img_hw)
+        self._ev_front.record(torch.cuda.current_stream(self.device))
+        self._step_back(p)
+
+    # ------------------------------------------------------------------ whole-step CUDA graphs
     def _graph_usable(self, p, gt) -> bool:
         if not self.use_graph or self._prof is not None or p.get("graph_failed"):
             return False
@@ -695,14 +739,24 @@ class NativeTrainer:
         return gt.shape[1] <= self.graph_gt_cap
 
     def _load_static(self, p, images_u8, gt, gt_count, img_hw):
-        dst = p["in_img"]
-        H, W = images_u8.shape[1:3]
-        if (H, W) != tuple(dst.shape[1:3]):          # bucket padding: colour that preprocesses to zero
-            dst[..., 0], dst[..., 1], dst[..., 2] = self._pad_bgr()
-        dst[:, :H, :W].copy_(images_u8, non_blocking=True)
-        p["in_gt"][:, :gt.shape[1]].copy_(gt, non_blocking=True)
-        p["in_cnt"].copy_(gt_count, non_blocking=True)
-        p["in_hw"].copy_(img_hw, non_blocking=True)
+        """Inputs -> the graphs' static buffers.  Host tensors are copied on a side stream that only waits for the
+        PREVIOUS step's front half (which consumed the buffers), so the transfer overlaps that step's backward."""
+        main = torch.cuda.current_stream(self.device)
+        side = self._copy_stream if not images_u8.is_cuda else None
+        if side is not None:
+            side.wait_event(self._ev_front)
+        with torch.cuda.stream(side if side is not None else main):
+            dst = p["in_img"]
+            H, W = images_u8.shape[1:3]
+            if (H, W) != tuple(dst.shape[1:3]):          # bucket padding: colour that preprocesses to zero
+                dst[..., 0], dst[..., 1], dst[..., 2] = self._pad_bgr()
+            dst[:, :H, :W].copy_(images_u8, non_blocking=True)
+            p["in_gt"][:, :gt.shape[1]].copy_(gt, non_blocking=True)
+            p["in_cnt"].copy_(gt_count, non_blocking=True)
+            p["in_hw"].copy_(img_hw, non_blocking=True)
+        if side is not None:
+            self._ev_h2d.record(side)
+            main.wait_event(self._ev_h2d)
 
     def _graph_step(self, p, images_u8, gt, gt_count, img_hw):
         """Warm-up (eager) steps of a plan, then capture + first replay.  Inputs are on the device, bucketed."""
@@ -719,17 +773,21 @@ class NativeTrainer:
         try:
             torch.cuda.synchronize(self.device)
             k0 = native.launch_count()
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self._step_body(p, p["in_img"], p["in_gt"], p["in_cnt"], p["in_hw"])
+            ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(ga):
+                self._step_front(p, p["in_img"], p["in_gt"], p["in_cnt"], p["in_hw"])
+            with torch.cuda.graph(gb):
+                self._step_back(p)
             p["graph_kernels"] = native.launch_count() - k0     # capture counted them once: that is the first replay
         except Exception as e:  # noqa: BLE001 - capture is an optimisation: fall back to eager launches
             warnings.warn(f"CUDA-graph capture of the training step failed ({e}); continuing with eager launches")
             p["graph_failed"] = True
             self._step_body(p, images_u8, gt, gt_count, img_hw)
             return
-        p["graph"] = g
-        g.replay()
+        p["graph"] = (ga, gb)
+        ga.replay()
+        self._ev_front.record(torch.cuda.current_stream(self.device))
+        gb.replay()
 
     @torch.no_grad()
     def forward_loss(self, images_u8, gt, gt_count, img_hw):

@@ -155,9 +155,16 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    step_async = getattr(trainer, "train_step_async", None)
+
     def run(n, sets, read_loss):
         last = None
         for i in range(n):
+            if read_loss and step_async is not None:
+                # public API: the handle's loss_cpu() is the device->host read of the step's result (loss triple);
+                # it is ready after the forward half, so the next step's H2D copy overlaps this step's backward
+                last = step_async(*sets[i % len(sets)]).loss_cpu()
+                continue
             last = trainer.train_step(*sets[i % len(sets)])
             if read_loss:
                 last = last.cpu()  # device->host read of the step's result (loss triple)

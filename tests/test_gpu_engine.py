@@ -158,3 +158,21 @@ def test_freeze_backbone_trains_only_fpn_and_heads():
     assert losses[-1] < losses[0], losses
     assert torch.equal(nt.P[nt.n_train:], frozen0)
     assert not torch.equal(nt.P[:nt.n_train], head0)
+
+
+def test_async_step_handle_returns_the_same_loss_early():
+    """train_step_async: loss_cpu() (pinned copy taken after the forward half) == the device tensor of train_step."""
+    from batchai_retinanet_horovod_coco_b200.engine.trainer import NativeTrainer
+    torch.manual_seed(0)
+    B, H, W = 2, 160, 224
+    nt = NativeTrainer("resnet50", 80, device="cuda", batch=B, image_hw=(H, W), lr=1e-4, clipnorm=0.0)
+    for step in range(6):                                    # eager warm-up steps, capture, replays
+        batch = [t.pin_memory() for t in _inputs(B, H, W, seed=step)]
+        h = nt.train_step_async(*batch)
+        early = h.loss_cpu()
+        assert torch.equal(early, h.loss.cpu()), (step, early, h.loss)
+        assert torch.isfinite(early).all() and early[0] > 0
+    h1 = nt.train_step_async(*batch)
+    h2 = nt.train_step_async(*batch)
+    assert torch.equal(h1.loss_cpu(), h1.loss.cpu())         # stale handle: falls back to its own device tensor
+    assert torch.equal(h2.loss_cpu(), h2.loss.cpu())
