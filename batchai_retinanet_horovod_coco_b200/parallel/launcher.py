@@ -46,7 +46,9 @@ def parse(argv):
     return np_, argv[i:]
 
 
-def launch(np_: int, cmd, env_extra=None, timeout=None) -> int:
+def launch(np_: int, cmd, env_extra=None, timeout=None, log_dir=None) -> int:
+    """``log_dir``: write each rank's output to ``stdout-<rank>.txt`` / ``stderr-<rank>.txt`` there (rank 0 is
+    also echoed to the console), as Batch AI does under ``stdOutErrPathPrefix`` (reference ``training_job.json:9``)."""
     job = uuid.uuid4().hex[:12]
     port = _free_port()
     procs = []
@@ -58,7 +60,12 @@ def launch(np_: int, cmd, env_extra=None, timeout=None) -> int:
                     "OMPI_COMM_WORLD_RANK": str(r), "OMPI_COMM_WORLD_SIZE": str(np_),
                     "OMPI_COMM_WORLD_LOCAL_RANK": str(r), "OMPI_COMM_WORLD_LOCAL_SIZE": str(np_)})
         env.update(env_extra or {})
-        procs.append(subprocess.Popen(cmd, env=env, start_new_session=True))
+        out = err = None
+        if log_dir and r > 0:
+            os.makedirs(log_dir, exist_ok=True)
+            out = open(os.path.join(log_dir, f"stdout-{r}.txt"), "w")
+            err = open(os.path.join(log_dir, f"stderr-{r}.txt"), "w")
+        procs.append(subprocess.Popen(cmd, env=env, start_new_session=True, stdout=out, stderr=err))
     t0 = time.time()
     rc = 0
     alive = set(range(np_))
@@ -94,8 +101,58 @@ def launch(np_: int, cmd, env_extra=None, timeout=None) -> int:
     return rc
 
 
+def load_job(path: str, mount_root: str | None = None):
+    """Job spec in the layout of the reference's ``training_job.json``: ``properties.nodeCount``,
+    ``customToolkitSettings.processCount`` / ``commandLine``, ``stdOutErrPathPrefix`` and ``outputDirectories``.
+
+    Returns ``(np, argv, env, log_dir)``.  ``$AZ_BATCHAI_MOUNT_ROOT`` resolves to ``mount_root`` (default: the
+    directory of the spec), every output directory ``id`` becomes ``$AZ_BATCHAI_OUTPUT_<id>`` and is created, and a
+    leading ``mpirun ...`` / ``horovodrun ...`` in the command line is dropped together with its flags (this launcher
+    takes its place).  ``nodeCount`` > 1 is folded onto this node with a warning (NVLink does not leave the box).
+    """
+    import json
+    import shlex
+    with open(path) as f:
+        props = json.load(f).get("properties", {})
+    if int(props.get("nodeCount", 1)) != 1:   # the reference's own spec says 2 nodes x 4 GPUs: same 8 ranks, one box
+        sys.stderr.write("[launcher] job spec asks for %s nodes; running all %s ranks on this node\n"
+                         % (props.get("nodeCount"), tk_count(props)))
+    tk = props.get("customToolkitSettings", {})
+    env = {"AZ_BATCHAI_MOUNT_ROOT": os.path.abspath(mount_root or os.path.dirname(os.path.abspath(path)))}
+
+    def expand(s: str) -> str:
+        return os.path.expandvars(_subst(s, env))
+
+    for d in props.get("outputDirectories", []):
+        out = os.path.join(expand(d.get("pathPrefix", ".")), d.get("pathSuffix", ""))
+        os.makedirs(out, exist_ok=True)
+        env["AZ_BATCHAI_OUTPUT_" + d["id"]] = out
+    log_dir = expand(props["stdOutErrPathPrefix"]) if props.get("stdOutErrPathPrefix") else None
+    argv = [expand(a) for a in shlex.split(tk.get("commandLine", ""))]
+    if argv and os.path.basename(argv[0]) in ("mpirun", "mpiexec", "horovodrun"):
+        _, argv = parse(argv[1:])
+    return int(tk.get("processCount", 1)), argv, env, log_dir
+
+
+def tk_count(props) -> int:
+    return int(props.get("customToolkitSettings", {}).get("processCount", 1))
+
+
+def _subst(s: str, env: dict) -> str:
+    for k in sorted(env, key=len, reverse=True):
+        s = s.replace("${" + k + "}", env[k]).replace("$" + k, env[k])
+    return s
+
+
 def main(argv=None):
-    np_, cmd = parse(list(sys.argv[1:] if argv is None else argv))
+    argv = list(sys.argv[1:] if argv is None else argv)
+    if argv and argv[0] == "--job":
+        if len(argv) < 2:
+            sys.stderr.write("--job needs a path to a job spec (JSON)\n")
+            return 2
+        np_, cmd, env, log_dir = load_job(argv[1], mount_root=argv[3] if len(argv) > 3 and argv[2] == "--mount-root" else None)
+        return launch(np_, cmd, env_extra=env, log_dir=log_dir)
+    np_, cmd = parse(argv)
     if not cmd:
         sys.stderr.write(__doc__)
         return 2

@@ -64,3 +64,29 @@ def test_launcher_accepts_mpirun_style_flags():
     np_, cmd = parse(["-mca", "btl_tcp_if_exclude", "docker0,lo", "--allow-run-as-root", "--hostfile", "h", "-np", "8",
                       "python", "train.py", "--steps", "500"])
     assert np_ == 8 and cmd == ["python", "train.py", "--steps", "500"]
+
+
+def test_launcher_job_spec(tmp_path):
+    """--job: the reference's training_job.json layout (nodeCount / processCount / commandLine / output dirs / logs)."""
+    import json, subprocess, sys, os
+    from batchai_retinanet_horovod_coco_b200.parallel import launcher
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = {"properties": {"nodeCount": 2, "customToolkitSettings": {"processCount": 3, "commandLine":
+            "mpirun -mca btl_tcp_if_exclude docker0,lo --allow-run-as-root --hostfile $AZ_BATCHAI_MPI_HOST_FILE "
+            + sys.executable + " -c \"import os;open(os.environ['AZ_BATCHAI_OUTPUT_OUTPUTFILES']+'/r'+os.environ['RANK'],'w')"
+            ".write(os.environ['WORLD_SIZE']);print('hello from',os.environ['RANK'])\""},
+            "stdOutErrPathPrefix": "$AZ_BATCHAI_MOUNT_ROOT/logs",
+            "outputDirectories": [{"id": "OUTPUTFILES", "pathPrefix": "$AZ_BATCHAI_MOUNT_ROOT/afs", "pathSuffix": "output"}]}}
+    path = tmp_path / "job.json"
+    path.write_text(json.dumps(spec))
+    np_, argv, env, log_dir = launcher.load_job(str(path))
+    assert np_ == 3 and argv[0] == sys.executable and argv[1] == "-c" and log_dir == str(tmp_path / "logs")
+    r = subprocess.run([sys.executable, "-m", "batchai_retinanet_horovod_coco_b200.parallel.launcher", "--job", str(path)],
+                       capture_output=True, text=True, timeout=120, env=dict(os.environ, PYTHONPATH=root))
+    assert r.returncode == 0, r.stderr
+    out = tmp_path / "afs" / "output"
+    assert sorted(os.listdir(out)) == ["r0", "r1", "r2"] and (out / "r1").read_text() == "3"
+    assert "hello from 0" in r.stdout and "hello from 2" in (tmp_path / "logs" / "stdout-2.txt").read_text()
+    # the shipped spec parses and targets 8 ranks on one node
+    np8, argv8, env8, _ = launcher.load_job(os.path.join(root, "configs", "training_job.json"), mount_root=str(tmp_path))
+    assert np8 == 8 and argv8[:2] == ["python", "train.py"] and argv8[-1] == str(tmp_path / "coco")
