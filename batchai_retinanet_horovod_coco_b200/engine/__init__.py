@@ -1,7 +1,22 @@
 """Training engines: ``NativeTrainer`` (hand-written sm_100a kernels, the product), ``HybridTrainer``
-(same kernels for FPN / heads / losses / optimizer / allreduce, autograd for a non-ResNet backbone), ``SpecTrainer``
+(same kernels for FPN / heads / losses / optimizer / allreduce, autograd for a MobileNet / DenseNet backbone),
+``VGGTrainer`` (VGG backbone on the same conv kernels), ``SpecTrainer``
 (PyTorch autograd + KerasAdam + Horovod-style optimizer; CPU capable), ``LibraryTrainer`` (cuDNN +
 DDP/NCCL measured baseline)."""
+
+
+def native_engine_class(model):
+    """ResNet and VGG run entirely on the native kernels; MobileNet / DenseNet keep an autograd backbone."""
+    from ..models.resnet import ResNet
+    from ..models.vgg import VGG
+    if isinstance(model.backbone, ResNet):
+        from .trainer import NativeTrainer
+        return NativeTrainer
+    if isinstance(model.backbone, VGG):
+        from .vgg_native import VGGTrainer
+        return VGGTrainer
+    from .hybrid import HybridTrainer
+    return HybridTrainer
 
 
 def create_trainer(model, device, lr=1e-5, clipnorm=0.001, batch=1, image_hw=(800, 1333), freeze_backbone=False,
@@ -13,12 +28,7 @@ def create_trainer(model, device, lr=1e-5, clipnorm=0.001, batch=1, image_hw=(80
     if engine == "auto":
         engine = "native" if device.type == "cuda" else "spec"
     if engine == "native":
-        from .trainer import NativeTrainer
-        from ..models.resnet import ResNet
-        cls = NativeTrainer
-        if not isinstance(model.backbone, ResNet):
-            from .hybrid import HybridTrainer
-            cls = HybridTrainer
+        cls = native_engine_class(model)
         comm = None
         if hvd.is_initialized() and hvd.size() > 1:
             from ..parallel.p2p import P2PComm

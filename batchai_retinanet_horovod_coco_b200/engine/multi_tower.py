@@ -33,10 +33,8 @@ class MultiTowerTrainer:
                                f"found {torch.cuda.device_count() if torch.cuda.is_available() else 0}")
         if batch < num_towers:
             raise ValueError(f"Batch size ({batch}) must be equal to or higher than the number of GPUs ({num_towers})")
-        from ..models.resnet import ResNet
-        from .hybrid import HybridTrainer
-        from .trainer import NativeTrainer
-        cls = NativeTrainer if isinstance(model.backbone, ResNet) else HybridTrainer
+        from . import native_engine_class
+        cls = native_engine_class(model)
         self.n = num_towers
         self.model = model
         self._pool = ThreadPoolExecutor(max_workers=num_towers, thread_name_prefix="tower")

@@ -327,6 +327,18 @@ def clip_scale(sumsq_t, clipnorm, scale):
     _check(_load().b200_clip_scale(_ptr(sumsq_t), C.c_float(clipnorm), _ptr(scale), _stream()), "clip_scale")
 
 
+def maxpool2_fwd(x, y):
+    """2x2/2 max-pool, valid padding: x bf16 [N,H,W,C] -> y [N,H//2,W//2,C]."""
+    n, h, w, c = x.shape
+    _check(require().b200_maxpool2_fwd(_ptr(x), _ptr(y), n, h, w, c, _stream()), "maxpool2_fwd")
+
+
+def maxpool2_relu_bwd(x, dy, dx):
+    """dx = gradient w.r.t. the pre-activation of the ReLU output ``x`` that was pooled (dy: gradient of the pool)."""
+    n, h, w, c = x.shape
+    _check(require().b200_maxpool2_relu_bwd(_ptr(x), _ptr(dy), _ptr(dx), n, h, w, c, _stream()), "maxpool2_relu_bwd")
+
+
 def adam(p, g, m, v, grad_scale, lr_t, beta1, beta2, eps):
     """``lr_t`` may be a float or a 1-element fp32 device tensor (read on the device: CUDA-graph friendly)."""
     if isinstance(lr_t, torch.Tensor):

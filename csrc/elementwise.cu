@@ -343,6 +343,78 @@ static int grid_for(long long work, int block) {
   return static_cast<int>(g);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// 2x2 / 2 max-pool with "valid" padding (VGG: sizes floor) over NHWC bf16.  The pooled tensor x is a ReLU
+// output, so backward folds that ReLU's mask in: the result is the gradient w.r.t. the PRE-activation of the
+// conv that produced x (first maximum in scan order wins, as in the library kernels; a maximum of 0 passes
+// nothing).  Windows hanging over an odd last row / column only zero-fill their in-range inputs.
+__global__ void maxpool2_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int H,
+                                    int W, int C, int OH, int OW) {
+  const int cg = C >> 3;
+  const long long total = static_cast<long long>(N) * OH * OW * cg;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % cg) * 8;
+    long long t = i / cg;
+    const int ow = static_cast<int>(t % OW);
+    t /= OW;
+    const int oh = static_cast<int>(t % OH);
+    const int n = static_cast<int>(t / OH);
+    const __nv_bfloat16* base = x + ((static_cast<long long>(n) * H + 2 * oh) * W + 2 * ow) * C + c;
+    float a[8], b[8], m[8];
+    load8(base, a);
+    load8(base + C, b);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) m[e] = fmaxf(a[e], b[e]);
+    load8(base + static_cast<long long>(W) * C, a);
+    load8(base + static_cast<long long>(W) * C + C, b);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) m[e] = fmaxf(m[e], fmaxf(a[e], b[e]));
+    store8(y + ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c, m);
+  }
+}
+
+__global__ void maxpool2_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                    __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int OH, int OW) {
+  const int cg = C >> 3;
+  const int WH = (H + 1) >> 1, WW = (W + 1) >> 1;   // windows including the ones hanging over an odd edge
+  const long long total = static_cast<long long>(N) * WH * WW * cg;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % cg) * 8;
+    long long t = i / cg;
+    const int ow = static_cast<int>(t % WW);
+    t /= WW;
+    const int oh = static_cast<int>(t % WH);
+    const int n = static_cast<int>(t / WH);
+    const bool full = oh < OH && ow < OW;
+    float v[4][8], g[8], best[8];
+    int arg[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { best[e] = 0.f; arg[e] = -1; g[e] = 0.f; }
+    if (full) {
+      load8(dy + ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c, g);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        load8(x + ((static_cast<long long>(n) * H + 2 * oh + (q >> 1)) * W + 2 * ow + (q & 1)) * C + c, v[q]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (v[q][e] > best[e]) { best[e] = v[q][e]; arg[e] = q; }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int h = 2 * oh + (q >> 1), w = 2 * ow + (q & 1);
+      if (h >= H || w >= W) continue;
+      float o[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = (arg[e] == q) ? g[e] : 0.f;
+      store8(dx + ((static_cast<long long>(n) * H + h) * W + w) * C + c, o);
+    }
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -405,6 +477,26 @@ int b200_upsample_bwd_add(const void* dmerged, void* dtop, int N, int H, int W, 
   upsample_bwd_add_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dmerged), static_cast<__nv_bfloat16*>(dtop), N, H, W, C, TH, TW);
   return check_launch("upsample_bwd_add");
+}
+
+int b200_maxpool2_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream) {
+  if (C % 8) return set_error(-1, "maxpool2: C must be a multiple of 8");
+  const int OH = H / 2, OW = W / 2;
+  const long long total = static_cast<long long>(N) * OH * OW * (C / 8);
+  if (total == 0) return 0;
+  maxpool2_fwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), N, H, W, C, OH, OW);
+  return check_launch("maxpool2_fwd");
+}
+
+int b200_maxpool2_relu_bwd(const void* x, const void* dy, void* dx, int N, int H, int W, int C, void* stream) {
+  if (C % 8) return set_error(-1, "maxpool2: C must be a multiple of 8");
+  const long long total = static_cast<long long>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
+  if (total == 0) return 0;
+  maxpool2_bwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), N, H,
+      W, C, H / 2, W / 2);
+  return check_launch("maxpool2_relu_bwd");
 }
 
 int b200_relu(const void* x, void* y, long long n, void* stream) {

@@ -125,6 +125,10 @@ int b200_upsample_add(const void* lateral, const void* top, void* out, int N, in
 int b200_upsample_bwd_add(const void* dmerged, void* dtop_inout, int N, int H, int W, int C, int TH, int TW,
                           void* stream);
 /* y = relu(x) and dx = dy * (y > 0) on bf16 buffers (P7's input; generic). */
+/* 2x2/2 max-pool, "valid" padding (VGG blocks), NHWC bf16 [N,H,W,C] -> [N,H/2,W/2,C].  Backward takes the pooled
+ * tensor x (a ReLU output) and also applies that ReLU's mask: dx is the gradient w.r.t. the pre-activation. */
+int b200_maxpool2_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream);
+int b200_maxpool2_relu_bwd(const void* x, const void* dy, void* dx, int N, int H, int W, int C, void* stream);
 int b200_relu(const void* x, void* y, long long n, void* stream);
 int b200_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* stream);
 /* out = (a + b) * (mask > 0); b optional (merge of gradient branches + ReLU backward). */
