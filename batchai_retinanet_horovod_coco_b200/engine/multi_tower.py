@@ -37,6 +37,7 @@ class MultiTowerTrainer:
         cls = native_engine_class(model)
         self.n = num_towers
         self.model = model
+        self.device = torch.device("cuda", 0)     # where losses are gathered and predictions run
         self._pool = ThreadPoolExecutor(max_workers=num_towers, thread_name_prefix="tower")
         group = LocalGroup(num_towers)
         models = [model] + [copy.deepcopy(model) for _ in range(num_towers - 1)]

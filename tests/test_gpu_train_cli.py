@@ -42,3 +42,16 @@ def test_native_cli_two_gpus(tmp_path):
              cwd=str(tmp_path))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     assert os.listdir(tmp_path / "snap") == ["checkpoint-01.h5"]
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_native_cli_multi_gpu_towers(tmp_path):
+    """--multi-gpu 2 --multi-gpu-force (reference train.py:367-368): one process, two towers, evaluation + snapshot."""
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    cmd = [sys.executable, os.path.join(ROOT, "train.py"), "--no-weights", "--multi-gpu", "2", "--multi-gpu-force",
+           "--batch-size", "2", "--steps", "3", "--epochs", "1", "--image-min-side", "192", "--image-max-side", "256",
+           "--snapshot-path", str(tmp_path / "snap"), "--tensorboard-dir", "", "--lr", "1e-4", "synthetic",
+           "--synthetic-images", "4", "--synthetic-classes", "5", "--synthetic-width", "256"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(tmp_path), env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert os.listdir(tmp_path / "snap") == ["checkpoint-01.h5"] and "mAP" in r.stdout
