@@ -38,6 +38,25 @@ def makedirs(path):
     os.makedirs(path, exist_ok=True)
 
 
+MINIMUM_TORCH = (2, 4)
+OPS_ABI = 1
+
+
+def check_versions(device=None):
+    """The reference asserts a minimum Keras version before building anything (``check_keras_version()``,
+    train.py:52,393).  The equivalents here: a minimum PyTorch, and -- on the GPU path -- that the in-tree native
+    library is the one this Python layer was written against and that the device is a Blackwell part."""
+    have = tuple(int(v) for v in torch.__version__.split("+")[0].split(".")[:2])
+    assert have >= MINIMUM_TORCH, "You are using PyTorch version {}. The minimum required version is {}.".format(
+        torch.__version__, ".".join(map(str, MINIMUM_TORCH)))
+    if device is not None and torch.device(device).type == "cuda":
+        from ..ops import native
+        abi = int(native.require().b200_ops_abi_version())
+        assert abi == OPS_ABI, f"libb200ops ABI {abi} does not match this package ({OPS_ABI}); run python build_native.py"
+        major, _ = torch.cuda.get_device_capability(device)
+        assert major >= 10, "the native engine needs an sm_100a (B200) device; use --cpu for the spec engine elsewhere"
+
+
 def get_device(args):
     """One process per GPU, pinned by local rank (reference ``get_session``, train.py:68-72).  ``--gpu``
     wins over the local rank when given."""
@@ -263,6 +282,7 @@ def main(args=None):
         hvd.timeline_start(args.timeline)
     backbone = models.backbone(args.backbone)
     device = get_device(args)
+    check_versions(device)
     train_generator, validation_generator = create_generators(args)
     initial_epoch = 0
     state = None

@@ -36,6 +36,30 @@ if mode == "basic":
     hvd.barrier()
     st = hvd.stats()
     assert st["fused_tensors"] >= 2, st
+    # the hvd.callbacks.* that train.py does not use but Horovod ships
+    from batchai_retinanet_horovod_coco_b200.callbacks import (LearningRateScheduleCallback, LearningRateWarmupCallback,
+                                                                MetricAverageCallback)
+    logs = {"loss": float(r), "mAP": 1.0 + r, "note": "text"}
+    MetricAverageCallback().on_epoch_end(0, logs)
+    assert abs(logs["loss"] - (n - 1) / 2) < 1e-9 and abs(logs["mAP"] - (1.0 + (n - 1) / 2)) < 1e-9 and logs["note"] == "text"
+
+    class _T:
+        lr = 0.8
+    warm = LearningRateWarmupCallback(warmup_epochs=4)
+    warm.trainer = _T()
+    warm.on_epoch_begin(0)
+    assert abs(_T.lr - 0.8) < 1e-12 and abs(warm.trainer.lr - 0.8 / n) < 1e-12     # starts at lr / size ...
+    warm.on_epoch_begin(2)
+    assert abs(warm.trainer.lr - 0.8 / n * (2 * (n - 1) / 4 + 1)) < 1e-12          # ... and ramps linearly to lr
+    sched = LearningRateScheduleCallback(lambda e: 0.1 ** e, start_epoch=1)
+    sched.trainer = _T()
+    sched.on_epoch_begin(0)
+    sched.on_epoch_begin(2)
+    assert abs(sched.trainer.lr - 0.8 * 0.01) < 1e-12
+    x = torch.tensor([1.0002, -3.0]) * (r + 1)
+    y = hvd.allreduce(x, average=False, compression=hvd.Compression.fp16)
+    want = sum(float(torch.tensor(1.0002 * (k + 1)).half()) for k in range(n))
+    assert y.dtype == torch.float32 and abs(y[0].item() - want) < 1e-6, (y, want)   # values travel fp16-rounded
     hvd.timeline_stop()
 elif mode == "mismatch":
     t = torch.zeros(4 if r == 0 else 5)
