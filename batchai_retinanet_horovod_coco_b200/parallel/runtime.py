@@ -14,7 +14,9 @@ import os
 import torch
 
 _LIB = None
-_LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_native", "libb200rt.so")
+# B200RT_LIB points at an alternative build of the runtime (the ThreadSanitizer build of scripts/tsan_runtime.sh)
+_LIB_PATH = os.environ.get("B200RT_LIB") or os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_native",
+                                                        "libb200rt.so")
 
 ALLREDUCE, BROADCAST, ALLGATHER = 0, 1, 2
 _DTYPES = {torch.float32: 0, torch.float64: 1, torch.int32: 2, torch.int64: 3, torch.uint8: 4}

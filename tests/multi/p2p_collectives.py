@@ -39,6 +39,21 @@ assert (t == 1).all()
 t = torch.full((12345,), float(rank + 1), device=dev)
 comm.allreduce_sum_(t)
 assert abs(t[0].item() - world * (world + 1) / 2) < 1e-5
+# flag-protocol stress: ranks drift apart by random host delays, collectives are issued back to back
+# without host syncs and the bucket is rewritten right after each one -- a rank that left a barrier early, or an epoch
+# that was reused, shows up as a wrong average
+import random, time
+rnd = random.Random(1000 + rank)
+err = torch.zeros((), device=dev)
+for it in range(300):
+    if rnd.random() < 0.25:
+        time.sleep(rnd.random() * 0.003)
+    n = (1024, 4096, 262144, 1 << 20)[it % 4]
+    bucket[:n].fill_(float(rank + it))
+    comm.allreduce_avg(bucket, comm.result, n, prescale=False, algo=(0, 1, 2, 3)[(it // 4) % 4])
+    err = torch.maximum(err, (comm.result[:n] - (it + (world - 1) / 2)).abs().max())
+torch.cuda.synchronize()
+assert err.item() < 1e-4, (rank, err.item())
 # bandwidth (device timed, max over ranks)
 for nbytes in (1 << 12, 1 << 16, 1 << 20, 1 << 24, N * 4):
     n = nbytes // 4
