@@ -57,6 +57,18 @@ def check_versions(device=None):
         assert major >= 10, "the native engine needs an sm_100a (B200) device; use --cpu for the spec engine elsewhere"
 
 
+def latest_snapshot(snapshot_path: str):
+    """Newest ``checkpoint-NN.h5`` (highest NN) in ``snapshot_path``, or None."""
+    import re
+    best = None
+    if os.path.isdir(snapshot_path):
+        for f in os.listdir(snapshot_path):
+            m = re.fullmatch(r"checkpoint-(\d+)\.h5", f)
+            if m and (best is None or int(m.group(1)) > best[0]):
+                best = (int(m.group(1)), os.path.join(snapshot_path, f))
+    return best[1] if best else None
+
+
 def get_device(args):
     """One process per GPU, pinned by local rank (reference ``get_session``, train.py:68-72).  ``--gpu``
     wins over the local rank when given."""
@@ -206,7 +218,9 @@ def parse_args(args):
     syn_parser.add_argument("--synthetic-width", type=int, default=0)
 
     group = parser.add_mutually_exclusive_group()
-    group.add_argument("--snapshot", help="Resume training from a snapshot.")
+    group.add_argument("--snapshot", help="Resume training from a snapshot. (extension) 'auto': the newest "
+                       "checkpoint-NN.h5 under --snapshot-path if there is one, else start as if the flag were absent "
+                       "-- a requeued job (reference cluster.json:6) then continues instead of restarting.")
     group.add_argument("--imagenet-weights", help="Initialize the model with pretrained imagenet weights. This is the default behaviour.", action="store_const", const=True, default=True)
     group.add_argument("--weights", help="Initialize the model with weights from a file.")
     group.add_argument("--no-weights", help="Don't initialize the model with any weights.", dest="imagenet_weights", action="store_const", const=False)
@@ -286,6 +300,10 @@ def main(args=None):
     train_generator, validation_generator = create_generators(args)
     initial_epoch = 0
     state = None
+    if args.snapshot == "auto":
+        args.snapshot = latest_snapshot(args.snapshot_path)
+        if hvd.rank() == 0:
+            print("--snapshot auto: " + (f"resuming from {args.snapshot}" if args.snapshot else "no checkpoint yet, starting fresh"))
     if args.snapshot is not None:
         print("Loading model, this may take a second...")
         model, state = models.load_model(args.snapshot, backbone_name=args.backbone)

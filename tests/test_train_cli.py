@@ -148,8 +148,8 @@ def test_two_rank_cpu_training_run(tmp_path):
     assert any(e["name"] == "SHM_ALLREDUCE" for e in ev)
     # resume: optimizer state and epoch counter come back, training continues at epoch 3
     base2 = [a for a in base if a != "--no-weights"]          # --snapshot and --no-weights are mutually exclusive
-    r2 = subprocess.run(base2 + ["--steps", "1", "--epochs", "3", "--no-evaluation", "--snapshot",
-                                str(snap / "checkpoint-02.h5"), "coco", root], capture_output=True, text=True, timeout=800,
+    r2 = subprocess.run(base2 + ["--steps", "1", "--epochs", "3", "--no-evaluation", "--snapshot", "auto",   # newest = 02
+                                "coco", root], capture_output=True, text=True, timeout=800,
                         cwd=str(tmp_path), env=env)
     assert r2.returncode == 0, r2.stdout[-3000:] + r2.stderr[-3000:]
     assert "Epoch 3/3" in r2.stdout and "Epoch 1/3" not in r2.stdout
@@ -205,3 +205,10 @@ def test_batch_prefetcher_order_coverage_and_errors():
     with pytest.raises(OSError, match="unreadable"):
         with BatchPrefetcher(Broken(num_images=4, image_hw=(32, 32), classes=2, batch_size=2), workers=2) as pf:
             pf.next()
+
+
+def test_latest_snapshot_picks_highest_epoch(tmp_path):
+    assert T.latest_snapshot(str(tmp_path / "missing")) is None and T.latest_snapshot(str(tmp_path)) is None
+    for n in ("checkpoint-02.h5", "checkpoint-10.h5", "checkpoint-9.h5", "checkpoint-xx.h5", "other.h5"):
+        (tmp_path / n).write_text("")
+    assert T.latest_snapshot(str(tmp_path)) == str(tmp_path / "checkpoint-10.h5")
