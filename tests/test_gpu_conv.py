@@ -225,3 +225,66 @@ def test_stem_wgrad(n, h, w):
     y.backward(dy.float().permute(0, 3, 1, 2))
     ref = cv.pack_master(wz.grad) * scale.view(1, 64, 1)
     _close(dw, ref)
+
+
+def _guarded(shape, dtype, fill=0.0):
+    """A tensor carved out of the middle of a larger allocation whose guard zones hold a sentinel: kernels that
+    write outside their output are caught without compute-sanitizer (which this GPU pool does not offer)."""
+    n = 1
+    for s in shape:
+        n *= s
+    guard = 4096
+    raw = torch.full((n + 2 * guard,), 12345.0, device="cuda", dtype=dtype)
+    view = raw[guard:guard + n].view(shape)
+    view.fill_(fill)
+    return raw, view, guard
+
+
+def _guards_intact(raw, guard):
+    return bool((raw[:guard] == 12345.0).all() and (raw[-guard:] == 12345.0).all())
+
+
+def test_kernels_do_not_write_outside_their_outputs():
+    """Odd sizes (partial tiles in every dimension), every kernel family, outputs surrounded by sentinels."""
+    torch.manual_seed(3)
+    n, h, w, cin, cout = 2, 13, 21, 128, 72
+    x = _mk(n, h, w, cin)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda") * 0.03
+    wf, wd = cv.pack_working(cv.pack_master(wt))
+    # fprop stride 1 (+ shift, ReLU, residual)
+    raw, y, g = _guarded((n, h, w, cv.round8(cout)), torch.bfloat16)
+    res = _mk(n, h, w, cout, seed=5)
+    native.conv_raw(0, [(x, y, res, None)], wf, cin, x.shape[-1], cout, y.shape[-1], 3, 3, 1, 1, 1,
+                    shift=torch.zeros(cout, device="cuda"), relu=True)
+    torch.cuda.synchronize()
+    assert _guards_intact(raw, g)
+    # dgrad stride 1 (+ mask)
+    dy = _mk(n, h, w, cout, seed=6)
+    raw, dx, g = _guarded((n, h, w, cin), torch.bfloat16)
+    native.conv_raw(1, [(dy, dx, None, x)], wd, cout, dy.shape[-1], cin, dx.shape[-1], 3, 3, 1, 1, 1)
+    torch.cuda.synchronize()
+    assert _guards_intact(raw, g)
+    # wgrad + bias gradient into fp32 buffers
+    raw, dw, g = _guarded((9, cout, cin), torch.float32)
+    rawb, db, gb = _guarded((cout,), torch.float32)
+    native.wgrad_raw([(x, dy)], dw, cin, x.shape[-1], cout, dy.shape[-1], 3, 3, 1, 1, 1, dbias=db)
+    torch.cuda.synchronize()
+    assert _guards_intact(raw, g) and _guards_intact(rawb, gb) and dw.abs().sum() > 0
+    # stem conv / stem wgrad at an odd size
+    x4 = torch.zeros(1, 75, 101, 4, device="cuda", dtype=torch.bfloat16)
+    x4[..., :3] = (torch.randn(1, 75, 101, 3, device="cuda") * 50).to(torch.bfloat16)
+    wp = native.pack_stem_weight(torch.randn(49, 64, 3, device="cuda") * 0.05)
+    raw, ys, g = _guarded((1, 38, 51, 64), torch.bfloat16)
+    native.stem_conv(x4, wp, torch.zeros(64, device="cuda"), ys)
+    raww, dws, gw = _guarded((49, 64, 3), torch.float32)
+    native.stem_wgrad(x4, ys, torch.ones(64, device="cuda"), dws)
+    torch.cuda.synchronize()
+    assert _guards_intact(raw, g) and _guards_intact(raww, gw)
+    # 2x2 pool forward / backward at odd sizes
+    xp = torch.relu(_mk(2, 9, 13, 64, seed=7))
+    raw, yp, g = _guarded((2, 4, 6, 64), torch.bfloat16)
+    native.maxpool2_fwd(xp, yp)
+    rawd, dxp, gd = _guarded((2, 9, 13, 64), torch.bfloat16)
+    native.maxpool2_relu_bwd(xp, torch.ones_like(yp), dxp)
+    torch.cuda.synchronize()
+    assert _guards_intact(raw, g) and _guards_intact(rawd, gd)
