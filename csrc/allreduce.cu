@@ -400,10 +400,14 @@ int b200_allreduce_host(const B200ArHostArgs* a, void* stream_) {
     break;
   switch (p.world) {
     B200_AR_LAUNCH(2)
+    B200_AR_LAUNCH(3)
     B200_AR_LAUNCH(4)
+    B200_AR_LAUNCH(5)
+    B200_AR_LAUNCH(6)
+    B200_AR_LAUNCH(7)
     B200_AR_LAUNCH(8)
     default:
-      return set_error(-1, "allreduce: world size %d not instantiated (1, 2, 4, 8)", p.world);
+      return set_error(-1, "allreduce: world size %d not instantiated (1..8)", p.world);
   }
 #undef B200_AR_LAUNCH
   if (a->epoch_ptr) epoch_bump_kernel<<<1, 1, 0, stream>>>(a->epoch_ptr);
@@ -426,7 +430,11 @@ int b200_broadcast_host(const B200ArHostArgs* a, int root, void* stream_) {
     if (!p.mc_out || p.external_sync) return set_error(-1, "broadcast: NVLS needs a multicast result address");
     switch (p.world) {
       case 2: broadcast_nvls_kernel<2><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+      case 3: broadcast_nvls_kernel<3><<<blocks, kArThreads, 0, stream>>>(p, root); break;
       case 4: broadcast_nvls_kernel<4><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+      case 5: broadcast_nvls_kernel<5><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+      case 6: broadcast_nvls_kernel<6><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+      case 7: broadcast_nvls_kernel<7><<<blocks, kArThreads, 0, stream>>>(p, root); break;
       case 8: broadcast_nvls_kernel<8><<<blocks, kArThreads, 0, stream>>>(p, root); break;
       default: return set_error(-1, "broadcast: world size %d not instantiated", p.world);
     }
@@ -435,7 +443,11 @@ int b200_broadcast_host(const B200ArHostArgs* a, int root, void* stream_) {
   }
   switch (p.world) {
     case 2: broadcast_kernel<2><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+    case 3: broadcast_kernel<3><<<blocks, kArThreads, 0, stream>>>(p, root); break;
     case 4: broadcast_kernel<4><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+    case 5: broadcast_kernel<5><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+    case 6: broadcast_kernel<6><<<blocks, kArThreads, 0, stream>>>(p, root); break;
+    case 7: broadcast_kernel<7><<<blocks, kArThreads, 0, stream>>>(p, root); break;
     case 8: broadcast_kernel<8><<<blocks, kArThreads, 0, stream>>>(p, root); break;
     default: return set_error(-1, "broadcast: world size %d not instantiated", p.world);
   }
