@@ -268,27 +268,42 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       // flight, so everything a tile needs is put in flight at once, behind the MMA.
       constexpr int kChunkStep = 32 * (kEpiWarps / 4);
       const int c0 = cq * 32;
-      const long long own_row = static_cast<long long>(pix) * ldo + col0;
+      // Operands are fetched in the same COALESCED pattern as the stores (8 rows x 64 B per instruction, lane ->
+      // row i*8 + lane/4, 16-byte piece lane%4) and transposed to row-per-thread through the staging buffer.
+      // Row-per-thread loads touch 32 different 128-byte lines per instruction; the L1 tag stage then caps the
+      // operand stream at ~3.2 TB/s (scripts/epilogue_probe.py), well below what the TMA-fed operands reach.
       uint4 ka[2][4], km[2][4];
       float sh[2] = {0.f, 0.f};
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const int c = c0 + h * kChunkStep;
         const bool chunk_ok = c < BN && col0 + c < col_end;
+        const bool pc_ok = chunk_ok && (col0 + c + cpiece * 8 < col_end_pad);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const bool ok = chunk_ok && valid && (col0 + c + j * 8 < col_end_pad);
-          if constexpr (kMask && !kAdd) km[h][j] = ok ? *reinterpret_cast<const uint4*>(maskp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
-          if constexpr (kAdd && !kMask) ka[h][j] = ok ? *reinterpret_cast<const uint4*>(addp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+        for (int i = 0; i < 4; ++i) {
+          const bool ok = pc_ok && ok_r[i];
+          if constexpr (kMask && !kAdd) km[h][i] = ok ? *reinterpret_cast<const uint4*>(maskp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
+          if constexpr (kAdd && !kMask) ka[h][i] = ok ? *reinterpret_cast<const uint4*>(addp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
           if constexpr (kAdd && kMask) {
             if (h == 0) {  // both operands: only the first chunk up front (register budget)
-              km[0][j] = ok ? *reinterpret_cast<const uint4*>(maskp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
-              ka[0][j] = ok ? *reinterpret_cast<const uint4*>(addp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+              km[0][i] = ok ? *reinterpret_cast<const uint4*>(maskp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
+              ka[0][i] = ok ? *reinterpret_cast<const uint4*>(addp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
             }
           }
         }
         if (shiftp && chunk_ok && col0 + c + lane < col_end_pad) sh[h] = __ldg(shiftp + col0 + c + lane);
       }
+      // coalesced layout -> row-per-thread layout (in place in the registers), through the warp's staging buffer
+      auto to_rows = [&](uint4(&v)[4]) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(so_r[i]), "r"(v[i].x), "r"(v[i].y), "r"(v[i].z), "r"(v[i].w) : "memory");
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w) : "r"(own_off[j]) : "memory");
+        __syncwarp();
+      };
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * 256;
@@ -301,15 +316,17 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         if constexpr (kAdd && kMask) {
           if (h == 1) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const bool ok = valid && (col + j * 8 < col_end_pad);
-              km[1][j] = ok ? *reinterpret_cast<const uint4*>(maskp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
-              ka[1][j] = ok ? *reinterpret_cast<const uint4*>(addp + own_row + c + j * 8) : make_uint4(0u, 0u, 0u, 0u);
+            for (int i = 0; i < 4; ++i) {
+              const bool ok = piece_ok && ok_r[i];
+              km[1][i] = ok ? *reinterpret_cast<const uint4*>(maskp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
+              ka[1][i] = ok ? *reinterpret_cast<const uint4*>(addp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
             }
           }
         }
         uint32_t r[32];
         tmem_ld_32x32(t_row + c, r);
+        if constexpr (kAdd) to_rows(ka[h]);     // the TMEM load is in flight meanwhile
+        if constexpr (kMask) to_rows(km[h]);
         tmem_ld_wait();
         // ---- row-per-thread math, result into the staging buffer (issue-bound: keep it short)
 #pragma unroll
