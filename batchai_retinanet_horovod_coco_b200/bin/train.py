@@ -12,7 +12,6 @@ Extra flags (not in the reference) are grouped at the end of ``parse_args``.
 from __future__ import annotations
 
 import argparse
-import functools
 import os
 import sys
 import warnings

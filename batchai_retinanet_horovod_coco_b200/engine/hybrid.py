@@ -20,8 +20,7 @@ from __future__ import annotations
 
 import torch
 
-from ..ops import native
-from .trainer import BF16, CAFFE_MEAN_BGR, NativeTrainer, _align4
+from .trainer import BF16, NativeTrainer, _align4
 
 
 class HybridTrainer(NativeTrainer):

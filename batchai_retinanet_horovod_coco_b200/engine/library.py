@@ -10,7 +10,6 @@ It also runs on CPU (gloo) and is the oracle for the native engine's end-to-end 
 from __future__ import annotations
 
 import torch
-import torch.nn.functional as F
 
 from ..models.retinanet import RetinaNet
 from ..ops import anchors as anchor_ops

@@ -30,11 +30,9 @@ import os
 import warnings
 
 import torch
-import torch.nn.functional as F
 
-from ..models.resnet import BLOCKS, tf_same_pad
+from ..models.resnet import tf_same_pad
 from ..models.retinanet import RetinaNet
-from ..ops import anchors as anchor_ops
 from ..ops import native
 from ..ops.conv import round8
 

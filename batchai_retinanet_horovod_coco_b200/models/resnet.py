@@ -18,7 +18,6 @@ Structure notes that matter for weight parity:
 
 from __future__ import annotations
 
-import math
 from collections import OrderedDict
 
 import torch

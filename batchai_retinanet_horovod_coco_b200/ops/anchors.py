@@ -18,7 +18,6 @@ The native GPU path (csrc/targets.cu) implements the same rules; this file is it
 from __future__ import annotations
 
 import functools
-import math
 
 import torch
 

@@ -12,7 +12,6 @@ synchronise.  Layout convention: activations are NHWC bf16 tensors of shape ``[N
 from __future__ import annotations
 
 import ctypes as C
-import math
 import os
 import threading
 

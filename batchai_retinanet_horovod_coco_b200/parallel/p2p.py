@@ -16,7 +16,6 @@ IPC handles once, and for the rendezvous itself.
 
 from __future__ import annotations
 
-import ctypes as C
 import os
 import socket
 import threading

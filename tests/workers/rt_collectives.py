@@ -59,7 +59,7 @@ if mode == "basic":
     x = torch.tensor([1.0002, -3.0]) * (r + 1)
     y = hvd.allreduce(x, average=False, compression=hvd.Compression.fp16)
     want = sum(float(torch.tensor(1.0002 * (k + 1)).half()) for k in range(n))
-    assert y.dtype == torch.float32 and abs(y[0].item() - want) < 1e-6, (y, want)   # values travel fp16-rounded
+    assert y.dtype == torch.float32 and abs(y[0].item() - want) < 1e-5, (y, want)   # values travel fp16-rounded
     hvd.timeline_stop()
 elif mode == "mismatch":
     t = torch.zeros(4 if r == 0 else 5)
