@@ -112,7 +112,12 @@ def test_engine_shape_buckets_and_plan_lru():
 
 
 def test_graph_replay_matches_eager_steps():
-    """Whole-step CUDA graph (captured after two eager steps of a plan) vs plain launches: same trajectory."""
+    """Whole-step CUDA graphs (captured after two eager steps of a plan) vs plain launches, ONE STEP AT A TIME from
+    identical state.  A multi-step trajectory cannot be compared tightly: two EAGER trainers drift apart just as
+    much as a graph / eager pair (fp32 atomics in wgrad make gradients differ by ~1e-8, and Adam's first updates are
+    lr * sign(g), so every element whose gradient is zero up to that noise moves by 2 * lr; measured over 14
+    three-arm trials with scripts/debug_graph3.py: both pairs agree to 1e-7 for two steps, then either pair jumps to
+    1e-4 .. 4e-3 in the loss).  So before every compared step the graph trainer takes the eager trainer's state."""
     import copy
     from batchai_retinanet_horovod_coco_b200.engine.trainer import NativeTrainer
     from batchai_retinanet_horovod_coco_b200.ops import native
@@ -121,26 +126,33 @@ def test_graph_replay_matches_eager_steps():
     model = RetinaNet(80, "resnet50")
     a = NativeTrainer(model=copy.deepcopy(model), device="cuda", batch=B, image_hw=(H, W), lr=1e-4, clipnorm=0.001, use_graph=True)
     b = NativeTrainer(model=copy.deepcopy(model), device="cuda", batch=B, image_hw=(H, W), lr=1e-4, clipnorm=0.001, use_graph=False)
-    la, lb = [], []
-    for step in range(7):
+    n = a.n_train
+    for step in range(6):
         img, gt, cnt, hw = _inputs(B, H, W, seed=step)
         if step % 2:
             gt, cnt = gt[:, :3], torch.full_like(cnt, 3)       # the captured step takes a varying number of boxes
+        with torch.no_grad():                                    # same weights, Adam slots and step count
+            for dst, src in ((a.P, b.P), (a.M, b.M), (a.V, b.V)):
+                dst.copy_(src)
+            a.iterations = b.iterations
+            a._refresh_weights()
         pinned = [t.pin_memory() for t in (img, gt, cnt, hw)]  # host inputs go straight into the static buffers
         k0 = native.launch_count()
-        la.append(a.train_step(*pinned).cpu())
+        la = a.train_step(*pinned).cpu()
         ka = native.launch_count() - k0
-        lb.append(b.train_step(img, gt, cnt, hw).cpu())
+        lb = b.train_step(img, gt, cnt, hw).cpu()
         kb = native.launch_count() - k0 - ka
+        torch.cuda.synchronize()
         assert ka == kb, (step, ka, kb)                          # replayed kernels are accounted for
-    plan = a._plan(B, H, W)
-    assert "graph" in plan and a.iterations == b.iterations == 7
-    # fp32 atomics in wgrad make two EAGER runs drift apart too (1e-8 in P per step, amplified by Adam's
-    # normalisation once gradients are tiny): tight on the first steps, loose later (scripts/debug_graph.py)
-    for i, (x, y) in enumerate(zip(la, lb)):
-        assert torch.allclose(x, y, rtol=1e-4 if i < 4 else 1e-2, atol=1e-4), (i, la, lb)
-    torch.cuda.synchronize()
-    assert (a.P - b.P).abs().max().item() < 5e-4 and (a.P != 0).any()
+        # forward from identical weights: only the final loss sums use atomics
+        assert torch.allclose(la, lb, rtol=1e-5, atol=1e-6), (step, la, lb)
+        ga, gb = a.G[:n].double(), b.G[:n].double()              # raw local gradients of this step
+        cos = float((ga @ gb) / (ga.norm() * gb.norm()))
+        assert cos > 0.99999 and abs(float(ga.norm() / gb.norm()) - 1) < 1e-4, (step, cos, float(ga.norm()), float(gb.norm()))
+        # one Adam step from the same slots: at most a sign flip (2 * lr_t) on elements whose gradient is noise
+        assert (a.P - b.P).abs().max().item() <= 2.5 * 1e-4 * 3.2, step
+        assert ((a.P - b.P).abs() > 1e-6).float().mean().item() < 1e-3, step
+    assert "graph" in a._plan(B, H, W) and a.iterations == b.iterations == 6
 
 
 def test_freeze_backbone_trains_only_fpn_and_heads():
