@@ -84,9 +84,11 @@ class MultiTowerTrainer:
     # ---- steps ---------------------------------------------------------------------------------
     def _split(self, t):
         """Split the batch axis into N contiguous chunks (``multi_gpu_model`` slices the same way)."""
+        # every tower gets floor(B / n) samples and the last one also the remainder, as keras.utils.multi_gpu_model
+        # does (reference train.py:86-89); ceil-sized chunks would leave the last tower empty for e.g. B=5, n=4
         B = t.shape[0]
-        per = -(-B // self.n)
-        return [t[i * per:min(B, (i + 1) * per)] for i in range(self.n)]
+        per = B // self.n
+        return [t[i * per:(B if i == self.n - 1 else (i + 1) * per)] for i in range(self.n)]
 
     def train_step(self, images_u8, gt, gt_count, img_hw):
         if images_u8.shape[0] < self.n:

@@ -584,7 +584,7 @@ class NativeTrainer:
             else:
                 g = g_next
         self._mark("bwd_backbone")
-        # stem: max-pool + ReLU + BN backward, then cuDNN wgrad for the 7x7x3 filter
+        # stem: max-pool + ReLU + BN backward, then the native weight-gradient kernel for the 7x7x3 filter
         native.bn_relu_maxpool_bwd(p["pool_idx"], self.ones64, g, p["dstem"], *p["pool_pad"])
         if self.stem.trainable:
             native.stem_wgrad(p["img"], p["dstem"], self.stem.scale, self.stem.wview(self.G))
@@ -606,6 +606,7 @@ class NativeTrainer:
         it = torch.tensor([float(self.iterations), float(self.lr), 0.0, 0.0], device=self.device)
         self.comm.broadcast_(it, root)
         self.iterations, self.lr = int(it[0].item()), float(it[1].item())
+        self.__dict__.pop("_stem_idx", None)      # the packed-stem helper caches the (just replaced) BN scale
         self._refresh_weights()
 
     def _begin_step(self):

@@ -254,7 +254,7 @@ class P2PComm:
         a.max_blocks = 0
         a.has_prescale = int(has_prescale)
         a.external_sync = int(self.external_sync)
-        self.epoch = (self.epoch + 4) & 0x7FFFFFFF
+        self.epoch = (self.epoch + 4) & 0xFFFFFFFF    # wraps mod 2^32 like the device-side counter
         return a
 
     def allreduce_avg(self, bucket: torch.Tensor, out: torch.Tensor, n: int, prescale: bool = True, algo: int = 0):

@@ -33,7 +33,7 @@ sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "library", "reference"])
     ap.add_argument("--backbone", default="resnet50")
@@ -201,6 +201,22 @@ def main():
         e2e = {"value": args.batch * world * args.steps / (ms_e / 1e3), "unit": "images/sec",
                "ms_per_step": ms_e / args.steps, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 12}
 
+    # Every rank must hold bit-identical master weights after the same averaged updates (Horovod's contract,
+    # reference train.py:103,111): compare a checksum of the flat parameter buffer across ranks.
+    replicas_equal = None
+    P = getattr(trainer, "P", None)
+    if P is not None:
+        n_tr = getattr(trainer, "n_train", P.numel())
+        bits = P[:n_tr].view(torch.int32).to(torch.int64)
+        chk = torch.stack([bits.sum(), (bits * (torch.arange(n_tr, device=dev) % 8191 + 1)).sum()]).double()
+        if world > 1:
+            lo, hi = chk.clone(), chk.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            replicas_equal = bool((lo == hi).all().item())
+        else:
+            replicas_equal = True
+
     if rank == 0:
         value = args.batch * world * args.steps / (ms / 1e3)
         line = {
@@ -213,6 +229,7 @@ def main():
                        "parallelism": f"dp{world}", "optimizer": "adam lr1e-5 clipnorm1e-3",
                        "l2_policy": "inputs+activations per step (>2 GB) exceed the 126 MB L2; 4 rotating input sets"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "loss": loss_val,
+            "replicas_equal": replicas_equal,
         }
         print(json.dumps(line))
     if world > 1:

@@ -53,7 +53,8 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 // collective sees a fresh epoch at every replay (a one-thread kernel bumps the counter after each collective).
 __device__ __forceinline__ uint32_t ar_epoch(const ArParams& p) { return p.epoch_ptr ? *p.epoch_ptr : p.epoch; }
 
-__global__ void epoch_bump_kernel(uint32_t* e) { *e = (*e + 4u) & 0x7fffffffu; }
+// The counter wraps mod 2^32; rank_barrier compares with a signed difference, which is wrap-safe.
+__global__ void epoch_bump_kernel(uint32_t* e) { *e = *e + 4u; }
 
 __device__ __forceinline__ void rank_barrier(const ArParams& p, uint32_t value) {
   if (p.external_sync) return;
@@ -236,20 +237,28 @@ __global__ void __launch_bounds__(kArThreads) allreduce_nvls_kernel(const ArPara
   const long long n4 = p.count >> 2;
   const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  const long long per = (n4 + kWorld - 1) / kWorld;
   if (p.has_prescale) {
     const float s = *p.prescale[p.rank];
     if (s != 1.f) {
+      // The in-place pre-scale uses the SAME index -> block mapping as the reduce below (slice r, then
+      // tid + k * nthreads inside it): the elements block b of rank r will ld_reduce were scaled, on every
+      // rank, by that rank's block b, and rank_barrier orders exactly block b of all ranks.  (A flat
+      // i = tid + k * nthreads mapping hands them to a different block, which nothing orders.)
       float4* mine = reinterpret_cast<float4*>(p.bufs[p.rank] + p.offset);
-      for (long long i = tid; i < n4; i += nthreads) {
-        float4 v = mine[i];
-        v.x *= s; v.y *= s; v.z *= s; v.w *= s;
-        mine[i] = v;
+#pragma unroll 1
+      for (int r = 0; r < kWorld; ++r) {
+        const long long r_hi = (r + 1) * per < n4 ? (r + 1) * per : n4;
+        for (long long i = r * per + tid; i < r_hi; i += nthreads) {
+          float4 v = mine[i];
+          v.x *= s; v.y *= s; v.z *= s; v.w *= s;
+          mine[i] = v;
+        }
       }
       __threadfence_system();
     }
   }
   rank_barrier(p, ar_epoch(p) + 1);
-  const long long per = (n4 + kWorld - 1) / kWorld;
   const long long lo = p.rank * per;
   const long long hi = lo + per < n4 ? lo + per : n4;
   const float* in = p.mc_buf + p.offset;

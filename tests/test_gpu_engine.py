@@ -116,7 +116,7 @@ def test_graph_replay_matches_eager_steps():
     identical state.  A multi-step trajectory cannot be compared tightly: two EAGER trainers drift apart just as
     much as a graph / eager pair (fp32 atomics in wgrad make gradients differ by ~1e-8, and Adam's first updates are
     lr * sign(g), so every element whose gradient is zero up to that noise moves by 2 * lr; measured over 14
-    three-arm trials with scripts/debug_graph3.py: both pairs agree to 1e-7 for two steps, then either pair jumps to
+    three-arm trials with scripts/determinism_trials.py: both pairs agree to 1e-7 for two steps, then either pair jumps to
     1e-4 .. 4e-3 in the loss).  So before every compared step the graph trainer takes the eager trainer's state."""
     import copy
     from batchai_retinanet_horovod_coco_b200.engine.trainer import NativeTrainer

@@ -41,6 +41,12 @@ def test_small_fusion_buffer_chunks_large_tensors():
     assert r.returncode == 0, r.stdout + r.stderr
 
 
+def test_allreduce_followed_by_broadcast_in_one_response():
+    r = _launch(3, ["ar_then_bcast"], env={"B200RT_FAULT": "delay:1:3"})
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.count("WORKER_OK") == 3
+
+
 def test_shape_mismatch_is_reported_on_every_rank():
     r = _launch(2, ["mismatch"])
     assert r.returncode == 0, r.stdout + r.stderr

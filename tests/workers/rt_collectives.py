@@ -61,6 +61,22 @@ if mode == "basic":
     want = sum(float(torch.tensor(1.0002 * (k + 1)).half()) for k in range(n))
     assert y.dtype == torch.float32 and abs(y[0].item() - want) < 1e-5, (y, want)   # values travel fp16-rounded
     hvd.timeline_stop()
+elif mode == "ar_then_bcast":
+    # An allreduce and a broadcast released by the SAME response: the root must not overwrite the shared
+    # result area while slower ranks are still copying the allreduce result out of it (the broadcast stages
+    # in the root's own region).  Rank 1 is slowed down by B200RT_FAULT=delay.
+    from batchai_retinanet_horovod_coco_b200.parallel import runtime as _rt
+    nel = 1 << 20
+    for it in range(12):
+        a = torch.full((nel,), float(r + 1 + it))
+        b = torch.full((nel,), -7.0 - it) if r == 0 else torch.zeros(nel)
+        ha = hvd.allreduce_async_(a, average=False, name=f"ar{it}")
+        hb = _rt.enqueue(_rt.BROADCAST, f"bc{it}", b, b, nel, 0)
+        ha.wait()
+        hb.wait()
+        want = float(sum(q + 1 + it for q in range(n)))
+        assert bool((a == want).all()), (it, a.min().item(), a.max().item(), want)
+        assert bool((b == -7.0 - it).all()), (it, b[:4])
 elif mode == "mismatch":
     t = torch.zeros(4 if r == 0 else 5)
     try:
