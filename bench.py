@@ -208,7 +208,7 @@ def main():
     if P is not None:
         n_tr = getattr(trainer, "n_train", P.numel())
         bits = P[:n_tr].view(torch.int32).to(torch.int64)
-        chk = torch.stack([bits.sum(), (bits * (torch.arange(n_tr, device=dev) % 8191 + 1)).sum()]).double()
+        chk = torch.stack([bits.sum(), (bits * (torch.arange(n_tr, device=dev) % 8191 + 1)).sum()])   # int64, exact
         if world > 1:
             lo, hi = chk.clone(), chk.clone()
             dist.all_reduce(lo, op=dist.ReduceOp.MIN)

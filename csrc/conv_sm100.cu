@@ -1,4 +1,4 @@
-// Implicit-GEMM convolution (fprop and dgrad) for sm_100a: TMA + tcgen05.mma + TMEM.
+// Implicit-GEMM convolution (fprop and dgrad) for sm_100a: TMA + tcgen05.mma + TMEM, TMA-fed epilogue.
 //
 //   out[n, y, x, :] = epilogue( sum_{tap} sum_{k} in[n, y + dh(tap), x + dw(tap), k] * w[tap][:, k] )
 //
@@ -7,37 +7,51 @@
 // N = output channels (BN <= 256 per tile), K = taps x input channels (64 per pipeline stage).
 //
 // Warp roles (640 threads, 1 CTA per SM, persistent over tiles):
-//   warp 0   TMA producer  (one lane): A box [64ch, tw, th, 1] + B box [64ch, BN rows, 1 tap]
-//   warp 1   MMA issuer    (one lane): 4 x tcgen05.mma (K=16) per stage, commit -> empty barrier
-//   warp 2   TMEM allocator (512 columns = two 256-column accumulators, double-buffered)
-//   warps 4-19 epilogue (4 per TMEM lane quarter): tcgen05.ld 32 lanes x 32 columns, fused
-//            shift/add/mask/ReLU, swizzled smem transpose, coalesced bf16 loads/stores
+//   warp 0   operand producer (lane 0: activation box [64ch, tw, th, 1], lane 1: weight box [64ch, BN rows, 1 tap])
+//   warp 1   MMA issuer (one lane): 4 x tcgen05.mma (K=16) per stage, commit -> empty barrier
+//   warp 2   TMEM allocator (512 columns = two 256-column accumulators), then the STORE issuer: one TMA store per
+//            finished 128-pixel x 64-channel chunk, then releases the chunk's smem slot
+//   warp 3   epilogue-operand loader: TMA loads of the residual / ReLU-mask chunk of every tile into smem slots,
+//            running ahead of the MMA as far as free slots allow
+//   warps 4-19 epilogue math: tcgen05.ld (32 lanes x 32 columns), + shift, + residual, ReLU mask, ReLU, bf16,
+//            written IN PLACE over the operand chunk in its slot (row-per-thread, conflict-free under the 128 B swizzle)
 //
-// Stride-2 convolutions use one tensor map per input parity class (strided views), so every
-// tap is still a plain shifted box.  Stride-2 dgrad computes one output parity class per launch.
+// The first version of this kernel moved the epilogue operands and results through registers with LSU loads /
+// stores (csrc/conv_v1_sm100.cu): the memory-bound bottleneck layers then ran at 3.2-3.8 TB/s, limited by the epilogue's
+// instruction issue and by how many bytes its loads kept in flight.  Here the epilogue touches global memory only
+// through TMA: nothing but smem <-> register traffic and the math is left in the 16 epilogue warps, and the smem not
+// needed by the operand ring (memory-bound layers have short K loops) becomes up to 12 chunk slots of prefetch depth.
+//
+// Stride-2 convolutions use one tensor map per input parity class (strided views), so every tap is still a plain
+// shifted box.  Stride-2 dgrad computes one output parity class per launch through a strided output map.
 //
 // Replaces cuDNN fprop/dgrad + separate bias/BN/ReLU/add kernels of the reference stack
 // (SURVEY.md G2-G4, G6, G8, G12); the reference itself has no CUDA source.
 #include <cstdlib>
+#include <cstring>
 
 #include "../include/b200_ops.h"
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 
+extern "C" int b200_conv_v1(const B200ConvArgs* a, void* stream_);
+
 namespace b200 {
 
-constexpr int kStages = 4;
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kAStageBytes = kBM * kBK * 2;       // 16 KB
-constexpr int kBStageBytes = 256 * kBK * 2;       // 32 KB (BN <= 256)
+constexpr int kMaxStages = 4;
+constexpr int kMaxSlots = 12;
+constexpr int kSlotBytes = kBM * 64 * 2;          // one [128 pixels][64 channels] bf16 chunk, 128 B rows, SWIZZLE_128B
 constexpr int kMaxTaps = 49;
 constexpr int kMaxMaps = 8;
 constexpr int kTmemCols = 512;
-constexpr int kEpiWarps = 16;                        // 4 warps per TMEM lane quarter (column slots)
+constexpr int kEpiWarps = 16;                     // 4 TMEM lane quarters x 2 column halves x 2 chunk groups
 constexpr int kConvThreads = 128 + 32 * kEpiWarps;
-constexpr int kStagingBytes = kEpiWarps * 2048;      // per epilogue warp: one 32 rows x 64 B buffer
-constexpr int kSmemBytes = kStages * (kAStageBytes + kBStageBytes) + kStagingBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kShiftBytes = kEpiWarps * 128;      // per epilogue warp: the 32 shift values of its current chunk half
+constexpr int kBarBytes = 512;
+constexpr int kSmemLimit = 232448;                // 227 KB
 
 struct Tap {
   int8_t dh, dw, map, pad;
@@ -45,11 +59,6 @@ struct Tap {
 };
 
 struct DevProblem {
-  void* out;
-  const void* add;
-  const void* mask;
-  int N, OH, OW;        // GEMM pixel grid
-  int OHo, OWo;         // output tensor spatial dims
   int tiles_h, tiles_w; // spatial tiles per image
   int tile_begin;       // first m-tile of this problem
   int th_log2, tw_log2;
@@ -59,14 +68,17 @@ struct DevProblem {
 struct ConvParams {
   CUtensorMap in_maps[kMaxMaps];
   CUtensorMap w_map;
+  CUtensorMap out_maps[B200_MAX_PROBLEMS];
+  CUtensorMap add_maps[B200_MAX_PROBLEMS];
+  CUtensorMap mask_maps[B200_MAX_PROBLEMS];
   DevProblem prob[B200_MAX_PROBLEMS];
   Tap taps[kMaxTaps];
   const float* shift;
   int num_problems, num_m_tiles, num_n_tiles;
-  int Nrows, ldo, BN;
+  int Nrows, BN;
   int num_taps, num_kc;
-  int os, oy, ox;       // output scatter: (y*os + oy, x*os + ox)
-  int relu, out_fp32, add_after_mask;
+  int relu, add_after_mask;
+  int stages, slots, b_stage_bytes, smem_bytes;
 };
 
 __device__ __forceinline__ void decode_tile(const ConvParams& p, int tile, int& pi, int& n, int& y0, int& x0,
@@ -88,20 +100,49 @@ __device__ __forceinline__ void decode_tile(const ConvParams& p, int tile, int& 
   x0 = tx << q.tw_log2;
 }
 
+// 64-column chunks of an N tile that hold at least one (8-padded) valid output channel
+__device__ __forceinline__ int tile_chunks(const ConvParams& p, int n_tile) {
+  const int col0 = n_tile * p.BN;
+  const int col_end = min(p.Nrows, col0 + p.BN);
+  return (((col_end + 7) & ~7) - col0 + 63) >> 6;
+}
+
+// Ring of chunk slots.  A chunk takes 1 position (operand loaded in place, or no operand) or 2 (residual + mask).
+struct SlotCursor {
+  int slot;
+  uint32_t par;
+  __device__ __forceinline__ void advance(int n, int nslots) {
+    slot += n;
+    if (slot >= nslots) {
+      slot -= nslots;
+      par ^= 1u;
+    }
+  }
+};
+
 template <bool kAdd, bool kMask>
 __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  constexpr bool kLoads = kAdd || kMask;
+  constexpr int kPPC = (kAdd && kMask) ? 2 : 1;     // slot positions per chunk
+  const int stages = p.stages, nslots = p.slots;
+  const uint32_t raw_base = smem_u32(smem_raw);
+  const uint32_t smem_base = (raw_base + 1023u) & ~1023u;
   const uint32_t a_smem = smem_base;
-  const uint32_t b_smem = smem_base + kStages * kAStageBytes;
-  const uint32_t stg_base = b_smem + kStages * kBStageBytes;
-  const uint32_t bar_base = stg_base + kStagingBytes;
-  // barrier layout (8 bytes each): full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], tmem_ptr
+  const uint32_t b_smem = a_smem + stages * kAStageBytes;
+  const uint32_t slot_base = b_smem + stages * p.b_stage_bytes;
+  const uint32_t shift_base = slot_base + nslots * kSlotBytes;
+  const uint32_t bar_base = shift_base + kShiftBytes;
+  if (bar_base + kBarBytes - raw_base > static_cast<uint32_t>(p.smem_bytes)) __trap();   // layout does not fit
+  // barriers (8 bytes each)
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
-  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
-  const uint32_t tmem_ptr_smem = bar_base + 8u * (2 * kStages + 4);
+  auto empty_bar = [&](int s) { return bar_base + 32u + 8u * s; };
+  auto tfull_bar = [&](int a) { return bar_base + 64u + 8u * a; };
+  auto tempty_bar = [&](int a) { return bar_base + 80u + 8u * a; };
+  auto ldfull_bar = [&](int s) { return bar_base + 96u + 8u * s; };     // operand chunk landed in slot s
+  auto free_bar = [&](int s) { return bar_base + 192u + 8u * s; };      // slot s may be overwritten
+  auto stfull_bar = [&](int s) { return bar_base + 288u + 8u * s; };    // result chunk complete in slot s
+  const uint32_t tmem_ptr_smem = bar_base + 384u;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -112,15 +153,25 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < kMaxMaps; ++i) tma_prefetch_desc(&p.in_maps[i]);
     tma_prefetch_desc(&p.w_map);
+    for (int i = 0; i < p.num_problems; ++i) {
+      tma_prefetch_desc(&p.out_maps[i]);
+      if (kAdd) tma_prefetch_desc(&p.add_maps[i]);
+      if (kMask) tma_prefetch_desc(&p.mask_maps[i]);
+    }
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < kMaxStages; ++s) {
       mbar_init(full_bar(s), 1);
       mbar_init(empty_bar(s), 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
       mbar_init(tempty_bar(a), 32 * kEpiWarps);
+    }
+    for (int s = 0; s < kMaxSlots; ++s) {
+      mbar_init(ldfull_bar(s), 1);
+      mbar_init(free_bar(s), 1);
+      mbar_init(stfull_bar(s), 256);
     }
     fence_barrier_init();
   }
@@ -138,16 +189,15 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   pdl_wait();
 
   if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
+    // ------------------------------------------------------------------ operand producer
     // The whole warp runs the loop; lane 0 arms the barrier and issues the activation box, lane 1 issues
-    // the weight box, so the two TMA issues of a stage overlap (a single issuing thread was measurably
-    // the bottleneck in the weight-gradient kernel).
+    // the weight box, so the two TMA issues of a stage overlap.
     int stage = 0;
     uint32_t phase = 0;
     bool first_pass = true;
-    // Weights stay resident: when the whole K loop fits the ring (num_k divides kStages) and there is a
+    // Weights stay resident: when the whole K loop fits the ring (num_k divides the stage count) and there is a
     // single N tile, stage s always holds the same weight tile, so it is fetched once.
-    const bool weights_resident = (p.num_n_tiles == 1) && (kStages % num_k == 0);
+    const bool weights_resident = (p.num_n_tiles == 1) && (stages % num_k == 0);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       int pi, n, y0, x0, n_tile;
       decode_tile(p, tile, pi, n, y0, x0, n_tile);
@@ -164,8 +214,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           }
           __syncwarp();
           if (lane == 1 && load_b)
-            tma_load_3d(b_smem + stage * kBStageBytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
-          if (++stage == kStages) {
+            tma_load_3d(b_smem + stage * p.b_stage_bytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
+          if (++stage == stages) {
             stage = 0;
             phase ^= 1;
             first_pass = false;
@@ -175,12 +225,15 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    const uint32_t idesc = make_idesc_bf16(kBM, p.BN, 0, 0);
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      // the last N tile may be narrower: do not multiply zero-filled weight rows
+      const int n_tile = tile / p.num_m_tiles;
+      const int cols = min(p.Nrows - n_tile * p.BN, p.BN);
+      const uint32_t idesc = make_idesc_bf16(kBM, max(16, (cols + 15) & ~15), 0, 0);
       mbar_wait(tempty_bar(acc), acc_phase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * 256;
@@ -189,7 +242,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         tc_fence_after();
         if (lane == 0) {
           const uint64_t adesc = make_smem_desc(a_smem + stage * kAStageBytes, 16, 1024);
-          const uint64_t bdesc = make_smem_desc(b_smem + stage * kBStageBytes, 16, 1024);
+          const uint64_t bdesc = make_smem_desc(b_smem + stage * p.b_stage_bytes, 16, 1024);
 #pragma unroll
           for (int k = 0; k < kBK / 16; ++k) {
             // advance 16 bf16 = 32 bytes along K inside the 128B swizzle row: +2 in (addr >> 4) units
@@ -199,7 +252,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           if (kb == num_k - 1) umma_commit(tfull_bar(acc));
         }
         __syncwarp();
-        if (++stage == kStages) {
+        if (++stage == stages) {
           stage = 0;
           phase ^= 1;
         }
@@ -207,148 +260,169 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
-  } else if (warp >= 4) {
-    // ------------------------------------------------------------------ epilogue
-    // 16 warps: warp (quarter q, column slot cq) owns TMEM lanes 32q..32q+31 and the 32-column chunks
-    // cq, cq+4, ... of the tile.  A thread holds one accumulator row, but row-per-thread global
-    // accesses would touch 32 lines per instruction with partial sectors, so every chunk goes through a
-    // warp-private XOR-swizzled 2 KB smem buffer: global <-> smem moves are 8 rows x 64 B per
-    // instruction (sector-complete), smem <-> registers are row-per-thread.  The kernel is latency
-    // bound here for small K (ncu: long_scoreboard), hence 4 warps per scheduler and the mask/residual
-    // loads of a chunk issued back to back before anything waits on them.
-    const int ew = warp - 4;
-    const int quarter = ew & 3;   // TMEM lanes this warp may read: 32 * (warp_id % 4)
-    const int cq = ew >> 2;       // column slot
-    const int m = quarter * 32 + lane;
-    const uint32_t buf = stg_base + ew * 2048;
-    const int crow = lane >> 2, cpiece = lane & 3;
-    const uint32_t own_sw = (lane >> 1) & 3;
-    const uint32_t own_base = buf + lane * 64;
-    uint32_t own_off[4], so_r[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) own_off[j] = own_base + ((static_cast<uint32_t>(j) ^ own_sw) << 4);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int rr = i * 8 + crow;
-      so_r[i] = buf + rr * 64 + ((cpiece ^ ((rr >> 1) & 3)) << 4);
+  } else if (warp == 2) {
+    // ------------------------------------------------------------------ store issuer (one thread)
+    // Waits until all 256 threads of a chunk have written (and proxy-fenced) their results, stores the chunk with
+    // one TMA box -- pixels / channels outside the tensor are clipped by the hardware -- and hands the slot(s)
+    // back once the TMA engine has read them.  One store is in flight per CTA; a 16 KB smem read is short next
+    // to the time a tile takes.
+    if (lane == 0) {
+      SlotCursor cur{0, 0u};
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int pi, n, y0, x0, n_tile;
+        decode_tile(p, tile, pi, n, y0, x0, n_tile);
+        const int nch = tile_chunks(p, n_tile);
+        for (int c = 0; c < nch; ++c) {
+          mbar_wait(stfull_bar(cur.slot), cur.par);
+          if constexpr (kPPC == 2) {
+            int sb = cur.slot + 1;
+            if (sb >= nslots) sb -= nslots;
+            mbar_arrive(free_bar(sb));              // the mask chunk has been consumed
+          }
+          tma_store_4d(&p.out_maps[pi], slot_base + cur.slot * kSlotBytes, n_tile * p.BN + c * 64, x0, y0, n);
+          tma_store_commit();
+          tma_store_wait_read();
+          mbar_arrive(free_bar(cur.slot));
+          cur.advance(kPPC, nslots);
+        }
+      }
     }
+  } else if (warp == 3) {
+    // ------------------------------------------------------------------ epilogue-operand loader (one thread)
+    if constexpr (kLoads) {
+      if (lane == 0) {
+        SlotCursor cur{0, 0u};
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+          int pi, n, y0, x0, n_tile;
+          decode_tile(p, tile, pi, n, y0, x0, n_tile);
+          const int nch = tile_chunks(p, n_tile);
+          for (int c = 0; c < nch; ++c) {
+            const int col = n_tile * p.BN + c * 64;
+            mbar_wait(free_bar(cur.slot), cur.par ^ 1);
+            mbar_expect_tx(ldfull_bar(cur.slot), kSlotBytes);
+            tma_load_4d(slot_base + cur.slot * kSlotBytes, kAdd ? &p.add_maps[pi] : &p.mask_maps[pi],
+                        ldfull_bar(cur.slot), col, x0, y0, n);
+            if constexpr (kPPC == 2) {
+              SlotCursor cb = cur;
+              cb.advance(1, nslots);
+              mbar_wait(free_bar(cb.slot), cb.par ^ 1);
+              mbar_expect_tx(ldfull_bar(cb.slot), kSlotBytes);
+              tma_load_4d(slot_base + cb.slot * kSlotBytes, &p.mask_maps[pi], ldfull_bar(cb.slot), col, x0, y0, n);
+            }
+            cur.advance(kPPC, nslots);
+          }
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue math
+    // Warp (quarter q, half hh, group gi): TMEM lanes 32q..32q+31 (the rows a warp may read are fixed by
+    // warp_id % 4), columns 32hh..32hh+31 of a 64-column chunk, chunks with (running chunk index) % 2 == gi.
+    // A thread owns one pixel row of the chunk: its 4 x 16 B pieces sit at (piece ^ (row & 7)) inside the row's
+    // 128 bytes (SWIZZLE_128B, the layout TMA reads and writes), so a quarter-warp's 16-byte accesses cover all
+    // 32 banks once.
+    const int ew = warp - 4;
+    const int quarter = ew & 3;
+    const int hh = (ew >> 2) & 1;
+    const int gi = ew >> 3;
+    const int m = quarter * 32 + lane;
+    uint32_t poff[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) poff[j] = static_cast<uint32_t>(m) * 128u + (static_cast<uint32_t>((hh * 4 + j) ^ (m & 7)) << 4);
+    const uint32_t shift_s = shift_base + ew * 128;
     const float* __restrict__ shiftp = p.shift;
     const bool relu = p.relu != 0, add_post = p.add_after_mask != 0;
-    const int ldo = p.ldo, BN = p.BN, Nrows = p.Nrows;
+    const int BN = p.BN, Nrows = p.Nrows;
+    SlotCursor cur{0, 0u};
+    int g = 0;                 // running chunk index of this CTA
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      int pi, n, y0, x0, n_tile;
-      decode_tile(p, tile, pi, n, y0, x0, n_tile);
-      const DevProblem& q = p.prob[pi];
-      const int y = y0 + (m >> q.tw_log2);
-      const int x = x0 + (m & ((1 << q.tw_log2) - 1));
-      const bool valid = (y < q.OH) && (x < q.OW);
-      const int pix = (n * q.OHo + (y * p.os + p.oy)) * q.OWo + (x * p.os + p.ox);  // < 2^31 pixels
-      const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
+      const int n_tile = tile / p.num_m_tiles;
       const int col0 = n_tile * BN;
       const int col_end = min(Nrows, col0 + BN);
-      const int col_end_pad = (col_end + 7) & ~7;
-      __nv_bfloat16* __restrict__ outp = static_cast<__nv_bfloat16*>(q.out);
-      const __nv_bfloat16* __restrict__ addp = static_cast<const __nv_bfloat16*>(q.add);
-      const __nv_bfloat16* __restrict__ maskp = static_cast<const __nv_bfloat16*>(q.mask);
-      long long roff_r[4];  // element offset of (row handled in the coalesced pattern, this lane's 16-byte piece)
-      bool ok_r[4];
+      const int nch = tile_chunks(p, n_tile);
+      // my chunks of this tile (at most 2 of the <= 4) and their shift values, requested before the accumulator wait
+      int my_last = -1;
+      float shv[2] = {0.f, 0.f};
+      {
+        int k = 0;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int rr = i * 8 + crow;
-        roff_r[i] = static_cast<long long>(__shfl_sync(0xffffffffu, pix, rr)) * ldo + col0 + cpiece * 8;
-        ok_r[i] = (valid_mask >> rr) & 1u;
-      }
-
-      // A warp owns at most two 32-column chunks of a tile (c0 and c0 + 128).  Their epilogue operands
-      // (residual / ReLU mask: the 64 contiguous bytes of this thread's row, 4 x 16 B, every sector fully
-      // consumed) and the shift row (one coalesced float per lane, broadcast later with shuffles) are all
-      // requested BEFORE waiting for the accumulator: the epilogue is bound by DRAM latency x bytes in
-      // flight, so everything a tile needs is put in flight at once, behind the MMA.
-      constexpr int kChunkStep = 32 * (kEpiWarps / 4);
-      const int c0 = cq * 32;
-      // Operands are fetched in the same COALESCED pattern as the stores (8 rows x 64 B per instruction, lane ->
-      // row i*8 + lane/4, 16-byte piece lane%4) and transposed to row-per-thread through the staging buffer.
-      // Row-per-thread loads touch 32 different 128-byte lines per instruction; the L1 tag stage then caps the
-      // operand stream at ~3.2 TB/s (scripts/epilogue_probe.py), well below what the TMA-fed operands reach.
-      uint4 ka[2][4], km[2][4];
-      float sh[2] = {0.f, 0.f};
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int c = c0 + h * kChunkStep;
-        const bool chunk_ok = c < BN && col0 + c < col_end;
-        const bool pc_ok = chunk_ok && (col0 + c + cpiece * 8 < col_end_pad);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const bool ok = pc_ok && ok_r[i];
-          if constexpr (kMask && !kAdd) km[h][i] = ok ? *reinterpret_cast<const uint4*>(maskp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
-          if constexpr (kAdd && !kMask) ka[h][i] = ok ? *reinterpret_cast<const uint4*>(addp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
-          if constexpr (kAdd && kMask) {
-            if (h == 0) {  // both operands: only the first chunk up front (register budget)
-              km[0][i] = ok ? *reinterpret_cast<const uint4*>(maskp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
-              ka[0][i] = ok ? *reinterpret_cast<const uint4*>(addp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
-            }
+        for (int c = 0; c < 4; ++c) {
+          if (c < nch && ((g + c) & 1) == gi) {
+            my_last = c;
+            const int col = col0 + c * 64 + hh * 32 + lane;
+            if (shiftp && col < Nrows) shv[k] = __ldg(shiftp + col);
+            ++k;
           }
         }
-        if (shiftp && chunk_ok && col0 + c + lane < col_end_pad) sh[h] = __ldg(shiftp + col0 + c + lane);
       }
-      // coalesced layout -> row-per-thread layout (in place in the registers), through the warp's staging buffer
-      auto to_rows = [&](uint4(&v)[4]) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(so_r[i]), "r"(v[i].x), "r"(v[i].y), "r"(v[i].z), "r"(v[i].w) : "memory");
-        __syncwarp();
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w) : "r"(own_off[j]) : "memory");
-        __syncwarp();
-      };
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
+      if (my_last < 0) {
+        tc_fence_before();
+        mbar_arrive(tempty_bar(acc));
+      }
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * 256;
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int c = c0 + h * kChunkStep;
-        const int col = col0 + c;
-        if (c >= BN || col >= col_end) break;
-        const bool piece_ok = col + cpiece * 8 < col_end_pad;
-        if constexpr (kAdd && kMask) {
-          if (h == 1) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const bool ok = piece_ok && ok_r[i];
-              km[1][i] = ok ? *reinterpret_cast<const uint4*>(maskp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
-              ka[1][i] = ok ? *reinterpret_cast<const uint4*>(addp + roff_r[i] + c) : make_uint4(0u, 0u, 0u, 0u);
+      int k = 0;
+      for (int c = 0; c < nch; ++c) {
+        if (((g + c) & 1) == gi) {
+          const int col = col0 + c * 64 + hh * 32;
+          const uint32_t sA = slot_base + cur.slot * kSlotBytes;
+          uint32_t sB = sA;
+          if constexpr (kLoads) {
+            mbar_wait(ldfull_bar(cur.slot), cur.par);
+            if constexpr (kPPC == 2) {
+              SlotCursor cb = cur;
+              cb.advance(1, nslots);
+              mbar_wait(ldfull_bar(cb.slot), cb.par);
+              sB = slot_base + cb.slot * kSlotBytes;
             }
+          } else {
+            mbar_wait(free_bar(cur.slot), cur.par ^ 1);
           }
-        }
-        uint32_t r[32];
-        tmem_ld_32x32(t_row + c, r);
-        if constexpr (kAdd) to_rows(ka[h]);     // the TMEM load is in flight meanwhile
-        if constexpr (kMask) to_rows(km[h]);
-        tmem_ld_wait();
-        // ---- row-per-thread math, result into the staging buffer (issue-bound: keep it short)
+          uint32_t r[32];
+          tmem_ld_32x32(t_row + c * 64 + hh * 32, r);
+          uint4 ka[4], km[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int cj = col + j * 8;
-          float v[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j * 8 + e]);
+          for (int j = 0; j < 4; ++j) {
+            if constexpr (kAdd)
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(ka[j].x), "=r"(ka[j].y), "=r"(ka[j].z), "=r"(ka[j].w) : "r"(sA + poff[j]) : "memory");
+            if constexpr (kMask)
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(km[j].x), "=r"(km[j].y), "=r"(km[j].z), "=r"(km[j].w) : "r"(sB + poff[j]) : "memory");
+          }
           if (shiftp) {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] += __shfl_sync(0xffffffffu, sh[h], j * 8 + e);
+            __syncwarp();
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(shift_s + lane * 4), "f"(k == 0 ? shv[0] : shv[1]) : "memory");
+            __syncwarp();
           }
-          if (valid && cj < col_end) {
+          tmem_ld_wait();
+          if (c == my_last) {          // the accumulator is in registers: the MMA of the tile after next may start
+            tc_fence_before();
+            mbar_arrive(tempty_bar(acc));
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int cj = col + j * 8;
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j * 8 + e]);
+            if (shiftp) {
+              float4 s0, s1;
+              asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(s0.x), "=f"(s0.y), "=f"(s0.z), "=f"(s0.w) : "r"(shift_s + j * 32) : "memory");
+              asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(s1.x), "=f"(s1.y), "=f"(s1.z), "=f"(s1.w) : "r"(shift_s + j * 32 + 16) : "memory");
+              v[0] += s0.x; v[1] += s0.y; v[2] += s0.z; v[3] += s0.w;
+              v[4] += s1.x; v[5] += s1.y; v[6] += s1.z; v[7] += s1.w;
+            }
             if constexpr (kAdd) {
               if (!add_post) {
-                v[0] += bf16_lo(ka[h][j].x); v[1] += bf16_hi(ka[h][j].x); v[2] += bf16_lo(ka[h][j].y); v[3] += bf16_hi(ka[h][j].y);
-                v[4] += bf16_lo(ka[h][j].z); v[5] += bf16_hi(ka[h][j].z); v[6] += bf16_lo(ka[h][j].w); v[7] += bf16_hi(ka[h][j].w);
+                v[0] += bf16_lo(ka[j].x); v[1] += bf16_hi(ka[j].x); v[2] += bf16_lo(ka[j].y); v[3] += bf16_hi(ka[j].y);
+                v[4] += bf16_lo(ka[j].z); v[5] += bf16_hi(ka[j].z); v[6] += bf16_lo(ka[j].w); v[7] += bf16_hi(ka[j].w);
               }
             }
             if constexpr (kMask) {
               // bf16 > 0  <=>  its 16-bit pattern, read as a signed integer, is > 0
-              const uint32_t w4[4] = {km[h][j].x, km[h][j].y, km[h][j].z, km[h][j].w};
+              const uint32_t w4[4] = {km[j].x, km[j].y, km[j].z, km[j].w};
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 if (static_cast<int>(w4[e] << 16) <= 0) v[2 * e] = 0.f;
@@ -357,8 +431,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             }
             if constexpr (kAdd) {
               if (add_post) {
-                v[0] += bf16_lo(ka[h][j].x); v[1] += bf16_hi(ka[h][j].x); v[2] += bf16_lo(ka[h][j].y); v[3] += bf16_hi(ka[h][j].y);
-                v[4] += bf16_lo(ka[h][j].z); v[5] += bf16_hi(ka[h][j].z); v[6] += bf16_lo(ka[h][j].w); v[7] += bf16_hi(ka[h][j].w);
+                v[0] += bf16_lo(ka[j].x); v[1] += bf16_hi(ka[j].x); v[2] += bf16_lo(ka[j].y); v[3] += bf16_hi(ka[j].y);
+                v[4] += bf16_lo(ka[j].z); v[5] += bf16_hi(ka[j].z); v[6] += bf16_lo(ka[j].w); v[7] += bf16_hi(ka[j].w);
               }
             }
             if (relu) {
@@ -372,23 +446,15 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             }
             const uint32_t o0 = pack_bf16x2(v[0], v[1]), o1 = pack_bf16x2(v[2], v[3]);
             const uint32_t o2 = pack_bf16x2(v[4], v[5]), o3 = pack_bf16x2(v[6], v[7]);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_off[j]), "r"(o0), "r"(o1), "r"(o2), "r"(o3) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sA + poff[j]), "r"(o0), "r"(o1), "r"(o2), "r"(o3) : "memory");
           }
+          fence_proxy_async();
+          mbar_arrive(stfull_bar(cur.slot));
+          ++k;
         }
-        __syncwarp();
-        // ---- coalesced smem -> global store
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          if (ok_r[i] && piece_ok) {
-            uint4 t;
-            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(t.x), "=r"(t.y), "=r"(t.z), "=r"(t.w) : "r"(so_r[i]));
-            *reinterpret_cast<uint4*>(outp + roff_r[i] + c) = t;
-          }
-        }
-        __syncwarp();
+        cur.advance(kPPC, nslots);
       }
-      tc_fence_before();
-      mbar_arrive(tempty_bar(acc));
+      g += nch;
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
@@ -419,42 +485,38 @@ static void pick_tile(int OH, int OW, int& th_log2, int& tw_log2) {
   }
 }
 
-static int pick_bn(int nrows) {
-  if (nrows <= 256) return (nrows + 15) / 16 * 16;
-  // largest multiple of 16 <= 256 that minimises padded work
-  int best = 256;
-  long long best_cost = -1;
-  for (int bn = 256; bn >= 128; bn -= 16) {
-    const long long tiles = (nrows + bn - 1) / bn;
-    const long long cost = tiles * bn;
-    if (best_cost < 0 || cost < best_cost) {
-      best_cost = cost;
-      best = bn;
-    }
+// One N tile when the output channels fit 256 columns; otherwise 256-column tiles (a multiple of the 64-column
+// store chunk, so a chunk never straddles two N tiles; the last tile's MMA is narrowed to its valid columns).
+static int pick_bn(int nrows) { return nrows <= 256 ? (nrows + 15) / 16 * 16 : 256; }
+
+template <bool kAdd, bool kMask>
+static int launch_variant(const ConvParams& p, int grid, cudaStream_t stream) {
+  static std::atomic<unsigned long long> attr_set{0};   // per device
+  if (device_needs_setup(attr_set)) {
+    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<kAdd, kMask>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    device_setup_done(attr_set);
   }
-  return best;
+  launch_pdl(conv_igemm_kernel<kAdd, kMask>, grid, kConvThreads, static_cast<size_t>(p.smem_bytes), stream, p);
+  return check_launch("conv_igemm_kernel");
 }
 
 }  // namespace b200
 
 extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   using namespace b200;
+  static int impl = -1;
+  if (impl < 0) {
+    const char* e = getenv("B200_CONV_IMPL");
+    impl = e ? atoi(e) : 2;
+  }
+  if (impl == 1) return b200_conv_v1(a, stream_);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!a || a->num_problems < 1 || a->num_problems > B200_MAX_PROBLEMS) return set_error(-1, "b200_conv: bad num_problems");
   if (a->stride != 1 && a->stride != 2) return set_error(-1, "b200_conv: stride must be 1 or 2");
   if (a->stride == 2 && a->num_problems != 1) return set_error(-1, "b200_conv: grouped launch needs stride 1");
   if (a->KH * a->KW > kMaxTaps) return set_error(-1, "b200_conv: too many taps");
   if ((a->ldi % 8) || (a->ldw % 8) || (a->ldo % 8)) return set_error(-1, "b200_conv: ld* must be multiples of 8");
-
   if (a->out_fp32) return set_error(-1, "b200_conv: fp32 output is not supported (bf16 activations only)");
-  static std::atomic<unsigned long long> attr_set{0};   // per device
-  if (device_needs_setup(attr_set)) {
-    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    device_setup_done(attr_set);
-  }
   const bool has_add = a->prob[0].add != nullptr, has_mask = a->prob[0].mask != nullptr;
   for (int i = 1; i < a->num_problems; ++i)
     if ((a->prob[i].add != nullptr) != has_add || (a->prob[i].mask != nullptr) != has_mask)
@@ -464,16 +526,13 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   memset(&p, 0, sizeof(p));
   p.num_problems = a->num_problems;
   p.Nrows = a->Nrows;
-  p.ldo = a->ldo;
   p.BN = pick_bn(a->Nrows);
   p.num_n_tiles = (a->Nrows + p.BN - 1) / p.BN;
   p.num_kc = (a->K + kBK - 1) / kBK;
   p.shift = a->shift;
   p.relu = a->relu;
-  p.out_fp32 = a->out_fp32;
   p.add_after_mask = a->add_after_mask;
-  p.os = 1;
-  p.oy = p.ox = 0;
+  int os = 1, oy = 0, ox = 0;   // output scatter: (y*os + oy, x*os + ox)
 
   // ---- tap table
   const int s = a->stride;
@@ -493,9 +552,9 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
       }
   } else {
     if (s == 2) {
-      p.os = 2;
-      p.oy = a->par_y;
-      p.ox = a->par_x;
+      os = 2;
+      oy = a->par_y;
+      ox = a->par_x;
     }
     for (int r = 0; r < a->KH; ++r)
       for (int c = 0; c < a->KW; ++c) {
@@ -517,27 +576,23 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   // ---- problems + tensor maps
   int tile_begin = 0;
   int map_count = 0;
+  const unsigned long long c8 = static_cast<unsigned long long>((a->Nrows + 7) / 8 * 8);   // stored channels
   for (int i = 0; i < a->num_problems; ++i) {
     const B200ConvProblem& q = a->prob[i];
     DevProblem& d = p.prob[i];
-    d.out = q.out;
-    d.add = q.add;
-    d.mask = q.mask;
-    d.N = q.N;
-    d.OHo = q.OHo;
-    d.OWo = q.OWo;
+    int OH, OW;   // GEMM pixel grid
     if (a->mode == 1 && s == 2) {
-      d.OH = (q.OHo - a->par_y + 1) / 2;
-      d.OW = (q.OWo - a->par_x + 1) / 2;
+      OH = (q.OHo - a->par_y + 1) / 2;
+      OW = (q.OWo - a->par_x + 1) / 2;
     } else {
-      d.OH = q.OHo;
-      d.OW = q.OWo;
+      OH = q.OHo;
+      OW = q.OWo;
     }
-    if (d.OH <= 0 || d.OW <= 0) return set_error(-1, "b200_conv: empty problem");
-    pick_tile(d.OH, d.OW, d.th_log2, d.tw_log2);
+    if (OH <= 0 || OW <= 0) return set_error(-1, "b200_conv: empty problem");
+    pick_tile(OH, OW, d.th_log2, d.tw_log2);
     const int th = 1 << d.th_log2, tw = 1 << d.tw_log2;
-    d.tiles_h = (d.OH + th - 1) / th;
-    d.tiles_w = (d.OW + tw - 1) / tw;
+    d.tiles_h = (OH + th - 1) / th;
+    d.tiles_w = (OW + tw - 1) / tw;
     d.tile_begin = tile_begin;
     tile_begin += q.N * d.tiles_h * d.tiles_w;
     d.map_base = map_count;
@@ -559,6 +614,27 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
       if (rc) return rc;
     }
     map_count += nmaps;
+    // output-geometry maps (out / residual / mask): 64-channel x tw x th boxes over the GEMM pixel grid, which for a
+    // stride-2 dgrad parity class is a strided view of the output tensor
+    {
+      const long long off = (static_cast<long long>(oy) * q.OWo + ox) * a->ldo;
+      unsigned long long dims[4] = {c8, static_cast<unsigned long long>(OW), static_cast<unsigned long long>(OH),
+                                    static_cast<unsigned long long>(q.N)};
+      unsigned long long strides[3] = {static_cast<unsigned long long>(os) * a->ldo * 2ull,
+                                       static_cast<unsigned long long>(os) * q.OWo * a->ldo * 2ull,
+                                       static_cast<unsigned long long>(q.OHo) * q.OWo * a->ldo * 2ull};
+      const unsigned int obox[4] = {64u, static_cast<unsigned>(tw), static_cast<unsigned>(th), 1u};
+      int rc = make_tmap_bf16(&p.out_maps[i], static_cast<const __nv_bfloat16*>(q.out) + off, 4, dims, strides, obox);
+      if (rc) return rc;
+      if (has_add) {
+        rc = make_tmap_bf16(&p.add_maps[i], static_cast<const __nv_bfloat16*>(q.add) + off, 4, dims, strides, obox);
+        if (rc) return rc;
+      }
+      if (has_mask) {
+        rc = make_tmap_bf16(&p.mask_maps[i], static_cast<const __nv_bfloat16*>(q.mask) + off, 4, dims, strides, obox);
+        if (rc) return rc;
+      }
+    }
   }
   p.num_m_tiles = tile_begin;
   {
@@ -573,11 +649,33 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   // unused map slots must still be valid descriptors for the prefetch: replicate slot 0
   for (int i = map_count; i < kMaxMaps; ++i) p.in_maps[i] = p.in_maps[0];
 
+  // ---- shared-memory split between the operand ring and the epilogue chunk slots.
+  // Short K loops (the memory-bound 1x1 layers) need few ring stages -- the weights stay resident and one stage is one
+  // whole tile -- and give the rest to chunk slots = bytes of residual / mask / result in flight per SM.
+  const int num_k = nt * p.num_kc;
+  const int ppc = (has_add && has_mask) ? 2 : 1;
+  p.b_stage_bytes = p.BN * kBK * 2;
+  int stages = num_k >= kMaxStages ? kMaxStages : (num_k < 2 ? 2 : num_k);
+  const int fixed = kShiftBytes + kBarBytes;
+  auto slots_for = [&](int st) {
+    int sl = (kSmemLimit - fixed - st * (kAStageBytes + p.b_stage_bytes)) / kSlotBytes;
+    if (sl > kMaxSlots) sl = kMaxSlots;
+    if (ppc == 2) sl &= ~1;
+    return sl;
+  };
+  while (stages > 2 && slots_for(stages) < 2 * ppc) --stages;
+  p.stages = stages;
+  p.slots = slots_for(stages);
+  if (p.slots < 2 * ppc) return set_error(-1, "b200_conv: shared-memory layout does not fit");
+  {
+    const int need = stages * (kAStageBytes + p.b_stage_bytes) + p.slots * kSlotBytes + fixed;
+    p.smem_bytes = need + 1024 <= kSmemLimit ? need + 1024 : kSmemLimit;   // the base is 1024-aligned in practice
+  }
+
   const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles;
   const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
-  if (has_add && has_mask) launch_pdl(conv_igemm_kernel<true, true>, grid, kConvThreads, kSmemBytes, stream, p);
-  else if (has_add) launch_pdl(conv_igemm_kernel<true, false>, grid, kConvThreads, kSmemBytes, stream, p);
-  else if (has_mask) launch_pdl(conv_igemm_kernel<false, true>, grid, kConvThreads, kSmemBytes, stream, p);
-  else launch_pdl(conv_igemm_kernel<false, false>, grid, kConvThreads, kSmemBytes, stream, p);
-  return check_launch("conv_igemm_kernel");
+  if (has_add && has_mask) return launch_variant<true, true>(p, grid, stream);
+  if (has_add) return launch_variant<true, false>(p, grid, stream);
+  if (has_mask) return launch_variant<false, true>(p, grid, stream);
+  return launch_variant<false, false>(p, grid, stream);
 }
