@@ -334,8 +334,11 @@ class NativeTrainer:
             a0 = acts[si][0]
             f = st[0]["a"].cout
             ho, wo = a0["hw"]
-            gb.append({"g": buf(ho, wo, f * 4), "ga": buf(ho, wo, f), "gb": buf(ho, wo, f),
-                       "gx": buf(*a0["in_hw"], st[0]["a"].cin), "tmp": buf(*a0["in_hw"], st[0]["a"].cin)})
+            # gx = gradient w.r.t. the stage's input = the previous stage's output gradient: the same buffer
+            gx = gb[si - 1]["g"] if si > 0 else buf(*a0["in_hw"], st[0]["a"].cin)
+            assert tuple(gx.shape[1:]) == (*a0["in_hw"], st[0]["a"].cin)
+            gb.append({"g": buf(ho, wo, f * 4), "ga": buf(ho, wo, f), "gb": buf(ho, wo, f), "gx": gx,
+                       "tmp": buf(*a0["in_hw"], st[0]["a"].cin) if si == 0 else None})
         p["gb"] = gb
         p["dstem"] = torch.empty(B, h1, w1, 64, device=dev, dtype=BF16)
         return acts[1][-1]["hw"], acts[2][-1]["hw"], acts[3][-1]["hw"]
@@ -397,34 +400,42 @@ class NativeTrainer:
         native.conv_raw(0, [(x, o, None, None) for x, o in zip(xs, outs)], c.wf, c.cin, xs[0].shape[-1], c.cout,
                         outs[0].shape[-1], c.kh, c.kw, 1, c.kh // 2, c.kw // 2, shift=c.bview(self.P), relu=relu)
 
-    def _dgrad(self, c: Conv, dy, out, mask=None, add=None, add_after_mask=False):
-        """Gradient w.r.t. the conv input.  out [N,H,W,cin]."""
+    def _dgrad(self, c: Conv, dy, out, mask=None, add=None, add_after_mask=False, colsum=None):
+        """Gradient w.r.t. the conv input.  out [N,H,W,cin].  ``colsum``: fp32 vector that receives the sum of ``out``
+        over pixels -- the bias gradient of the layer whose dY this is -- computed by the kernel's store warp
+        (with stride 2 every parity class must then have taps, which holds for 3x3)."""
         h, w = out.shape[1:3]
         ph, pw, _, _ = c.pads(h, w)
         if c.stride == 1:
-            native.conv_raw(1, [(dy, out, add, mask)], c.wd, c.cout, dy.shape[-1], c.cin, out.shape[-1], c.kh, c.kw, 1,
-                            ph, pw, add_after_mask=add_after_mask)
+            native.conv_raw(1, [(dy, out, add, mask, colsum)], c.wd, c.cout, dy.shape[-1], c.cin, out.shape[-1], c.kh,
+                            c.kw, 1, ph, pw, add_after_mask=add_after_mask)
             return
         for py in range(2):
             for px in range(2):
                 ok = any((py + ph - r) % 2 == 0 for r in range(c.kh)) and any((px + pw - s) % 2 == 0 for s in range(c.kw))
+                assert ok or colsum is None
                 if ok:
-                    native.conv_raw(1, [(dy, out, add, mask)], c.wd, c.cout, dy.shape[-1], c.cin, out.shape[-1], c.kh,
-                                    c.kw, 2, ph, pw, par=(py, px), add_after_mask=add_after_mask)
+                    native.conv_raw(1, [(dy, out, add, mask, colsum)], c.wd, c.cout, dy.shape[-1], c.cin, out.shape[-1],
+                                    c.kh, c.kw, 2, ph, pw, par=(py, px), add_after_mask=add_after_mask)
 
-    def _dgrad_group(self, c: Conv, dys, outs, masks=None, adds=None):
-        probs = [(dy, o, None if adds is None else adds[i], None if masks is None else masks[i])
-                 for i, (dy, o) in enumerate(zip(dys, outs))]
+    def _dgrad_group(self, c: Conv, dys, outs, masks=None, adds=None, colsums=None):
+        probs = [(dy, o, None if adds is None else adds[i], None if masks is None else masks[i],
+                  None if colsums is None else colsums[i]) for i, (dy, o) in enumerate(zip(dys, outs))]
         native.conv_raw(1, probs, c.wd, c.cout, dys[0].shape[-1], c.cin, outs[0].shape[-1], c.kh, c.kw, 1, c.kh // 2,
                         c.kw // 2)
 
-    def _wgrad(self, c: Conv, xs, dys):
+    def _wgrad(self, c: Conv, xs, dys, dbias=True):
+        """``dbias=False``: the bias gradient was already produced by the kernel that wrote ``dys`` (colsum)."""
         if not c.trainable:
             return
         h, w = xs[0].shape[1:3]
         ph, pw, _, _ = c.pads(h, w)
         native.wgrad_raw(list(zip(xs, dys)), c.wview(self.G), c.cin, xs[0].shape[-1], c.cout, dys[0].shape[-1], c.kh,
-                         c.kw, c.stride, ph, pw, rowscale=c.scale, dbias=c.bview(self.G) if c.has_bias else None)
+                         c.kw, c.stride, ph, pw, rowscale=c.scale,
+                         dbias=c.bview(self.G) if (c.has_bias and dbias) else None)
+
+    def _bias_grad(self, c: Conv):
+        return c.bview(self.G) if (c.has_bias and c.trainable) else None
 
     # ------------------------------------------------------------------ forward
     def _forward(self, p, images_u8, img_hw=None):
@@ -497,16 +508,22 @@ class NativeTrainer:
         first = True
         for tower, outc, ts, douts in ((self.cls_tower, self.cls_out, p["cls_t"], p["dcls_o"]),
                                        (self.reg_tower, self.reg_out, p["reg_t"], p["dreg_o"])):
+            # Bias gradients: the dgrad that PRODUCES a layer's dY also sums it over pixels (store-warp column sums),
+            # so only the two output convs, whose dY comes from the loss kernels, and C4_reduced, whose dY is
+            # touched up by the upsample backward, still run the column-sum kernel.
             self._wgrad(outc, ts[3], douts)
             cur = p["dt"][0]
-            self._dgrad_group(outc, douts, cur, masks=ts[3])
+            self._dgrad_group(outc, douts, cur, masks=ts[3], colsums=[self._bias_grad(tower[3])] * 5)
             for i in (3, 2, 1):
-                self._wgrad(tower[i], ts[i - 1], cur)
+                self._wgrad(tower[i], ts[i - 1], cur, dbias=False)
                 nxt = p["dt"][1] if cur is p["dt"][0] else p["dt"][0]
-                self._dgrad_group(tower[i], cur, nxt, masks=ts[i - 1])
+                self._dgrad_group(tower[i], cur, nxt, masks=ts[i - 1], colsums=[self._bias_grad(tower[i - 1])] * 5)
                 cur = nxt
-            self._wgrad(tower[0], feats, cur)
-            self._dgrad_group(tower[0], cur, dP, adds=None if first else dP)
+            self._wgrad(tower[0], feats, cur, dbias=False)
+            pbias = None if first else [self._bias_grad(f[n]) for n in ("P3", "P4", "P5", "P6", "P7")]
+            if pbias is not None:
+                pbias[3] = None        # P6's dY also gets P7's gradient below
+            self._dgrad_group(tower[0], cur, dP, adds=None if first else dP, colsums=pbias)
             first = False
         self._mark("bwd_heads")
         dP3, dP4, dP5, dP6, dP7 = dP
@@ -514,20 +531,20 @@ class NativeTrainer:
         c3, c4, c5 = p["C"]
         P6 = feats[3]
         # P7 = conv(relu(P6)); P6 also feeds the heads directly
-        self._wgrad(f["P7"], [fp["r6"]], [dP7])
-        self._dgrad(f["P7"], dP7, df["p6"], mask=P6, add=dP6, add_after_mask=True)
-        self._wgrad(f["P6"], [c5], [df["p6"]])
+        self._wgrad(f["P7"], [fp["r6"]], [dP7], dbias=False)
+        self._dgrad(f["P7"], dP7, df["p6"], mask=P6, add=dP6, add_after_mask=True, colsum=self._bias_grad(f["P6"]))
+        self._wgrad(f["P6"], [c5], [df["p6"]], dbias=False)
         # P3 branch
-        self._wgrad(f["P3"], [fp["m3"]], [dP3])
-        self._dgrad(f["P3"], dP3, df["m3"])
-        self._wgrad(f["C3_reduced"], [c3], [df["m3"]])
+        self._wgrad(f["P3"], [fp["m3"]], [dP3], dbias=False)
+        self._dgrad(f["P3"], dP3, df["m3"], colsum=self._bias_grad(f["C3_reduced"]))
+        self._wgrad(f["C3_reduced"], [c3], [df["m3"]], dbias=False)
         # P4 branch
-        self._wgrad(f["P4"], [fp["m4"]], [dP4])
+        self._wgrad(f["P4"], [fp["m4"]], [dP4], dbias=False)
         self._dgrad(f["P4"], dP4, df["m4"])
         native.upsample_bwd_add(df["m3"], df["m4"])
         self._wgrad(f["C4_reduced"], [c4], [df["m4"]])
         # P5 branch
-        self._wgrad(f["P5"], [fp["c5r"]], [dP5])
+        self._wgrad(f["P5"], [fp["c5r"]], [dP5], dbias=False)
         self._dgrad(f["P5"], dP5, df["c5r"])
         native.upsample_bwd_add(df["m4"], df["c5r"])
         self._wgrad(f["C5_reduced"], [c5], [df["c5r"]])
@@ -566,23 +583,19 @@ class NativeTrainer:
                         self._dgrad(d["s"], g, b["tmp"])
                         self._dgrad(d["a"], b["ga"], gx, mask=x, add=b["tmp"])
                     else:
-                        gx.zero_()
-                        self._dgrad(d["s"], g, gx)
-                        self._dgrad(d["a"], b["ga"], gx, add=gx)
-                        # + FPN lateral gradient of the previous stage's output, then its ReLU mask
+                        # Stride-2 block: the 1x1/2 convs reach only the even-even pixels of x.  Every contribution is
+                        # masked by x's ReLU inside its own kernel (the mask distributes over the sum), so no
+                        # separate add / mask / copy passes: the FPN lateral's dgrad (all pixels) or a zero fill
+                        # comes first, then the two strided dgrads accumulate in place.
                         if (si - 1) in extra:
                             lat, dlat = extra[si - 1]
-                            self._dgrad(lat, dlat, b["tmp"])
-                            native.add_mask(gx, b["tmp"], x, gx)
+                            self._dgrad(lat, dlat, gx, mask=x)
                         else:
-                            native.add_mask(gx, None, x, gx)
+                            gx.zero_()
+                        self._dgrad(d["s"], g, gx, mask=x, add=gx, add_after_mask=True)
+                        self._dgrad(d["a"], b["ga"], gx, mask=x, add=gx, add_after_mask=True)
                     g_next = gx
-            if si > 0:
-                # gx has the geometry of stage si-1's output: copy into that stage's g buffer
-                gb[si - 1]["g"].copy_(g_next)
-                g = gb[si - 1]["g"]
-            else:
-                g = g_next
+            g = g_next      # stage si-1's output gradient (gb[si-1]["g"] is the same buffer as this stage's gx)
         self._mark("bwd_backbone")
         # stem: max-pool + ReLU + BN backward, then the native weight-gradient kernel for the 7x7x3 filter
         native.bn_relu_maxpool_bwd(p["pool_idx"], self.ones64, g, p["dstem"], *p["pool_pad"])

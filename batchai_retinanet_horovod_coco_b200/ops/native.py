@@ -26,7 +26,8 @@ MAX_PROBLEMS = 5
 
 class ConvProblem(C.Structure):
     _fields_ = [("inp", C.c_void_p), ("out", C.c_void_p), ("add", C.c_void_p), ("mask", C.c_void_p),
-                ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("OHo", C.c_int), ("OWo", C.c_int)]
+                ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("OHo", C.c_int), ("OWo", C.c_int),
+                ("colsum", C.c_void_p)]
 
 
 class ConvArgs(C.Structure):
@@ -134,13 +135,16 @@ def same_pad_before(n: int, k: int, s: int) -> int:
 def conv_raw(mode: int, problems, weight: torch.Tensor, K: int, ldi: int, Nrows: int, ldo: int, KH: int, KW: int,
              stride: int, pad_h: int, pad_w: int, shift=None, relu=False, out_fp32=False, par=(0, 0),
              add_after_mask=False):
-    """problems: list of (inp, out, add, mask) NHWC tensors.  weight: bf16 [taps, Nrows, ldw]."""
+    """problems: list of (inp, out, add, mask[, colsum]) NHWC tensors (colsum: fp32 [Nrows] vector that receives
+    += the sum of ``out`` over pixels).  weight: bf16 [taps, Nrows, ldw]."""
     lib = require()
     a = ConvArgs()
     a.mode = mode
     a.num_problems = len(problems)
-    for i, (inp, out, add, mask) in enumerate(problems):
+    for i, prob in enumerate(problems):
+        inp, out, add, mask = prob[:4]
         p = a.prob[i]
+        p.colsum = 0 if len(prob) < 5 or prob[4] is None else prob[4].data_ptr()
         p.inp, p.out = inp.data_ptr(), out.data_ptr()
         p.add = 0 if add is None else add.data_ptr()
         p.mask = 0 if mask is None else mask.data_ptr()

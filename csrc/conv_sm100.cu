@@ -10,15 +10,16 @@
 //   warp 0   operand producer (lane 0: activation box [64ch, tw, th, 1], lane 1: weight box [64ch, BN rows, 1 tap])
 //   warp 1   MMA issuer (one lane): 4 x tcgen05.mma (K=16) per stage, commit -> empty barrier
 //   warp 2   TMEM allocator (512 columns = two 256-column accumulators), then the STORE issuer: one TMA store per
-//            finished 128-pixel x 64-channel chunk, then releases the chunk's smem slot
+//            finished 128-pixel x 64-channel chunk, then releases the chunk's smem slot.  Optionally sums the
+//            chunk's columns first (the bias gradient of the layer that consumes this output as its dY)
 //   warp 3   epilogue-operand loader: TMA loads of the residual / ReLU-mask chunk of every tile into smem slots,
 //            running ahead of the MMA as far as free slots allow
 //   warps 4-19 epilogue math: tcgen05.ld (32 lanes x 32 columns), + shift, + residual, ReLU mask, ReLU, bf16,
 //            written IN PLACE over the operand chunk in its slot (row-per-thread, conflict-free under the 128 B swizzle)
 //
-// The first version of this kernel moved the epilogue operands and results through registers with LSU loads /
-// stores (csrc/conv_v1_sm100.cu): the memory-bound bottleneck layers then ran at 3.2-3.8 TB/s, limited by the epilogue's
-// instruction issue and by how many bytes its loads kept in flight.  Here the epilogue touches global memory only
+// The first version of this kernel (git history: round 1) moved the epilogue operands and results through registers
+// with LSU loads / stores: the memory-bound bottleneck layers then ran at 3.2-3.8 TB/s, limited by the epilogue's
+// instruction issue and by how many bytes its loads kept in flight (18.60 -> 17.67 ms per step at batch 8).  Here the epilogue touches global memory only
 // through TMA: nothing but smem <-> register traffic and the math is left in the 16 epilogue warps, and the smem not
 // needed by the operand ring (memory-bound layers have short K loops) becomes up to 12 chunk slots of prefetch depth.
 //
@@ -33,8 +34,6 @@
 #include "../include/b200_ops.h"
 #include "common.cuh"
 #include "ptx_sm100.cuh"
-
-extern "C" int b200_conv_v1(const B200ConvArgs* a, void* stream_);
 
 namespace b200 {
 
@@ -59,6 +58,7 @@ struct Tap {
 };
 
 struct DevProblem {
+  int OH, OW;           // GEMM pixel grid
   int tiles_h, tiles_w; // spatial tiles per image
   int tile_begin;       // first m-tile of this problem
   int th_log2, tw_log2;
@@ -74,6 +74,7 @@ struct ConvParams {
   DevProblem prob[B200_MAX_PROBLEMS];
   Tap taps[kMaxTaps];
   const float* shift;
+  float* colsum[B200_MAX_PROBLEMS];   // optional: += column sums of the problem's output (fp32 [Nrows])
   int num_problems, num_m_tiles, num_n_tiles;
   int Nrows, BN;
   int num_taps, num_kc;
@@ -266,26 +267,81 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     // one TMA box -- pixels / channels outside the tensor are clipped by the hardware -- and hands the slot(s)
     // back once the TMA engine has read them.  One store is in flight per CTA; a 16 KB smem read is short next
     // to the time a tile takes.
-    if (lane == 0) {
+    //
+    // Column sums (bias gradients): when the output of this launch is the dY of a biased layer, its bias gradient
+    // is the sum of this tensor over pixels.  The finished chunk sits in smem anyway, so the warp adds up its
+    // columns (lane -> 2 adjacent channels, 128 conflict-free 4-byte reads) before the store, keeps the sums in
+    // registers over all tiles of one (problem, N tile) and flushes them with one atomic per column.  Rows of a
+    // tile that lie outside the pixel grid are skipped: their accumulators are not zero (a tap can reach back
+    // into the image), only their store is clipped.
+    {
       SlotCursor cur{0, 0u};
+      float cs[4][2];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) cs[c][0] = cs[c][1] = 0.f;
+      int cs_pi = -1, cs_nt = -1;
+      auto flush = [&]() {
+        if (cs_pi >= 0) {
+          float* dst = p.colsum[cs_pi];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const int col = cs_nt * p.BN + c * 64 + 2 * lane;
+            if (col < p.Nrows && cs[c][0] != 0.f) atomicAdd(dst + col, cs[c][0]);
+            if (col + 1 < p.Nrows && cs[c][1] != 0.f) atomicAdd(dst + col + 1, cs[c][1]);
+            cs[c][0] = cs[c][1] = 0.f;
+          }
+        }
+      };
+      const uint32_t cs_off = (static_cast<uint32_t>(lane & 3) << 2);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         int pi, n, y0, x0, n_tile;
         decode_tile(p, tile, pi, n, y0, x0, n_tile);
         const int nch = tile_chunks(p, n_tile);
-        for (int c = 0; c < nch; ++c) {
-          mbar_wait(stfull_bar(cur.slot), cur.par);
-          if constexpr (kPPC == 2) {
-            int sb = cur.slot + 1;
-            if (sb >= nslots) sb -= nslots;
-            mbar_arrive(free_bar(sb));              // the mask chunk has been consumed
+        const bool do_cs = p.colsum[pi] != nullptr;
+        if (do_cs && (pi != cs_pi || n_tile != cs_nt)) {
+          flush();
+          cs_pi = pi;
+          cs_nt = n_tile;
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (c < nch) {
+            mbar_wait(stfull_bar(cur.slot), cur.par);
+            const uint32_t sA = slot_base + cur.slot * kSlotBytes;
+            if (do_cs) {
+              const DevProblem& q = p.prob[pi];
+              const int ny = q.OH - y0, nx = q.OW - x0, twm = (1 << q.tw_log2) - 1;
+              float s0 = 0.f, s1 = 0.f;
+#pragma unroll 16
+              for (int row = 0; row < kBM; ++row) {
+                // unconditional load + select (a branch here would serialise the 128 smem round trips)
+                uint32_t w;
+                asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(sA + row * 128 + (((lane >> 2) ^ (row & 7)) << 4) + cs_off));
+                if ((row >> q.tw_log2) >= ny || (row & twm) >= nx) w = 0u;
+                s0 += bf16_lo(w);
+                s1 += bf16_hi(w);
+              }
+              cs[c][0] += s0;
+              cs[c][1] += s1;
+              __syncwarp();
+            }
+            if (lane == 0) {
+              if constexpr (kPPC == 2) {
+                int sb = cur.slot + 1;
+                if (sb >= nslots) sb -= nslots;
+                mbar_arrive(free_bar(sb));              // the mask chunk has been consumed
+              }
+              tma_store_4d(&p.out_maps[pi], sA, n_tile * p.BN + c * 64, x0, y0, n);
+              tma_store_commit();
+              tma_store_wait_read();
+              mbar_arrive(free_bar(cur.slot));
+            }
+            __syncwarp();
+            cur.advance(kPPC, nslots);
           }
-          tma_store_4d(&p.out_maps[pi], slot_base + cur.slot * kSlotBytes, n_tile * p.BN + c * 64, x0, y0, n);
-          tma_store_commit();
-          tma_store_wait_read();
-          mbar_arrive(free_bar(cur.slot));
-          cur.advance(kPPC, nslots);
         }
       }
+      flush();
     }
   } else if (warp == 3) {
     // ------------------------------------------------------------------ epilogue-operand loader (one thread)
@@ -504,12 +560,6 @@ static int launch_variant(const ConvParams& p, int grid, cudaStream_t stream) {
 
 extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   using namespace b200;
-  static int impl = -1;
-  if (impl < 0) {
-    const char* e = getenv("B200_CONV_IMPL");
-    impl = e ? atoi(e) : 2;
-  }
-  if (impl == 1) return b200_conv_v1(a, stream_);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!a || a->num_problems < 1 || a->num_problems > B200_MAX_PROBLEMS) return set_error(-1, "b200_conv: bad num_problems");
   if (a->stride != 1 && a->stride != 2) return set_error(-1, "b200_conv: stride must be 1 or 2");
@@ -530,6 +580,7 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   p.num_n_tiles = (a->Nrows + p.BN - 1) / p.BN;
   p.num_kc = (a->K + kBK - 1) / kBK;
   p.shift = a->shift;
+  for (int i = 0; i < a->num_problems; ++i) p.colsum[i] = a->prob[i].colsum;
   p.relu = a->relu;
   p.add_after_mask = a->add_after_mask;
   int os = 1, oy = 0, ox = 0;   // output scatter: (y*os + oy, x*os + ox)
@@ -589,6 +640,8 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
       OW = q.OWo;
     }
     if (OH <= 0 || OW <= 0) return set_error(-1, "b200_conv: empty problem");
+    d.OH = OH;
+    d.OW = OW;
     pick_tile(OH, OW, d.th_log2, d.tw_log2);
     const int th = 1 << d.th_log2, tw = 1 << d.tw_log2;
     d.tiles_h = (OH + th - 1) / th;

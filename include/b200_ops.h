@@ -29,8 +29,9 @@ void b200_add_launch_count(long long n); /* kernels run by a CUDA-graph replay (
  * -> 128B-swizzled smem ring -> tcgen05.mma (M=128, N<=256, K=16, bf16 in / fp32 acc in TMEM)
  * -> tcgen05.ld epilogue fusing: + shift[c] (bias or frozen-BN shift; the BN scale is folded
  * into the bf16 working weights), + add (residual / gradient accumulation), * (mask > 0)
- * (ReLU backward), ReLU, bf16 or fp32 store.  Persistent, warp-specialised (TMA / MMA / TMEM
- * alloc / 4 epilogue warps), double-buffered accumulators.  Up to 5 same-weight problems
+ * (ReLU backward), ReLU, bf16 store.  The add / mask operands arrive by TMA into smem chunk slots and the
+ * results leave by TMA store.  Persistent, warp-specialised (operand TMA / MMA / TMEM alloc + store /
+ * epilogue-operand TMA / 16 epilogue warps), double-buffered accumulators.  Up to 5 same-weight problems
  * (the FPN levels of a shared head) are scheduled in one launch.
  * Replaces: cuDNN fprop + bias-add + fused-BN + ReLU + add (G2-G4, G6, G8) and dgrad (G12). */
 #define B200_MAX_PROBLEMS 5
@@ -42,6 +43,8 @@ typedef struct {
   const void* mask; /* optional bf16, geometry of out */
   int N, H, W;      /* dims of `in` */
   int OHo, OWo;     /* spatial dims of `out` */
+  float* colsum;    /* optional fp32 [Nrows]: += sum over pixels of `out` (the bias gradient of the layer whose dY
+                       this output is).  Several problems may name the same vector. */
 } B200ConvProblem;
 
 typedef struct {

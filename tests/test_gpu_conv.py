@@ -156,6 +156,46 @@ def test_epilogue_in_place_residual():
     _close(g, ref)
 
 
+def test_dgrad_column_sums():
+    """The store warp's column sums (bias gradient of the layer whose dY this output is) equal the sum of the stored
+    bf16 tensor over pixels: grouped launch into one shared vector, stride-2 parity launches, several N tiles."""
+    shapes = [(2, 25, 42), (2, 13, 21), (2, 7, 11)]
+    wt = torch.randn(256, 256, 3, 3, device="cuda") * 0.02
+    _, wd = cv.pack_working(cv.pack_master(wt))
+    dys = [_mk(n, h, w, 256, seed=i) for i, (n, h, w) in enumerate(shapes)]
+    masks = [_mk(n, h, w, 256, seed=20 + i) for i, (n, h, w) in enumerate(shapes)]
+    outs = [torch.empty_like(d) for d in dys]
+    db = torch.full((256,), 3.0, device="cuda")
+    native.conv_raw(1, [(d, o, None, m, db) for d, o, m in zip(dys, outs, masks)], wd, 256, 256, 256, 256, 3, 3, 1, 1, 1)
+    want = 3.0 + sum(o.float().sum(dim=(0, 1, 2)) for o in outs)
+    assert torch.allclose(db, want, rtol=1e-4, atol=1e-3 * float(want.abs().max())), (db - want).abs().max()
+    # 1x1, 64 -> 1024 channels (four N tiles), residual + mask, partial tiles
+    n, h, w, cin, cout = 2, 19, 23, 1024, 64
+    wt = torch.randn(cout, cin, 1, 1, device="cuda") * 0.1
+    _, wd = cv.pack_working(cv.pack_master(wt))
+    dy = _mk(n, h, w, cout)
+    add, mask = _mk(n, h, w, cin, seed=3), _mk(n, h, w, cin, seed=4)
+    out = torch.empty(n, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    db = torch.zeros(cin, device="cuda")
+    native.conv_raw(1, [(dy, out, add, mask, db)], wd, cout, dy.shape[-1], cin, cin, 1, 1, 1, 0, 0)
+    want = out.float().sum(dim=(0, 1, 2))
+    assert torch.allclose(db, want, rtol=1e-4, atol=1e-3 * float(want.abs().max()))
+    # 3x3 stride 2 (four parity launches into one vector)
+    from batchai_retinanet_horovod_coco_b200.models.resnet import tf_same_pad
+    h, w, cin, cout = 25, 42, 256, 256
+    ph, pw = tf_same_pad(h, 3, 2), tf_same_pad(w, 3, 2)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda") * 0.02
+    _, wd = cv.pack_working(cv.pack_master(wt))
+    dy = _mk(1, 13, 21, cout)
+    out = torch.zeros(1, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    db = torch.zeros(cin, device="cuda")
+    for py in range(2):
+        for px in range(2):
+            native.conv_raw(1, [(dy, out, None, None, db)], wd, cout, cout, cin, cin, 3, 3, 2, ph[0], pw[0], par=(py, px))
+    want = out.float().sum(dim=(0, 1, 2))
+    assert torch.allclose(db, want, rtol=1e-4, atol=1e-3 * float(want.abs().max()))
+
+
 def test_dgrad_group_masks():
     shapes = [(2, 25, 42), (2, 13, 21), (2, 7, 11), (2, 4, 6), (2, 2, 3)]
     wt = torch.randn(256, 256, 3, 3, device="cuda") * 0.02

@@ -67,11 +67,15 @@ def test_engine_matches_autograd():
         gw, gbias = grads_n[name]
         cw = _cos(gw, mod.weight.grad)
         ratio = float(gw.norm() / (mod.weight.grad.norm() + 1e-30))
-        if cw < 0.98 or not (0.9 < ratio < 1.1):
+        # The oracle is fp32 end to end, the engine keeps bf16 activations and gradients through ~50 layers: measured
+        # cosines are 0.998-0.9999 (0.987 for conv1, whose gradient has crossed every layer and the max-pool's
+        # arg-max ties).  A wrong tap, a dropped K slice or a missing residual branch gives < 0.95.
+        lim = 0.98 if name == "conv1" else 0.996
+        if cw < lim or not (0.97 < ratio < 1.03):
             bad.append((name, "w", round(cw, 4), round(ratio, 3)))
         if gbias is not None:
             cb = _cos(gbias, mod.bias.grad)
-            if cb < 0.98:
+            if cb < 0.995:
                 bad.append((name, "b", round(cb, 4)))
     assert not bad, f"gradient mismatches: {bad[:20]} ({len(bad)} total)"
 
