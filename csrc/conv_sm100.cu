@@ -40,7 +40,7 @@ namespace b200 {
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kAStageBytes = kBM * kBK * 2;       // 16 KB
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 8;
 constexpr int kMaxSlots = 12;
 constexpr int kSlotBytes = kBM * 64 * 2;          // one [128 pixels][64 channels] bf16 chunk, 128 B rows, SWIZZLE_128B
 constexpr int kMaxTaps = 49;
@@ -137,13 +137,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   if (bar_base + kBarBytes - raw_base > static_cast<uint32_t>(p.smem_bytes)) __trap();   // layout does not fit
   // barriers (8 bytes each)
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 32u + 8u * s; };
-  auto tfull_bar = [&](int a) { return bar_base + 64u + 8u * a; };
-  auto tempty_bar = [&](int a) { return bar_base + 80u + 8u * a; };
-  auto ldfull_bar = [&](int s) { return bar_base + 96u + 8u * s; };     // operand chunk landed in slot s
-  auto free_bar = [&](int s) { return bar_base + 192u + 8u * s; };      // slot s may be overwritten
-  auto stfull_bar = [&](int s) { return bar_base + 288u + 8u * s; };    // result chunk complete in slot s
-  const uint32_t tmem_ptr_smem = bar_base + 384u;
+  auto empty_bar = [&](int s) { return bar_base + 64u + 8u * s; };
+  auto tfull_bar = [&](int a) { return bar_base + 128u + 8u * a; };
+  auto tempty_bar = [&](int a) { return bar_base + 144u + 8u * a; };
+  auto ldfull_bar = [&](int s) { return bar_base + 160u + 8u * s; };    // operand chunk landed in slot s
+  auto free_bar = [&](int s) { return bar_base + 256u + 8u * s; };      // slot s may be overwritten
+  auto stfull_bar = [&](int s) { return bar_base + 352u + 8u * s; };    // result chunk complete in slot s
+  const uint32_t tmem_ptr_smem = bar_base + 448u;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -191,8 +191,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 
   if (warp == 0) {
     // ------------------------------------------------------------------ operand producer
-    // The whole warp runs the loop; lane 0 arms the barrier and issues the activation box, lane 1 issues
-    // the weight box, so the two TMA issues of a stage overlap.
+    // The whole warp runs the loop (uniform control flow); one ELECTED lane arms the barrier and issues the two
+    // boxes.  elect.sync instead of `lane == 0`: ptxas then keeps the TMA / MMA operands in uniform registers
+    // instead of wrapping every instruction in a leader-election loop (92 -> ~30 SASS instructions per K step in
+    // the MMA issuer, which was the limiter of every layer with N <= 128: 665 cycles per step for 128 cycles of
+    // tensor work at N = 64).
     int stage = 0;
     uint32_t phase = 0;
     bool first_pass = true;
@@ -209,13 +212,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         for (int kc = 0; kc < p.num_kc; ++kc) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const bool load_b = !weights_resident || first_pass;
-          if (lane == 0) {
+          if (elect_one()) {
             mbar_expect_tx(full_bar(stage), kAStageBytes + (load_b ? b_bytes : 0u));
             tma_load_4d(a_smem + stage * kAStageBytes, amap, full_bar(stage), kc * kBK, x0 + tap.dw, y0 + tap.dh, n);
+            if (load_b)
+              tma_load_3d(b_smem + stage * p.b_stage_bytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
           }
           __syncwarp();
-          if (lane == 1 && load_b)
-            tma_load_3d(b_smem + stage * p.b_stage_bytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
@@ -241,7 +244,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       for (int kb = 0; kb < num_k; ++kb) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
-        if (lane == 0) {
+        if (elect_one()) {
           const uint64_t adesc = make_smem_desc(a_smem + stage * kAStageBytes, 16, 1024);
           const uint64_t bdesc = make_smem_desc(b_smem + stage * p.b_stage_bytes, 16, 1024);
 #pragma unroll
@@ -325,7 +328,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
               cs[c][1] += s1;
               __syncwarp();
             }
-            if (lane == 0) {
+            if (elect_one()) {
               if constexpr (kPPC == 2) {
                 int sb = cur.slot + 1;
                 if (sb >= nslots) sb -= nslots;
@@ -346,7 +349,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   } else if (warp == 3) {
     // ------------------------------------------------------------------ epilogue-operand loader (one thread)
     if constexpr (kLoads) {
-      if (lane == 0) {
+      if (elect_one()) {
         SlotCursor cur{0, 0u};
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
           int pi, n, y0, x0, n_tile;
@@ -705,13 +708,26 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   // ---- shared-memory split between the operand ring and the epilogue chunk slots.
   // Short K loops (the memory-bound 1x1 layers) need few ring stages -- the weights stay resident and one stage is one
   // whole tile -- and give the rest to chunk slots = bytes of residual / mask / result in flight per SM.
+  // The ring must cover the latency of a box that misses L2 (~1.5 us) with stage-times that are as short as
+  // 130 cycles when N is small, so it is as deep as the smem allows (up to 8 stages) once the chunk slots the
+  // epilogue needs are set aside: 2 for plain outputs, 4 / 6 when residual / residual + mask chunks are loaded.
   const int num_k = nt * p.num_kc;
   const int ppc = (has_add && has_mask) ? 2 : 1;
   p.b_stage_bytes = p.BN * kBK * 2;
-  int stages = num_k >= kMaxStages ? kMaxStages : (num_k < 2 ? 2 : num_k);
+  const int stage_bytes = kAStageBytes + p.b_stage_bytes;
   const int fixed = kShiftBytes + kBarBytes;
+  const int want_slots = (has_add || has_mask) ? 2 + 2 * ppc : 2;
+  int stages = (kSmemLimit - fixed - want_slots * kSlotBytes) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) stages = 2;
+  if (num_k <= 4) {
+    // short K loops keep their weights resident (stage count = a multiple of the loop length)
+    const int mult = num_k < 2 ? 2 : num_k;
+    stages = stages / mult * mult;
+    if (stages < mult) stages = mult;
+  }
   auto slots_for = [&](int st) {
-    int sl = (kSmemLimit - fixed - st * (kAStageBytes + p.b_stage_bytes)) / kSlotBytes;
+    int sl = (kSmemLimit - fixed - st * stage_bytes) / kSlotBytes;
     if (sl > kMaxSlots) sl = kMaxSlots;
     if (ppc == 2) sl &= ~1;
     return sl;
@@ -721,7 +737,7 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   p.slots = slots_for(stages);
   if (p.slots < 2 * ppc) return set_error(-1, "b200_conv: shared-memory layout does not fit");
   {
-    const int need = stages * (kAStageBytes + p.b_stage_bytes) + p.slots * kSlotBytes + fixed;
+    const int need = stages * stage_bytes + p.slots * kSlotBytes + fixed;
     p.smem_bytes = need + 1024 <= kSmemLimit ? need + 1024 : kSmemLimit;   // the base is 1024-aligned in practice
   }
 

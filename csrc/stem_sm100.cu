@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_conv_kernel(const StemPa
       mbar_wait(tempty_bar(acc), acc_phase ^ 1);
       mbar_wait(full_bar(stage), phase);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
 #pragma unroll
         for (int kb = 0; kb < kStemKB; ++kb) {
           const uint64_t adesc = make_smem_desc(a_smem + stage * kStemABytes + kb * 16384, 16, 1024);
@@ -366,7 +366,7 @@ __global__ void __launch_bounds__(kSwThreads, 1) stem_wgrad_kernel(const __grid_
       // keep the dY loads kSwStages ahead
       while (issued < my_tiles && issued < it + kSwStages) {
         mbar_wait(empty_bar(stage_p), phase_p ^ 1);
-        if (lane == 0) {
+        if (elect_one()) {
           int n, y0, x0;
           decode(tile_p, n, y0, x0);
           mbar_expect_tx(full_bar(stage_p), 8192);
@@ -382,7 +382,7 @@ __global__ void __launch_bounds__(kSwThreads, 1) stem_wgrad_kernel(const __grid_
       }
       mbar_wait(full_bar(stage_c), phase_c);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint64_t adesc = make_smem_desc(a_smem + stage_c * kSwAStage, 8192, 1024);
         const uint64_t bdesc = make_smem_desc(b_smem + stage_c * kSwBStage, 8192, 1024);
 #pragma unroll

@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
       for (int pt = pt_begin; pt < pt_end; ++pt) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
-        if (lane == 0) {
+        if (elect_one()) {   // elect.sync, not lane == 0: keeps the MMA operands in uniform registers (no election loops)
           // MN-major: LBO = distance between 64-channel chunks, SBO = 8 pixel rows = 1024 B
           const uint64_t bdesc = make_smem_desc(b_smem + stage * kWBStage, kChunkBytes, 1024);
           for (int mt = 0; mt < mt_valid; ++mt) {
