@@ -6,9 +6,11 @@
 // (dh, dw) shift of the TMA box and the conv halo / padding is TMA's out-of-bounds zero fill),
 // N = output channels (BN <= 256 per tile), K = taps x input channels (64 per pipeline stage).
 //
-// Warp roles (640 threads, 1 CTA per SM, persistent over tiles):
-//   warp 0   operand producer (lane 0: activation box [64ch, tw, th, 1], lane 1: weight box [64ch, BN rows, 1 tap])
-//   warp 1   MMA issuer (one lane): 4 x tcgen05.mma (K=16) per stage, commit -> empty barrier
+// Warp roles (672 threads, 1 CTA per SM, persistent over tiles):
+//   warp 0   activation producer (one elected thread): one TMA box per GROUP of the K loop (see ConvParams::mode)
+//   warp 20  weight producer (one elected thread): box [64ch, BN rows, 1 tap] per sub-step, own ring; idle after the
+//            first tile when all weight tiles of the layer fit its ring (they stay resident)
+//   warp 1   MMA issuer: per group one wait, per sub-step 4 x tcgen05.mma (K=16) under elect.sync, commits
 //   warp 2   TMEM allocator (512 columns = two 256-column accumulators), then the STORE issuer: one TMA store per
 //            finished 128-pixel x 64-channel chunk, then releases the chunk's smem slot.  Optionally sums the
 //            chunk's columns first (the bias gradient of the layer that consumes this output as its dY)
@@ -40,16 +42,18 @@ namespace b200 {
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kAStageBytes = kBM * kBK * 2;       // 16 KB
-constexpr int kMaxStages = 8;
+constexpr int kMaxAStages = 6;
+constexpr int kMaxBStages = 12;
 constexpr int kMaxSlots = 12;
 constexpr int kSlotBytes = kBM * 64 * 2;          // one [128 pixels][64 channels] bf16 chunk, 128 B rows, SWIZZLE_128B
 constexpr int kMaxTaps = 49;
 constexpr int kMaxMaps = 8;
 constexpr int kTmemCols = 512;
 constexpr int kEpiWarps = 16;                     // 4 TMEM lane quarters x 2 column halves x 2 chunk groups
-constexpr int kConvThreads = 128 + 32 * kEpiWarps;
+constexpr int kConvThreads = 128 + 32 * kEpiWarps + 32;    // + the weight producer (warp 20)
+constexpr int kWeightWarp = kConvThreads / 32 - 1;
 constexpr int kShiftBytes = kEpiWarps * 128;      // per epilogue warp: the 32 shift values of its current chunk half
-constexpr int kBarBytes = 512;
+constexpr int kBarBytes = 640;
 constexpr int kSmemLimit = 232448;                // 227 KB
 
 struct Tap {
@@ -59,6 +63,8 @@ struct Tap {
 
 struct DevProblem {
   int OH, OW;           // GEMM pixel grid
+  int a_bytes;          // bytes of one activation box
+  int sub_stride;       // byte distance between the sub-tiles of a box
   int tiles_h, tiles_w; // spatial tiles per image
   int tile_begin;       // first m-tile of this problem
   int th_log2, tw_log2;
@@ -79,7 +85,16 @@ struct ConvParams {
   int Nrows, BN;
   int num_taps, num_kc;
   int relu, add_after_mask;
-  int stages, slots, b_stage_bytes, smem_bytes;
+  // K loop = activation GROUPS (one TMA box each) x up to gsz SUB-STEPS (one weight tile, 4 MMAs each):
+  //   mode 0 plain: box [64ch, tw, th, 1], gsz = 1, one group per (tap, k chunk);
+  //   mode 1 halo (3x3, stride 1): box [64ch, tw, th + 2, 1] serves the three taps dh = -1, 0, +1 of one filter
+  //          column as row-offset views (1024-byte aligned), so activations cross L2 -> smem 3 (th+2)/th times, not 9;
+  //   mode 2 kc (K a multiple of 64, >= 2 chunks): 5-D box [64ch, tw, th, 1, gsz chunks] = gsz k chunks per issue.
+  // Fewer, larger boxes matter because one thread issues them: ~600 cycles of instruction latency per issue bounded
+  // every layer with N <= 128 (ncu: producer and MMA warps busy, tensor pipe 20 % active).
+  int mode, gsz, tap_groups, kgroups;
+  int a_stages, b_stages, slots, a_stage_bytes, b_stage_bytes, smem_bytes;
+  int widx3[3][3];      // halo mode: [dw + 1][dh + 1] -> weight tap index
 };
 
 __device__ __forceinline__ void decode_tile(const ConvParams& p, int tile, int& pi, int& n, int& y0, int& x0,
@@ -126,30 +141,39 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   constexpr bool kLoads = kAdd || kMask;
   constexpr int kPPC = (kAdd && kMask) ? 2 : 1;     // slot positions per chunk
-  const int stages = p.stages, nslots = p.slots;
+  const int a_stages = p.a_stages, b_stages = p.b_stages, nslots = p.slots;
   const uint32_t raw_base = smem_u32(smem_raw);
   const uint32_t smem_base = (raw_base + 1023u) & ~1023u;
   const uint32_t a_smem = smem_base;
-  const uint32_t b_smem = a_smem + stages * kAStageBytes;
-  const uint32_t slot_base = b_smem + stages * p.b_stage_bytes;
+  const uint32_t b_smem = a_smem + a_stages * p.a_stage_bytes;
+  const uint32_t slot_base = b_smem + b_stages * p.b_stage_bytes;
   const uint32_t shift_base = slot_base + nslots * kSlotBytes;
   const uint32_t bar_base = shift_base + kShiftBytes;
   if (bar_base + kBarBytes - raw_base > static_cast<uint32_t>(p.smem_bytes)) __trap();   // layout does not fit
   // barriers (8 bytes each)
-  auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 64u + 8u * s; };
-  auto tfull_bar = [&](int a) { return bar_base + 128u + 8u * a; };
-  auto tempty_bar = [&](int a) { return bar_base + 144u + 8u * a; };
-  auto ldfull_bar = [&](int s) { return bar_base + 160u + 8u * s; };    // operand chunk landed in slot s
-  auto free_bar = [&](int s) { return bar_base + 256u + 8u * s; };      // slot s may be overwritten
-  auto stfull_bar = [&](int s) { return bar_base + 352u + 8u * s; };    // result chunk complete in slot s
-  const uint32_t tmem_ptr_smem = bar_base + 448u;
+  auto afull_bar = [&](int s) { return bar_base + 8u * s; };
+  auto aempty_bar = [&](int s) { return bar_base + 48u + 8u * s; };
+  auto bfull_bar = [&](int s) { return bar_base + 96u + 8u * s; };
+  auto bempty_bar = [&](int s) { return bar_base + 192u + 8u * s; };
+  auto tfull_bar = [&](int a) { return bar_base + 288u + 8u * a; };
+  auto tempty_bar = [&](int a) { return bar_base + 304u + 8u * a; };
+  auto ldfull_bar = [&](int s) { return bar_base + 320u + 8u * s; };    // operand chunk landed in slot s
+  auto free_bar = [&](int s) { return bar_base + 416u + 8u * s; };      // slot s may be overwritten
+  auto stfull_bar = [&](int s) { return bar_base + 512u + 8u * s; };    // result chunk complete in slot s
+  const uint32_t tmem_ptr_smem = bar_base + 608u;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = p.num_m_tiles * p.num_n_tiles;
-  const int num_k = p.num_taps * p.num_kc;
+  const int gsz = p.gsz, kgroups = p.kgroups;
+  const int num_groups = p.tap_groups * kgroups;          // activation boxes per tile
+  const int num_substeps = p.num_taps * p.num_kc;         // weight tiles per tile
   const uint32_t b_bytes = static_cast<uint32_t>(p.BN) * kBK * 2;
+  // Weights stay resident: when every weight tile of the K loop has its own ring stage and there is a single N
+  // tile, stage s always holds the same tile, so it is fetched once (first pass) and never released.
+  const bool weights_resident = (p.num_n_tiles == 1) && (b_stages == num_substeps);
+  // sub-steps of k group kg (the last group of a tap may be short in kc mode)
+  auto nsub = [&](int kg) { return p.mode == 2 ? min(gsz, p.num_kc - kg * gsz) : gsz; };
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < kMaxMaps; ++i) tma_prefetch_desc(&p.in_maps[i]);
@@ -161,9 +185,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kMaxStages; ++s) {
-      mbar_init(full_bar(s), 1);
-      mbar_init(empty_bar(s), 1);
+    for (int s = 0; s < kMaxAStages; ++s) {
+      mbar_init(afull_bar(s), 1);
+      mbar_init(aempty_bar(s), 1);
+    }
+    for (int s = 0; s < kMaxBStages; ++s) {
+      mbar_init(bfull_bar(s), 1);
+      mbar_init(bempty_bar(s), 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
@@ -190,79 +218,152 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   pdl_wait();
 
   if (warp == 0) {
-    // ------------------------------------------------------------------ operand producer
-    // The whole warp runs the loop (uniform control flow); one ELECTED lane arms the barrier and issues the two
-    // boxes.  elect.sync instead of `lane == 0`: ptxas then keeps the TMA / MMA operands in uniform registers
-    // instead of wrapping every instruction in a leader-election loop (92 -> ~30 SASS instructions per K step in
-    // the MMA issuer, which was the limiter of every layer with N <= 128: 665 cycles per step for 128 cycles of
-    // tensor work at N = 64).
-    int stage = 0;
-    uint32_t phase = 0;
-    bool first_pass = true;
-    // Weights stay resident: when the whole K loop fits the ring (num_k divides the stage count) and there is a
-    // single N tile, stage s always holds the same weight tile, so it is fetched once.
-    const bool weights_resident = (p.num_n_tiles == 1) && (stages % num_k == 0);
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      int pi, n, y0, x0, n_tile;
-      decode_tile(p, tile, pi, n, y0, x0, n_tile);
-      const int map_base = p.prob[pi].map_base;
-      for (int t = 0; t < p.num_taps; ++t) {
-        const Tap tap = p.taps[t];
-        const void* amap = &p.in_maps[map_base + tap.map];
-        for (int kc = 0; kc < p.num_kc; ++kc) {
-          mbar_wait(empty_bar(stage), phase ^ 1);
-          const bool load_b = !weights_resident || first_pass;
-          if (elect_one()) {
-            mbar_expect_tx(full_bar(stage), kAStageBytes + (load_b ? b_bytes : 0u));
-            tma_load_4d(a_smem + stage * kAStageBytes, amap, full_bar(stage), kc * kBK, x0 + tap.dw, y0 + tap.dh, n);
-            if (load_b)
-              tma_load_3d(b_smem + stage * p.b_stage_bytes, &p.w_map, full_bar(stage), kc * kBK, n_tile * p.BN, tap.widx);
+    // ------------------------------------------------------------------ activation producer (one elected thread)
+    // elect.sync, not `lane == 0`: ptxas then knows the region is single-lane and keeps the TMA operands in uniform
+    // registers instead of wrapping every instruction in a leader-election loop.
+    if (elect_one()) {
+      int sa = 0;
+      uint32_t pa = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int pi, n, y0, x0, n_tile;
+        decode_tile(p, tile, pi, n, y0, x0, n_tile);
+        const DevProblem& q = p.prob[pi];
+        const uint32_t a_bytes = static_cast<uint32_t>(q.a_bytes);
+        for (int t = 0; t < p.tap_groups; ++t) {
+          int x = x0, y = y0, map = q.map_base;
+          if (p.mode == 1) {            // filter column t - 1, rows y0 - 1 .. y0 + th
+            x += t - 1;
+            y -= 1;
+          } else {
+            const Tap tap = p.taps[t];
+            x += tap.dw;
+            y += tap.dh;
+            map += tap.map;
           }
-          __syncwarp();
-          if (++stage == stages) {
-            stage = 0;
-            phase ^= 1;
-            first_pass = false;
+          const void* amap = &p.in_maps[map];
+          for (int kg = 0; kg < kgroups; ++kg) {
+            mbar_wait(aempty_bar(sa), pa ^ 1);
+            mbar_expect_tx(afull_bar(sa), a_bytes);
+            const uint32_t dst = a_smem + sa * p.a_stage_bytes;
+            if (p.mode == 2) tma_load_5d(dst, amap, afull_bar(sa), 0, x, y, n, kg * gsz);
+            else tma_load_4d(dst, amap, afull_bar(sa), kg * kBK, x, y, n);
+            if (++sa == a_stages) {
+              sa = 0;
+              pa ^= 1;
+            }
           }
         }
       }
     }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    int stage = 0;
-    uint32_t phase = 0;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      // the last N tile may be narrower: do not multiply zero-filled weight rows
-      const int n_tile = tile / p.num_m_tiles;
-      const int cols = min(p.Nrows - n_tile * p.BN, p.BN);
-      const uint32_t idesc = make_idesc_bf16(kBM, max(16, (cols + 15) & ~15), 0, 0);
-      mbar_wait(tempty_bar(acc), acc_phase ^ 1);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * 256;
-      for (int kb = 0; kb < num_k; ++kb) {
-        mbar_wait(full_bar(stage), phase);
-        tc_fence_after();
-        if (elect_one()) {
-          const uint64_t adesc = make_smem_desc(a_smem + stage * kAStageBytes, 16, 1024);
-          const uint64_t bdesc = make_smem_desc(b_smem + stage * p.b_stage_bytes, 16, 1024);
-#pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the 128B swizzle row: +2 in (addr >> 4) units
-            umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+  } else if (warp == kWeightWarp) {
+    // ------------------------------------------------------------------ weight producer (one elected thread)
+    if (elect_one()) {
+      int sb = 0;
+      uint32_t pb = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int row0 = (tile / p.num_m_tiles) * p.BN;
+        for (int t = 0; t < p.tap_groups; ++t) {
+          for (int kg = 0; kg < kgroups; ++kg) {
+            const int ns = nsub(kg);
+            for (int j = 0; j < ns; ++j) {
+              const int widx = p.mode == 1 ? p.widx3[t][j] : p.taps[t].widx;
+              const int kc = p.mode == 2 ? kg * gsz + j : kg;
+              mbar_wait(bempty_bar(sb), pb ^ 1);
+              mbar_expect_tx(bfull_bar(sb), b_bytes);
+              tma_load_3d(b_smem + sb * p.b_stage_bytes, &p.w_map, bfull_bar(sb), kc * kBK, row0, widx);
+              if (++sb == b_stages) {
+                sb = 0;
+                pb ^= 1;
+              }
+            }
           }
-          umma_commit(empty_bar(stage));
-          if (kb == num_k - 1) umma_commit(tfull_bar(acc));
         }
-        __syncwarp();
-        if (++stage == stages) {
-          stage = 0;
-          phase ^= 1;
-        }
+        if (weights_resident) break;      // one pass filled every stage for good
       }
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1;
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (one elected thread)
+    // This thread's instruction latency IS the kernel's speed for every layer with N <= 128 (a sub-step is 128 cycles
+    // of tensor work at N = 64; ncu showed ~600 cycles of address arithmetic, elections and reconvergence around
+    // it).  So: one elect.sync for the whole loop (operands stay in uniform registers, no per-step ELECT / BSSY /
+    // BSYNC), descriptors advanced incrementally in 16-byte units (the 14-bit address field never carries: smem
+    // addresses are < 256 KB), no divisions in the K loop.
+    if (elect_one()) {
+      const uint64_t desc_hi = make_smem_desc(0, 16, 1024);        // everything but the start address
+      const uint32_t a_first = a_smem >> 4, b_first = b_smem >> 4;
+      const uint32_t a_step = static_cast<uint32_t>(p.a_stage_bytes) >> 4, b_step = static_cast<uint32_t>(p.b_stage_bytes) >> 4;
+      uint32_t a_cur = a_first, b_cur = b_first;
+      uint32_t afull = afull_bar(0), aempty = aempty_bar(0), bfull = bfull_bar(0), bempty = bempty_bar(0);
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0;
+      bool b_wait = true;                 // false once resident weights have all landed
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      const bool one_problem = p.num_problems == 1;
+      uint32_t sub_step = static_cast<uint32_t>(p.prob[0].sub_stride) >> 4;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n_tile = tile / p.num_m_tiles;
+        if (!one_problem) {               // halo tiles differ per pyramid level
+          int pi, n, y0, x0, nt2;
+          decode_tile(p, tile, pi, n, y0, x0, nt2);
+          sub_step = static_cast<uint32_t>(p.prob[pi].sub_stride) >> 4;
+        }
+        // the last N tile may be narrower: do not multiply zero-filled weight rows
+        const int cols = min(p.Nrows - n_tile * p.BN, p.BN);
+        const uint32_t idesc = make_idesc_bf16(kBM, max(16, (cols + 15) & ~15), 0, 0);
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * 256;
+        uint32_t accumulate = 0;
+        int kg = 0;
+        for (int g = 0; g < num_groups; ++g) {
+          const int ns = p.mode == 2 ? min(gsz, p.num_kc - kg * gsz) : gsz;
+          if (++kg == kgroups) kg = 0;
+          mbar_wait(afull, pa);
+          tc_fence_after();
+          uint32_t a_sub = a_cur;
+          for (int j = 0; j < ns; ++j) {
+            if (b_wait) {
+              mbar_wait(bfull, pb);
+              tc_fence_after();
+            }
+            const uint64_t adesc = desc_hi | a_sub, bdesc = desc_hi | b_cur;
+#pragma unroll
+            for (int k = 0; k < kBK / 16; ++k) {
+              // advance 16 bf16 = 32 bytes along K inside the 128B swizzle row: +2 in (addr >> 4) units
+              umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, accumulate | k);
+            }
+            if (!weights_resident) umma_commit(bempty);
+            accumulate = 1;
+            a_sub += sub_step;
+            b_cur += b_step;
+            bfull += 8;
+            bempty += 8;
+            if (++sb == b_stages) {
+              sb = 0;
+              pb ^= 1;
+              b_cur = b_first;
+              bfull = bfull_bar(0);
+              bempty = bempty_bar(0);
+              if (weights_resident) b_wait = false;
+            }
+          }
+          umma_commit(aempty);
+          if (g == num_groups - 1) umma_commit(tfull_bar(acc));
+          a_cur += a_step;
+          afull += 8;
+          aempty += 8;
+          if (++sa == a_stages) {
+            sa = 0;
+            pa ^= 1;
+            a_cur = a_first;
+            afull = afull_bar(0);
+            aempty = aempty_bar(0);
+          }
+        }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
     }
   } else if (warp == 2) {
     // ------------------------------------------------------------------ store issuer (one thread)
@@ -373,7 +474,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         }
       }
     }
-  } else {
+  } else if (warp < 4 + kEpiWarps) {
     // ------------------------------------------------------------------ epilogue math
     // Warp (quarter q, half hh, group gi): TMEM lanes 32q..32q+31 (the rows a warp may read are fixed by
     // warp_id % 4), columns 32hh..32hh+31 of a 64-column chunk, chunks with (running chunk index) % 2 == gi.
@@ -530,10 +631,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 static int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
 static int posmod(int a, int b) { return ((a % b) + b) % b; }
 
-static void pick_tile(int OH, int OW, int& th_log2, int& tw_log2) {
-  // 128 pixels as (128/tw) x tw; minimise padded tiles, prefer wide tiles on ties.
+static void pick_tile(int OH, int OW, int& th_log2, int& tw_log2, bool halo) {
+  // 128 pixels as (128/tw) x tw; minimise padded tiles, prefer wide tiles on ties.  Halo mode loads th + 2 rows per
+  // box: only 8 x 16 and 16 x 8 tiles keep the box small (<= 20 KB) and every row offset 1024-byte aligned.
   long long best = -1;
-  for (int tl = 7; tl >= 0; --tl) {
+  for (int tl = halo ? 4 : 7; tl >= (halo ? 3 : 0); --tl) {
     const int tw = 1 << tl, th = 128 >> tl;
     const long long tiles = static_cast<long long>((OH + th - 1) / th) * ((OW + tw - 1) / tw);
     if (best < 0 || tiles < best) {
@@ -626,6 +728,80 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   }
   p.num_taps = nt;
   if (nt == 0) return set_error(-6, "b200_conv: empty tap set (caller should zero-fill this parity class)");
+  // ---- K-loop mode (see ConvParams)
+  static int mode_env = -1;
+  if (mode_env < 0) {
+    const char* e = getenv("B200_CONV_GROUPS");      // 0: plain boxes only (A/B arm for profiles)
+    mode_env = (e && e[0] == '0') ? 0 : 1;
+  }
+  p.mode = 0;
+  p.gsz = 1;
+  if (mode_env && a->KH == 3 && a->KW == 3 && s == 1 && nt == 9) {
+    p.mode = 1;
+    for (int t = 0; t < 9; ++t) {
+      const Tap& tp = p.taps[t];
+      if (tp.dh < -1 || tp.dh > 1 || tp.dw < -1 || tp.dw > 1 || tp.map != 0) p.mode = 0;
+    }
+    if (p.mode == 1) {
+      p.gsz = 3;
+      for (int t = 0; t < 9; ++t) p.widx3[p.taps[t].dw + 1][p.taps[t].dh + 1] = p.taps[t].widx;
+    }
+  }
+  if (mode_env && p.mode == 0 && (a->K % kBK) == 0 && p.num_kc >= 2) {
+    p.mode = 2;
+    p.gsz = p.num_kc < 4 ? p.num_kc : 4;
+  }
+
+  // ---- shared-memory split: activation ring | weight ring | epilogue chunk slots.
+  // The weight ring holds every weight tile of the layer when they fit in 96 KB and there is one N tile (then they
+  // are fetched once); otherwise 4 stages.  The chunk slots the epilogue needs come next (2 for plain outputs, 4 / 6
+  // when residual / residual + mask chunks are loaded), and the activation ring gets the rest: it must cover the
+  // ~1.5 us of a box that misses L2 with stage times as short as 130 cycles when N is small.
+  const int ppc = (has_add && has_mask) ? 2 : 1;
+  const int num_substeps = nt * p.num_kc;
+  p.b_stage_bytes = p.BN * kBK * 2;
+  const int fixed = kShiftBytes + kBarBytes;
+  const int want_slots = (has_add || has_mask) ? 2 + 2 * ppc : 2;
+  int b_st = 4;
+  const bool resident = p.num_n_tiles == 1 && num_substeps <= kMaxBStages && num_substeps * p.b_stage_bytes <= 98304;
+  if (resident) b_st = num_substeps;
+  // kc boxes pay off where the step time is short (small layers, resident weights); with N = 256 and streamed
+  // weights, 4 fine-grained activation stages hide the TMA latency better than 2 coarse ones (measured)
+  if (p.mode == 2 && !resident) {
+    p.mode = 0;
+    p.gsz = 1;
+  }
+  int a_st = 0;
+  for (;;) {
+    p.a_stage_bytes = p.mode == 1 ? 20480 : p.gsz * kAStageBytes;
+    const int room = kSmemLimit - fixed - b_st * p.b_stage_bytes - want_slots * kSlotBytes;
+    a_st = room / p.a_stage_bytes;
+    if (a_st > kMaxAStages) a_st = kMaxAStages;
+    if (a_st >= (p.mode == 2 ? 3 : 2)) break;
+    if (p.mode == 2) {                          // smaller activation boxes first
+      p.gsz = p.gsz > 2 ? 2 : 1;
+      if (p.gsz == 1) p.mode = 0;
+      continue;
+    }
+    if (b_st > 2) {                             // then a shallower weight ring (gives up residency)
+      b_st = b_st > 4 ? 4 : b_st - 1;
+      continue;
+    }
+    return set_error(-1, "b200_conv: shared-memory layout does not fit");
+  }
+  p.a_stages = a_st;
+  p.b_stages = b_st;
+  {
+    int sl = (kSmemLimit - fixed - a_st * p.a_stage_bytes - b_st * p.b_stage_bytes) / kSlotBytes;
+    if (sl > kMaxSlots) sl = kMaxSlots;
+    if (ppc == 2) sl &= ~1;
+    p.slots = sl;
+    if (sl < 2 * ppc) return set_error(-1, "b200_conv: shared-memory layout does not fit (slots)");
+    const int need = a_st * p.a_stage_bytes + b_st * p.b_stage_bytes + sl * kSlotBytes + fixed;
+    p.smem_bytes = need + 1024 <= kSmemLimit ? need + 1024 : kSmemLimit;   // the base is 1024-aligned in practice
+  }
+  p.tap_groups = p.mode == 1 ? 3 : nt;
+  p.kgroups = p.mode == 2 ? (p.num_kc + p.gsz - 1) / p.gsz : p.num_kc;
 
   // ---- problems + tensor maps
   int tile_begin = 0;
@@ -645,14 +821,17 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
     if (OH <= 0 || OW <= 0) return set_error(-1, "b200_conv: empty problem");
     d.OH = OH;
     d.OW = OW;
-    pick_tile(OH, OW, d.th_log2, d.tw_log2);
+    pick_tile(OH, OW, d.th_log2, d.tw_log2, p.mode == 1);
     const int th = 1 << d.th_log2, tw = 1 << d.tw_log2;
+    d.a_bytes = p.mode == 1 ? (th + 2) * tw * kBK * 2 : p.gsz * kAStageBytes;
+    d.sub_stride = p.mode == 1 ? tw * kBK * 2 : kAStageBytes;
     d.tiles_h = (OH + th - 1) / th;
     d.tiles_w = (OW + tw - 1) / tw;
     d.tile_begin = tile_begin;
     tile_begin += q.N * d.tiles_h * d.tiles_w;
     d.map_base = map_count;
-    const unsigned int box[4] = {static_cast<unsigned>(kBK), static_cast<unsigned>(tw), static_cast<unsigned>(th), 1u};
+    const unsigned int box[5] = {static_cast<unsigned>(kBK), static_cast<unsigned>(tw),
+                                 static_cast<unsigned>(p.mode == 1 ? th + 2 : th), 1u, static_cast<unsigned>(p.gsz)};
     const int nmaps = (a->mode == 0 && s == 2) ? 4 : 1;
     if (map_count + nmaps > kMaxMaps) return set_error(-1, "b200_conv: too many tensor maps");
     for (int mi = 0; mi < nmaps; ++mi) {
@@ -661,12 +840,16 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
       const long long Wd = (q.W - px + step - 1) / step;
       const long long Hd = (q.H - py + step - 1) / step;
       const __nv_bfloat16* base = static_cast<const __nv_bfloat16*>(q.in) + (static_cast<long long>(py) * q.W + px) * a->ldi;
-      unsigned long long dims[4] = {static_cast<unsigned long long>(a->K), static_cast<unsigned long long>(Wd > 0 ? Wd : 1),
-                                    static_cast<unsigned long long>(Hd > 0 ? Hd : 1), static_cast<unsigned long long>(q.N)};
-      unsigned long long strides[3] = {static_cast<unsigned long long>(step) * a->ldi * 2ull,
+      // kc mode: the channel axis is split [k chunk][64] so that one 5-D box carries gsz chunks
+      const bool kcm = p.mode == 2;
+      unsigned long long dims[5] = {static_cast<unsigned long long>(kcm ? kBK : a->K),
+                                    static_cast<unsigned long long>(Wd > 0 ? Wd : 1),
+                                    static_cast<unsigned long long>(Hd > 0 ? Hd : 1), static_cast<unsigned long long>(q.N),
+                                    static_cast<unsigned long long>(p.num_kc)};
+      unsigned long long strides[4] = {static_cast<unsigned long long>(step) * a->ldi * 2ull,
                                        static_cast<unsigned long long>(step) * q.W * a->ldi * 2ull,
-                                       static_cast<unsigned long long>(q.H) * q.W * a->ldi * 2ull};
-      int rc = make_tmap_bf16(&p.in_maps[map_count + mi], base, 4, dims, strides, box);
+                                       static_cast<unsigned long long>(q.H) * q.W * a->ldi * 2ull, kBK * 2ull};
+      int rc = make_tmap_bf16(&p.in_maps[map_count + mi], base, kcm ? 5 : 4, dims, strides, box);
       if (rc) return rc;
     }
     map_count += nmaps;
@@ -708,39 +891,6 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   // ---- shared-memory split between the operand ring and the epilogue chunk slots.
   // Short K loops (the memory-bound 1x1 layers) need few ring stages -- the weights stay resident and one stage is one
   // whole tile -- and give the rest to chunk slots = bytes of residual / mask / result in flight per SM.
-  // The ring must cover the latency of a box that misses L2 (~1.5 us) with stage-times that are as short as
-  // 130 cycles when N is small, so it is as deep as the smem allows (up to 8 stages) once the chunk slots the
-  // epilogue needs are set aside: 2 for plain outputs, 4 / 6 when residual / residual + mask chunks are loaded.
-  const int num_k = nt * p.num_kc;
-  const int ppc = (has_add && has_mask) ? 2 : 1;
-  p.b_stage_bytes = p.BN * kBK * 2;
-  const int stage_bytes = kAStageBytes + p.b_stage_bytes;
-  const int fixed = kShiftBytes + kBarBytes;
-  const int want_slots = (has_add || has_mask) ? 2 + 2 * ppc : 2;
-  int stages = (kSmemLimit - fixed - want_slots * kSlotBytes) / stage_bytes;
-  if (stages > kMaxStages) stages = kMaxStages;
-  if (stages < 2) stages = 2;
-  if (num_k <= 4) {
-    // short K loops keep their weights resident (stage count = a multiple of the loop length)
-    const int mult = num_k < 2 ? 2 : num_k;
-    stages = stages / mult * mult;
-    if (stages < mult) stages = mult;
-  }
-  auto slots_for = [&](int st) {
-    int sl = (kSmemLimit - fixed - st * stage_bytes) / kSlotBytes;
-    if (sl > kMaxSlots) sl = kMaxSlots;
-    if (ppc == 2) sl &= ~1;
-    return sl;
-  };
-  while (stages > 2 && slots_for(stages) < 2 * ppc) --stages;
-  p.stages = stages;
-  p.slots = slots_for(stages);
-  if (p.slots < 2 * ppc) return set_error(-1, "b200_conv: shared-memory layout does not fit");
-  {
-    const int need = stages * stage_bytes + p.slots * kSlotBytes + fixed;
-    p.smem_bytes = need + 1024 <= kSmemLimit ? need + 1024 : kSmemLimit;   // the base is 1024-aligned in practice
-  }
-
   const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles;
   const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
   if (has_add && has_mask) return launch_variant<true, true>(p, grid, stream);
