@@ -199,6 +199,10 @@ class NativeTrainer:
                 off = _align4(off + c.cout)
         off = self._alloc_extra(off, True)
         self.n_train = off
+        # [0, cut) of G is final once the layer that ends there has run its weight gradient (parameters are laid
+        # out in backward-completion order): where the overlapped allreduce may start sending
+        self._cut_after = {c.name: (c.b_off + c.cout if c.has_bias else c.w_off + c.taps * c.cout * c.cin)
+                           for c in self.convs if c.trainable}
         for c in self.convs:
             if c.trainable:
                 continue
@@ -247,6 +251,8 @@ class NativeTrainer:
         self.lr_dev = torch.zeros(1, device=dev)          # bias-corrected Adam step size of the current step
         self.loss_out = torch.zeros(3, device=dev)        # [loss, regression_loss, classification_loss]
         self.loss_host = torch.zeros(3).pin_memory()      # the same triple, copied out right after the loss kernels
+        self._comm_stream = torch.cuda.Stream(device=dev)  # gradient scatter, beside the backward pass
+        self._pushed = 0                                  # elements of G already scattered in this step
         self._ev_front = torch.cuda.Event()               # forward + losses of the latest step are done
         self._ev_h2d = torch.cuda.Event()
         self._copy_stream = torch.cuda.Stream(device=dev)
@@ -500,8 +506,32 @@ class NativeTrainer:
             native.smooth_l1(p["reg_o"][l], p["dreg_o"][l], p["state"], p["reg_t_tgt"], A, p["a_off"][l], self.npos,
                              self.scal[2:3])
 
+    # ------------------------------------------------------------------ overlapped gradient scatter
+    def _overlap(self) -> bool:
+        return self.comm is not None and self.comm.world > 1 and self.comm.can_stage()
+
+    def _push_ready(self, upto: int):
+        """G[:upto] is final: scatter the new part to its owner ranks on the side stream (raw, un-clipped: the
+        clip factor of reference train.py:103-104 is applied by the owners once every rank knows its norm)."""
+        if not self._overlap():
+            return
+        upto = min(upto, self.n_train) // 4 * 4
+        if upto <= self._pushed:
+            return
+        main = torch.cuda.current_stream(self.device)
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self._comm_stream.wait_event(ev)
+        self.comm.scatter(self.n_train, self._pushed, upto, stream=self._comm_stream)
+        self._pushed = upto
+
+    def _push_after(self, conv):
+        if conv.trainable:
+            self._push_ready(self._cut_after[conv.name])
+
     # ------------------------------------------------------------------ backward
     def _backward(self, p):
+        self._pushed = 0
         fp, f = p["fpn"], self.fpn
         feats = fp["P"]
         dP = p["dP"]
@@ -525,6 +555,7 @@ class NativeTrainer:
                 pbias[3] = None        # P6's dY also gets P7's gradient below
             self._dgrad_group(tower[0], cur, dP, adds=None if first else dP, colsums=pbias)
             first = False
+        self._push_after(self.reg_tower[0])
         self._mark("bwd_heads")
         dP3, dP4, dP5, dP6, dP7 = dP
         df = p["dfpn"]
@@ -548,6 +579,7 @@ class NativeTrainer:
         self._dgrad(f["P5"], dP5, df["c5r"])
         native.upsample_bwd_add(df["m4"], df["c5r"])
         self._wgrad(f["C5_reduced"], [c5], [df["c5r"]])
+        self._push_after(f["C5_reduced"])
         self._mark("bwd_fpn")
         if not self.freeze_backbone:
             self._backward_backbone(p)
@@ -596,6 +628,8 @@ class NativeTrainer:
                         self._dgrad(d["a"], b["ga"], gx, mask=x, add=gx, add_after_mask=True)
                     g_next = gx
             g = g_next      # stage si-1's output gradient (gb[si-1]["g"] is the same buffer as this stage's gx)
+            if si >= 2:     # stages 5, 4 (98 % of the backbone's parameters); the small rest goes with the stem
+                self._push_after(st[0]["s"])
         self._mark("bwd_backbone")
         # stem: max-pool + ReLU + BN backward, then the native weight-gradient kernel for the 7x7x3 filter
         native.bn_relu_maxpool_bwd(p["pool_idx"], self.ones64, g, p["dstem"], *p["pool_pad"])
@@ -635,7 +669,15 @@ class NativeTrainer:
         if self.comm is not None and self.comm.world > 1:
             # the clip factor lives in peer-visible memory: peers apply it while reading my bucket
             native.clip_scale(self.scal[0:1], self.clipnorm, self.comm.prescale_local)
-            self.comm.allreduce_avg(self.G, self.Gavg, n, prescale=True)
+            if self._overlap():
+                # everything up to the last cut is already at its owner; send the tail, then reduce + gather
+                self._push_ready(n)
+                ev = torch.cuda.Event()
+                ev.record(self._comm_stream)
+                torch.cuda.current_stream(self.device).wait_event(ev)
+                self.comm.allreduce_staged_avg(n, prescale=True)
+            else:
+                self.comm.allreduce_avg(self.G, self.Gavg, n, prescale=True)
             native.adam(self.P[:n], self.Gavg[:n], self.M[:n], self.V[:n], None, self.lr_dev, self.beta1, self.beta2,
                         self.eps)
         else:

@@ -61,7 +61,7 @@ class ArHostArgs(C.Structure):
                 ("outs", C.c_void_p * 8), ("out", C.c_void_p), ("rank", C.c_int), ("world", C.c_int), ("offset", C.c_longlong),
                 ("count", C.c_longlong), ("postscale", C.c_float), ("epoch", C.c_uint32), ("algo", C.c_int),
                 ("max_blocks", C.c_int), ("has_prescale", C.c_int), ("epoch_ptr", C.c_void_p), ("mc_buf", C.c_void_p), ("mc_out", C.c_void_p),
-                ("external_sync", C.c_int)]
+                ("external_sync", C.c_int), ("stage", C.c_void_p * 8), ("wire_bf16", C.c_int)]
 
 
 def lib_path() -> str:
@@ -428,6 +428,15 @@ def flag_pad_bytes() -> int:
 
 def allreduce_host(args: ArHostArgs):
     _check(_load().b200_allreduce_host(C.byref(args), _stream()), "b200_allreduce_host")
+
+
+def ar_scatter(args: ArHostArgs, lo: int, hi: int, stream=None):
+    st = _stream() if stream is None else C.c_void_p(stream.cuda_stream)
+    _check(_load().b200_ar_scatter(C.byref(args), C.c_longlong(lo), C.c_longlong(hi), st), "b200_ar_scatter")
+
+
+def ar_reduce_staged(args: ArHostArgs):
+    _check(_load().b200_ar_reduce_staged(C.byref(args), _stream()), "b200_ar_reduce_staged")
 
 
 def broadcast_host(args: ArHostArgs, root: int):

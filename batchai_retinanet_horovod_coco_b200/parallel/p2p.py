@@ -3,7 +3,10 @@
 Replaces Horovod's NCCL/MPI data plane, fusion-buffer memcpys and the separate ``tf.div``
 (reference ``train.py:103``).  Each rank ``cudaMalloc``s ONE region
 
-    [ flag pad | 256 B scalars (this rank's clip factor) | fp32 bucket | fp32 result ]
+    [ flag pad | 256 B scalars (this rank's clip factor) | fp32 bucket | fp32 result | staging ]
+
+(staging = world slots of 1/world of the bucket: where the peers' raw slices of the part this rank owns land while
+backward is still running, see ``scatter`` / ``allreduce_staged_avg``)
 
 exports it with CUDA IPC, and maps every peer's region.  The engine's gradients are written
 straight into the bucket by the wgrad kernels, so there is nothing to copy in or out; the kernel
@@ -72,7 +75,10 @@ class P2PComm:
             return self.bucket[:nfloats]
         nfloats = (nfloats + 3) // 4 * 4
         self.bucket_elems = nfloats
-        total = self.flag_bytes + SCALARS_BYTES + 8 * nfloats   # bucket + peer-writable result buffer
+        self.stage_off = self.flag_bytes + SCALARS_BYTES + 8 * nfloats
+        per4 = -(-(nfloats // 4) // self.world)                       # float4 per owner slice
+        self.stage_bytes = self.world * per4 * 16
+        total = self.stage_off + self.stage_bytes   # bucket + peer-writable result buffer + staging
         with torch.cuda.device(self.device):
             if not self._alloc_region_vmm(total):
                 self._alloc_region_ipc(total)
@@ -232,9 +238,11 @@ class P2PComm:
 
     # ------------------------------------------------------------------ collectives
     def _args(self, out: torch.Tensor, offset: int, count: int, postscale: float, has_prescale: bool, algo: int,
-              push: bool = False):
+              push: bool = False, advance: bool = True):
         a = native.ArHostArgs()
+        a.wire_bf16 = int(os.environ.get("B200_AR_WIRE", "fp32") == "bf16")
         for r in range(self.world):
+            a.stage[r] = self.peer_base[r] + self.stage_off
             a.bufs[r] = self.peer_base[r] + self.flag_bytes + SCALARS_BYTES
             a.flags[r] = self.peer_base[r]
             a.prescale[r] = self.peer_base[r] + self.flag_bytes
@@ -254,7 +262,8 @@ class P2PComm:
         a.max_blocks = 0
         a.has_prescale = int(has_prescale)
         a.external_sync = int(self.external_sync)
-        self.epoch = (self.epoch + 4) & 0xFFFFFFFF    # wraps mod 2^32 like the device-side counter
+        if advance:
+            self.epoch = (self.epoch + 4) & 0xFFFFFFFF    # wraps mod 2^32 like the device-side counter
         return a
 
     def allreduce_avg(self, bucket: torch.Tensor, out: torch.Tensor, n: int, prescale: bool = True, algo: int = 0):
@@ -267,6 +276,25 @@ class P2PComm:
         self._before_collective()
         native.allreduce_host(a)
         self._after_collective()
+
+    # ---- allreduce split around backward: scatter raw slices as they become final, reduce + gather at the end
+    def can_stage(self) -> bool:
+        return self.world > 1 and not self.external_sync and os.environ.get("B200_AR_OVERLAP", "1") != "0"
+
+    def scatter(self, n: int, lo: int, hi: int, stream=None):
+        """Send elements [lo, hi) of the bucket (final on this rank, NOT yet clipped) to the staging area of their
+        owner rank.  No flags: ordering comes from the barrier at the start of ``allreduce_staged_avg``.  ``n`` must
+        be the ``n`` of that call."""
+        n4 = (n + 3) // 4 * 4
+        a = self._args(self.result, 0, n4, 1.0, False, 0, push=True, advance=False)
+        native.ar_scatter(a, lo, min(hi, n4), stream)
+
+    def allreduce_staged_avg(self, n: int, prescale: bool = True):
+        """result[:n] = (1/world) * sum_r prescale_r * bucket_r[:n] where every peer slice was already scattered:
+        this rank reduces its 1/world slice from LOCAL memory and multicasts (or pushes) it to every rank."""
+        n4 = (n + 3) // 4 * 4
+        a = self._args(self.result, 0, n4, 1.0 / self.world, prescale, 0, push=True)
+        native.ar_reduce_staged(a)
 
     def allreduce_sum_(self, t: torch.Tensor, average: bool = False):
         """Generic in-place allreduce of an arbitrary fp32 CUDA tensor, staged through the bucket."""

@@ -1,5 +1,5 @@
 // Peer-to-peer gradient allreduce / broadcast over NVLink (sm_100a), fused with the per-rank
-// global-norm clip factor, the 1/N averaging scale and (optionally) a bf16 wire format.
+// global-norm clip factor and the 1/N averaging scale; the staged (overlapped) path can carry bf16.
 //
 // Every rank maps every peer's bucket and flag pad (CUDA IPC) and runs the same kernel:
 //   one-shot : barrier; out[i] = post * sum_r pre_r * peer_r[i]; barrier           (small buckets)
@@ -13,6 +13,8 @@
 #include <cstdlib>
 
 #include "../include/b200_ops.h"
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -36,6 +38,8 @@ struct ArParams {
   float* mc_out;        // multicast address of the result buffer (NVLS), or null
   int has_prescale;
   int external_sync;  // no in-kernel flag barriers: the launching streams were ordered by the host
+  void* stage[kMaxWorld];   // peer-mapped staging areas (staged path)
+  int wire_bf16;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -313,6 +317,79 @@ __global__ void __launch_bounds__(kArThreads) broadcast_kernel(const ArParams p,
   rank_barrier(p, ar_epoch(p) + 2);
 }
 
+// ---- staged allreduce: scatter during backward, weighted reduce + all-gather after it ------------------------
+// Staging area of owner o: [world][per] float4 (or [world][per] 8-byte bf16x4), slot r = rank r's raw slice o.
+__device__ __forceinline__ uint2 pack_bf16x4(float4 v) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  return make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+}
+__device__ __forceinline__ float4 unpack_bf16x4(uint2 u) {
+  return make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u), __uint_as_float(u.y << 16),
+                     __uint_as_float(u.y & 0xffff0000u));
+}
+
+__global__ void __launch_bounds__(256) ar_scatter_kernel(const ArParams p, long long lo4, long long hi4) {
+  const long long n4 = p.count >> 2;
+  const long long per = (n4 + p.world - 1) / p.world;
+  const float4* mine = reinterpret_cast<const float4*>(p.bufs[p.rank] + p.offset);
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = lo4 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < hi4; i += stride) {
+    const int owner = static_cast<int>(i / per);
+    if (owner == p.rank) continue;
+    const float4 v = mine[i];
+    const long long slot = static_cast<long long>(p.rank) * per + (i - owner * per);
+    if (p.wire_bf16) reinterpret_cast<uint2*>(p.stage[owner])[slot] = pack_bf16x4(v);
+    else reinterpret_cast<float4*>(p.stage[owner])[slot] = v;
+  }
+  __threadfence_system();
+}
+
+template <int kWorld>
+__global__ void __launch_bounds__(kArThreads) ar_reduce_staged_kernel(const ArParams p) {
+  rank_barrier(p, ar_epoch(p) + 1);        // every rank's scatters have landed, every clip factor is published
+  float pre[kWorld];
+#pragma unroll
+  for (int r = 0; r < kWorld; ++r) pre[r] = p.has_prescale ? *p.prescale[r] : 1.f;
+  const long long n4 = p.count >> 2;
+  const long long per = (n4 + kWorld - 1) / kWorld;
+  const long long lo = per * p.rank, hi = min(n4, lo + per);
+  const float4* mine = reinterpret_cast<const float4*>(p.bufs[p.rank] + p.offset);
+  const float4* st32 = reinterpret_cast<const float4*>(p.stage[p.rank]);
+  const uint2* st16 = reinterpret_cast<const uint2*>(p.stage[p.rank]);
+  float* mc_out = p.mc_out ? p.mc_out + p.offset : nullptr;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = lo + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
+    // all loads of this element first (local HBM; the staged slices were written by the peers' scatter kernels)
+    float4 v[kWorld];
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) {
+      if (r == p.rank) {
+        v[r] = mine[i];
+      } else if (p.wire_bf16) {
+        uint2 u;
+        asm volatile("ld.global.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(u.x), "=r"(u.y) : "l"(st16 + r * per + (i - lo)) : "memory");
+        v[r] = unpack_bf16x4(u);
+      } else {
+        v[r] = ld_peer(reinterpret_cast<const float*>(st32 + r * per + (i - lo)));
+      }
+    }
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) {
+      acc.x += pre[r] * v[r].x; acc.y += pre[r] * v[r].y; acc.z += pre[r] * v[r].z; acc.w += pre[r] * v[r].w;
+    }
+    acc.x *= p.postscale; acc.y *= p.postscale; acc.z *= p.postscale; acc.w *= p.postscale;
+    if (mc_out) {
+      multimem_st(mc_out + i * 4, acc);      // one store, delivered to every rank's result buffer by the switch
+    } else {
+#pragma unroll
+      for (int r = 0; r < kWorld; ++r) reinterpret_cast<float4*>(p.outs[(p.rank + r) % kWorld] + p.offset)[i] = acc;
+    }
+  }
+  __threadfence_system();
+  rank_barrier(p, ar_epoch(p) + 2);
+}
+
 __global__ void scale_copy_kernel(const float* __restrict__ in, float* __restrict__ out, long long n4,
                                   const float* __restrict__ pre, float post) {
   const float s = (pre ? *pre : 1.f) * post;
@@ -355,6 +432,8 @@ static int fill(ArParams& p, const B200ArHostArgs* a) {
   p.mc_buf = static_cast<const float*>(a->mc_buf);
   p.mc_out = static_cast<float*>(a->mc_out);
   p.external_sync = a->external_sync;
+  for (int r = 0; r < kMaxWorld; ++r) p.stage[r] = r < a->world ? a->stage[r] : nullptr;
+  p.wire_bf16 = a->wire_bf16;
   return 0;
 }
 
@@ -421,6 +500,52 @@ int b200_allreduce_host(const B200ArHostArgs* a, void* stream_) {
 #undef B200_AR_LAUNCH
   if (a->epoch_ptr) epoch_bump_kernel<<<1, 1, 0, stream>>>(a->epoch_ptr);
   return check_launch("allreduce_kernel");
+}
+
+int b200_ar_scatter(const B200ArHostArgs* a, long long lo, long long hi, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  ArParams p;
+  int rc = fill(p, a);
+  if (rc) return rc;
+  if (p.world == 1 || hi <= lo) return 0;
+  if ((lo & 3) || (hi & 3) || hi > p.count) return set_error(-1, "ar_scatter: range must be float4-aligned and inside count");
+  if (!p.stage[0]) return set_error(-1, "ar_scatter: no staging areas");
+  const long long n4 = (hi - lo) >> 2;
+  // few, small blocks: this kernel runs beside the backward pass and only has to keep NVLink stores flowing
+  long long blocks = (n4 + 256 * 8 - 1) / (256 * 8);
+  if (blocks > 64) blocks = 64;
+  if (blocks < 1) blocks = 1;
+  ar_scatter_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(p, lo >> 2, hi >> 2);
+  return check_launch("ar_scatter_kernel");
+}
+
+int b200_ar_reduce_staged(const B200ArHostArgs* a, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  ArParams p;
+  int rc = fill(p, a);
+  if (rc) return rc;
+  const long long n4 = p.count >> 2;
+  if (n4 == 0) return 0;
+  if (p.world == 1) return b200_allreduce_host(a, stream_);
+  if (p.external_sync) return set_error(-1, "ar_reduce_staged: needs in-kernel flag barriers");
+  if (!p.stage[0] || (!p.mc_out && !p.outs[0])) return set_error(-1, "ar_reduce_staged: staging / output areas missing");
+  const long long work = (n4 + p.world - 1) / p.world;
+  int blocks = a->max_blocks > 0 ? a->max_blocks : 2 * num_sms();
+  if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  const long long need = (work + kArThreads - 1) / kArThreads;
+  if (need < blocks) blocks = static_cast<int>(need < 1 ? 1 : need);
+  switch (p.world) {
+    case 2: ar_reduce_staged_kernel<2><<<blocks, kArThreads, 0, stream>>>(p); break;
+    case 3: ar_reduce_staged_kernel<3><<<blocks, kArThreads, 0, stream>>>(p); break;
+    case 4: ar_reduce_staged_kernel<4><<<blocks, kArThreads, 0, stream>>>(p); break;
+    case 5: ar_reduce_staged_kernel<5><<<blocks, kArThreads, 0, stream>>>(p); break;
+    case 6: ar_reduce_staged_kernel<6><<<blocks, kArThreads, 0, stream>>>(p); break;
+    case 7: ar_reduce_staged_kernel<7><<<blocks, kArThreads, 0, stream>>>(p); break;
+    case 8: ar_reduce_staged_kernel<8><<<blocks, kArThreads, 0, stream>>>(p); break;
+    default: return set_error(-1, "ar_reduce_staged: world size %d not instantiated", p.world);
+  }
+  if (a->epoch_ptr) epoch_bump_kernel<<<1, 1, 0, stream>>>(a->epoch_ptr);
+  return check_launch("ar_reduce_staged_kernel");
 }
 
 int b200_broadcast_host(const B200ArHostArgs* a, int root, void* stream_) {

@@ -204,7 +204,7 @@ int b200_nms_sorted_noalloc_max(void);
 /* ------------------------------------------------------------------ peer-to-peer collectives
  * Allreduce over NVLink peer mappings: every rank passes the table of all ranks' bucket
  * pointers (mapped with CUDA IPC) and flag pads (host arrays, copied into kernel params).  Fused: per-rank pre-scale (global-norm clip
- * factor read from each peer), 1/N averaging, optional bf16 wire format.
+ * factor read from each peer), 1/N averaging; the staged path can carry the peers' slices as bf16.
  * Replaces: ncclAllReduce / MPI_Allreduce + tf.div + fusion-buffer memcpys (X1-X3). */
 typedef struct {
   void* bufs[8];            /* every rank's fp32 bucket base (peer-mapped device pointers) */
@@ -226,8 +226,23 @@ typedef struct {
   void* mc_out;             /* multicast (NVLS) address of the result buffer, or null */
   int external_sync;        /* 1: the caller orders the ranks with events (ranks = threads of one process); the
                                kernel then contains no flag barrier and algo is forced to one-shot */
+  void* stage[8];           /* every rank's peer-mapped STAGING area (world x ceil(count/4/world) float4), or null:
+                               used by b200_ar_scatter / b200_ar_reduce_staged */
+  int wire_bf16;            /* staged path: peers' raw slices travel and are staged as bf16 (half the scatter bytes) */
 } B200ArHostArgs;
 int b200_allreduce_host(const B200ArHostArgs* args, void* stream);
+/* Allreduce split around the backward pass (Horovod clips by the LOCAL global norm before averaging, reference
+ * train.py:103-104, so the weights of the sum are unknown until backward ends -- but the raw gradients are not):
+ *   b200_ar_scatter       elements [lo, hi) of this rank's bucket go, raw, to the staging area of the rank that
+ *                         owns them (owner = index / ceil(n/world)); call it on a side stream as soon as a range
+ *                         of the bucket is final, any number of times per step; no barrier, no flags;
+ *   b200_ar_reduce_staged after the clip factors exist: flag barrier, every rank forms
+ *                         post * sum_r pre_r * g_r over ITS slice from local memory (own bucket + staged peers) and
+ *                         stores it into every rank's result buffer (multimem.st through the switch when mc_out is
+ *                         given, else one store per peer), flag barrier.
+ * Only the all-gather half stays on the critical path.  `count` must be the same in both calls. */
+int b200_ar_scatter(const B200ArHostArgs* args, long long lo, long long hi, void* stream);
+int b200_ar_reduce_staged(const B200ArHostArgs* args, void* stream);
 int b200_broadcast_host(const B200ArHostArgs* args, int root, void* stream);
 long long b200_flag_pad_bytes(void);
 /* IPC helpers (cudaIpc*): 64-byte handles exchanged by the Python layer. */

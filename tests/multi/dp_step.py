@@ -31,6 +31,13 @@ torch.cuda.synchronize()
 gavg = nt.Gavg[:nt.n_train].clone()
 ref = gavg.clone(); dist.broadcast(ref, 0)
 assert torch.equal(ref, gavg), "averaged gradients differ between ranks"
+# the overlapped (scatter during backward + staged reduce) result equals a plain allreduce of the same bucket
+assert nt._overlap(), "the distributed engine should use the overlapped allreduce by default"
+plain = torch.zeros(nt.n_train + 64, device=dev)
+nt.comm.allreduce_avg(nt.G, plain, nt.n_train, prescale=True, algo=2)
+torch.cuda.synchronize()
+d = (plain[:nt.n_train] - gavg).abs().max().item()
+assert d <= 1e-6 * (1 + gavg.abs().max().item()), f"overlapped allreduce differs from the plain one by {d}"
 p1 = nt.P.clone(); chk = p1.clone(); dist.broadcast(chk, 0)
 assert torch.equal(chk, p1), "parameters diverged after one step"
 assert not torch.equal(p1, p0)
