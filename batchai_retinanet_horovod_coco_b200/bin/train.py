@@ -278,6 +278,8 @@ def fit_generator(trainer, generator, steps_per_epoch, epochs, callbacks, initia
                 m = (sums / (step + 1)).tolist()
                 cl.on_batch_end(step, {"loss": m[0], "regression_loss": m[1], "classification_loss": m[2]})
         m = (sums / steps_per_epoch).tolist()
+        if hasattr(trainer, "check_comm"):
+            trainer.check_comm()        # a peer that vanished shows up as a timed-out flag barrier, not as a hang
         logs = {"loss": m[0], "regression_loss": m[1], "classification_loss": m[2]}
         cl.on_epoch_end(epoch, logs)
         history.append(logs)

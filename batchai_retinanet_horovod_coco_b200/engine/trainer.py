@@ -132,6 +132,8 @@ class NativeTrainer:
         self.load_from_model(self.model)
         self._plans = {}
         self._prof = None  # list of (name, cuda event) when profiling
+        self._comm_prof = None   # [(lo, hi, start event, end event)] of the scatter pieces when tracing
+        self._nvtx = os.environ.get("B200_NVTX", "0") == "1"
         self.mean_t = torch.tensor(CAFFE_MEAN_BGR, device=self.device)
         if distributed and comm is None:
             from ..parallel.p2p import P2PComm
@@ -522,7 +524,13 @@ class NativeTrainer:
         ev = torch.cuda.Event()
         ev.record(main)
         self._comm_stream.wait_event(ev)
+        if self._comm_prof is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(self._comm_stream)
         self.comm.scatter(self.n_train, self._pushed, upto, stream=self._comm_stream)
+        if self._comm_prof is not None:
+            e1.record(self._comm_stream)
+            self._comm_prof.append((self._pushed, upto, e0, e1))
         self._pushed = upto
 
     def _push_after(self, conv):
@@ -656,6 +664,11 @@ class NativeTrainer:
         self.__dict__.pop("_stem_idx", None)      # the packed-stem helper caches the (just replaced) BN scale
         self._refresh_weights()
 
+    def check_comm(self):
+        """Raise if a gradient collective timed out since the last check (a peer rank is gone).  Synchronises."""
+        if self.comm is not None and hasattr(self.comm, "check"):
+            self.comm.check()
+
     def _begin_step(self):
         """Host-side per-step scalars, written to device memory OUTSIDE any captured graph."""
         self.iterations += 1
@@ -665,19 +678,30 @@ class NativeTrainer:
 
     def _optimizer_step(self):
         n = self.n_train
-        native.sumsq(self.G[:n], self.scal[0:1])
         if self.comm is not None and self.comm.world > 1:
-            # the clip factor lives in peer-visible memory: peers apply it while reading my bucket
-            native.clip_scale(self.scal[0:1], self.clipnorm, self.comm.prescale_local)
-            if self._overlap():
-                # everything up to the last cut is already at its owner; send the tail, then reduce + gather
-                self._push_ready(n)
-                ev = torch.cuda.Event()
-                ev.record(self._comm_stream)
-                torch.cuda.current_stream(self.device).wait_event(ev)
-                self.comm.allreduce_staged_avg(n, prescale=True)
-            else:
-                self.comm.allreduce_avg(self.G, self.Gavg, n, prescale=True)
+            with self._phase("allreduce"):
+                native.sumsq(self.G[:n], self.scal[0:1])
+                # the clip factor lives in peer-visible memory: peers apply it while reading my bucket
+                native.clip_scale(self.scal[0:1], self.clipnorm, self.comm.prescale_local)
+                if self._overlap():
+                    # everything up to the last cut is already at its owner; send the tail, then reduce + gather
+                    self._push_ready(n)
+                    ev = torch.cuda.Event()
+                    ev.record(self._comm_stream)
+                    torch.cuda.current_stream(self.device).wait_event(ev)
+                    self.comm.allreduce_staged_avg(n, prescale=True)
+                else:
+                    self.comm.allreduce_avg(self.G, self.Gavg, n, prescale=True)
+            with self._phase("optimizer"):
+                self._adam_and_refresh(distributed=True)
+            return
+        with self._phase("optimizer"):
+            native.sumsq(self.G[:n], self.scal[0:1])
+            self._adam_and_refresh(distributed=False)
+
+    def _adam_and_refresh(self, distributed: bool):
+        n = self.n_train
+        if distributed:
             native.adam(self.P[:n], self.Gavg[:n], self.M[:n], self.V[:n], None, self.lr_dev, self.beta1, self.beta2,
                         self.eps)
         else:
@@ -692,7 +716,49 @@ class NativeTrainer:
             ev.record()
             self._prof.append((name, ev))
 
-    def profile_step(self, *batch):
+    class _Phase:
+        """NVTX range (B200_NVTX=1; shows in nsys / ncu timelines) + profile mark around one phase of the step."""
+
+        def __init__(self, trainer, name):
+            self.t, self.name = trainer, name
+
+        def __enter__(self):
+            if self.t._nvtx:
+                torch.cuda.nvtx.range_push(self.name)
+
+        def __exit__(self, *exc):
+            if self.t._nvtx:
+                torch.cuda.nvtx.range_pop()
+            self.t._mark(self.name)
+            return False
+
+    def _phase(self, name):
+        return NativeTrainer._Phase(self, name)
+
+    def trace_step(self, *batch, tag: str = ""):
+        """One eager step timed with CUDA events per phase -- on the main stream AND on the gradient-scatter stream --
+        written into the runtime's Chrome-trace timeline (``--timeline`` / HOROVOD_TIMELINE) as GPU_<PHASE> events:
+        the overlapped allreduce (GRAD_SCATTER pieces beside BACKWARD, ALLREDUCE after it) becomes visible next to
+        the host runtime's phases.  Returns {phase: ms}."""
+        from .. import parallel as hvd
+        torch.cuda.synchronize(self.device)
+        t_anchor = hvd.timeline_now_ns() if hvd.timeline_active() else 0
+        self._comm_prof = []
+        out = self.profile_step(*batch, keep=True)
+        base = self._prof_events[0][1]
+        if hvd.timeline_active():
+            for (n0, e0), (n1, e1) in zip(self._prof_events[:-1], self._prof_events[1:]):
+                hvd.timeline_event("GPU_" + n1.upper(), tag or "step", t_anchor + int(base.elapsed_time(e0) * 1e6),
+                                   t_anchor + int(base.elapsed_time(e1) * 1e6))
+            for (lo, hi, e0, e1) in self._comm_prof:
+                hvd.timeline_event("GPU_GRAD_SCATTER", f"G[{lo}:{hi}]", t_anchor + int(base.elapsed_time(e0) * 1e6),
+                                   t_anchor + int(base.elapsed_time(e1) * 1e6))
+        out["grad_scatter_pieces"] = [(lo, hi, round(e0.elapsed_time(e1), 4)) for lo, hi, e0, e1 in self._comm_prof]
+        self._comm_prof = None
+        self._prof_events = None
+        return out
+
+    def profile_step(self, *batch, keep=False):
         """Run one step with CUDA events between phases; returns {phase: ms} (device time)."""
         self._prof = []
         self._mark("start")
@@ -701,6 +767,8 @@ class NativeTrainer:
         out = {}
         for (n0, e0), (n1, e1) in zip(self._prof[:-1], self._prof[1:]):
             out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+        if keep:
+            self._prof_events = self._prof
         self._prof = None
         return out
 
@@ -763,20 +831,19 @@ class NativeTrainer:
 
     def _step_front(self, p, images_u8, gt, gt_count, img_hw):
         """Forward + losses; the loss triple is final here and goes to pinned host memory."""
-        self.G.zero_()
-        self._mark("h2d+zero")
-        self._forward(p, images_u8, img_hw)
-        self._mark("forward")
-        self._losses(p, gt, gt_count, img_hw)
-        torch.stack([self.scal[2] + self.scal[3], self.scal[2], self.scal[3]], out=self.loss_out)
-        self.loss_host.copy_(self.loss_out, non_blocking=True)
-        self._mark("losses")
+        with self._phase("h2d+zero"):
+            self.G.zero_()
+        with self._phase("forward"):
+            self._forward(p, images_u8, img_hw)
+        with self._phase("losses"):
+            self._losses(p, gt, gt_count, img_hw)
+            torch.stack([self.scal[2] + self.scal[3], self.scal[2], self.scal[3]], out=self.loss_out)
+            self.loss_host.copy_(self.loss_out, non_blocking=True)
 
     def _step_back(self, p):
-        self._backward(p)
-        self._mark("backward")
+        with self._phase("backward"):
+            self._backward(p)
         self._optimizer_step()
-        self._mark("optimizer")
 
     def _step_body(self, p, images_u8, gt, gt_count, img_hw):
         """A whole step with plain launches, in stream order."""

@@ -61,7 +61,8 @@ class ArHostArgs(C.Structure):
                 ("outs", C.c_void_p * 8), ("out", C.c_void_p), ("rank", C.c_int), ("world", C.c_int), ("offset", C.c_longlong),
                 ("count", C.c_longlong), ("postscale", C.c_float), ("epoch", C.c_uint32), ("algo", C.c_int),
                 ("max_blocks", C.c_int), ("has_prescale", C.c_int), ("epoch_ptr", C.c_void_p), ("mc_buf", C.c_void_p), ("mc_out", C.c_void_p),
-                ("external_sync", C.c_int), ("stage", C.c_void_p * 8), ("wire_bf16", C.c_int)]
+                ("external_sync", C.c_int), ("stage", C.c_void_p * 8), ("wire_bf16", C.c_int),
+                ("err", C.c_void_p), ("timeout_cycles", C.c_longlong)]
 
 
 def lib_path() -> str:

@@ -129,6 +129,24 @@ def timeline_stop():
         _rt.lib().b200rt_timeline_stop()
 
 
+def timeline_active() -> bool:
+    return bool(_state["init"] and _rt.lib().b200rt_timeline_active())
+
+
+def timeline_now_ns() -> int:
+    import ctypes as C
+    f = _rt.lib().b200rt_now_ns
+    f.restype = C.c_ulonglong
+    return int(f())
+
+
+def timeline_event(phase: str, name: str, t0_ns: int, t1_ns: int):
+    """One complete event of the GPU path (device-timed) in the runtime's Chrome trace, next to the host phases."""
+    import ctypes as C
+    if timeline_active():
+        _rt.lib().b200rt_timeline_event(phase.encode(), name.encode(), C.c_ulonglong(int(t0_ns)), C.c_ulonglong(int(t1_ns)))
+
+
 def stats() -> dict:
     import ctypes as C
     out = (C.c_longlong * 5)()

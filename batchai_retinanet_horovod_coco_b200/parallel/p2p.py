@@ -87,6 +87,8 @@ class P2PComm:
         off = self.flag_bytes
         self.prescale_local = raw[off:off + 4].view(torch.float32)
         self.prescale_local.fill_(1.0)
+        self.err_word = raw[off + 96:off + 104].view(torch.int32)       # {code, peer} of a timed-out flag barrier
+        self.err_word.zero_()
         self.bucket = raw[off + SCALARS_BYTES:off + SCALARS_BYTES + 4 * nfloats].view(torch.float32)
         self.result = raw[off + SCALARS_BYTES + 4 * nfloats:off + SCALARS_BYTES + 8 * nfloats].view(torch.float32)
         torch.cuda.synchronize(self.device)
@@ -241,6 +243,9 @@ class P2PComm:
               push: bool = False, advance: bool = True):
         a = native.ArHostArgs()
         a.wire_bf16 = int(os.environ.get("B200_AR_WIRE", "fp32") == "bf16")
+        # flag barriers give up after B200_AR_TIMEOUT_S seconds (default 30; 0 = wait for ever); ~2 GHz SM clock
+        a.err = self.base + self.flag_bytes + 96
+        a.timeout_cycles = int(float(os.environ.get("B200_AR_TIMEOUT_S", "30")) * 2.0e9)
         for r in range(self.world):
             a.stage[r] = self.peer_base[r] + self.stage_off
             a.bufs[r] = self.peer_base[r] + self.flag_bytes + SCALARS_BYTES
@@ -338,6 +343,15 @@ class P2PComm:
                 flat[done:done + m].copy_(tmp[:m])
             done += m
         return t
+
+    def check(self):
+        """Raise if a flag barrier of an earlier collective timed out (a peer did not arrive).  Synchronises."""
+        if self.bucket is None or self.world == 1:
+            return
+        code, peer = (int(v) for v in self.err_word.cpu())
+        if code != 0:
+            raise RuntimeError(f"P2P collective timed out on rank {self.rank}: rank {peer} never reached the flag "
+                               f"barrier (epoch {code & 0x7FFFFFFF}); the job cannot continue")
 
     def close(self):
         torch.cuda.synchronize(self.device)

@@ -40,6 +40,8 @@ struct ArParams {
   int external_sync;  // no in-kernel flag barriers: the launching streams were ordered by the host
   void* stage[kMaxWorld];   // peer-mapped staging areas (staged path)
   int wire_bf16;
+  unsigned int* err;        // local {code, peer} word pair written when a barrier times out
+  long long timeout_cycles;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -67,7 +69,15 @@ __device__ __forceinline__ void rank_barrier(const ArParams& p, uint32_t value) 
     const int peer = threadIdx.x;
     st_release_sys(p.flags[peer] + blockIdx.x * kMaxWorld + p.rank, value);
     const uint32_t* mine = p.flags[p.rank] + blockIdx.x * kMaxWorld + peer;
+    // A peer that died or hangs between launches must not leave this GPU spinning in a kernel for ever (a hung
+    // kernel also blocks context teardown): after timeout_cycles the barrier records {awaited epoch, peer} and gives
+    // up; the host raises from P2PComm.check().  The results of a timed-out collective are garbage.
+    const long long t0 = clock64();
     while (static_cast<int32_t>(ld_acquire_sys(mine) - value) < 0) {
+      if (p.timeout_cycles > 0 && clock64() - t0 > p.timeout_cycles) {
+        if (p.err && atomicCAS(p.err, 0u, value | 0x80000000u) == 0u) p.err[1] = static_cast<unsigned int>(peer);
+        break;
+      }
     }
   }
   __syncthreads();
@@ -434,6 +444,8 @@ static int fill(ArParams& p, const B200ArHostArgs* a) {
   p.external_sync = a->external_sync;
   for (int r = 0; r < kMaxWorld; ++r) p.stage[r] = r < a->world ? a->stage[r] : nullptr;
   p.wire_bf16 = a->wire_bf16;
+  p.err = a->err;
+  p.timeout_cycles = a->timeout_cycles;
   return 0;
 }
 

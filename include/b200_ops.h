@@ -229,6 +229,10 @@ typedef struct {
   void* stage[8];           /* every rank's peer-mapped STAGING area (world x ceil(count/4/world) float4), or null:
                                used by b200_ar_scatter / b200_ar_reduce_staged */
   int wire_bf16;            /* staged path: peers' raw slices travel and are staged as bf16 (half the scatter bytes) */
+  unsigned int* err;        /* LOCAL device word pair {code, peer}: a flag barrier that waited longer than
+                               timeout_cycles for `peer` stores code = the awaited epoch here and gives up (the
+                               results of that call are then garbage); null: never written */
+  long long timeout_cycles; /* 0: wait for ever */
 } B200ArHostArgs;
 int b200_allreduce_host(const B200ArHostArgs* args, void* stream);
 /* Allreduce split around the backward pass (Horovod clips by the LOCAL global norm before averaging, reference

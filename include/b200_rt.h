@@ -49,6 +49,10 @@ const char* b200rt_last_error(void);
 
 int b200rt_timeline_start(const char* path);   /* rank 0 writes a Chrome trace (HOROVOD_TIMELINE) */
 int b200rt_timeline_stop(void);
+/* GPU-path phases (device-timed with CUDA events by the engine) written into the same trace, on this clock. */
+unsigned long long b200rt_now_ns(void);
+int b200rt_timeline_active(void);
+int b200rt_timeline_event(const char* phase, const char* tensor, unsigned long long t0_ns, unsigned long long t1_ns);
 /* statistics: cycles run, responses executed, tensors fused, bytes reduced, stall warnings */
 void b200rt_stats(long long out[5]);
 

@@ -44,7 +44,23 @@ assert not torch.equal(p1, p0)
 for _ in range(3):
     loss = nt.train_step(img[sl], gt[sl], cnt[sl], hw[sl])
 assert torch.isfinite(loss).all()
-nt.comm.close()
+# the overlapped allreduce must be visible in the Horovod-style timeline: scatter pieces beside the backward pass
+import json, tempfile
+import batchai_retinanet_horovod_coco_b200.parallel as hvd
+hvd.init()
+tl = os.path.join(tempfile.gettempdir(), f"b200_tl_{os.environ.get('MASTER_PORT', '0')}.json")
 if rank == 0:
-    print("DP_OK", loss.tolist())
+    hvd.timeline_start(tl)
+ph = nt.trace_step(img[sl], gt[sl], cnt[sl], hw[sl], tag="dp_step")
+assert ph["allreduce"] > 0 and len(ph["grad_scatter_pieces"]) >= 4, ph
+hvd.timeline_stop()
+if rank == 0:
+    names = {e["name"] for e in json.load(open(tl))}
+    assert {"GPU_GRAD_SCATTER", "GPU_ALLREDUCE", "GPU_BACKWARD", "GPU_FORWARD"} <= names, names
+    os.remove(tl)
+nt.check_comm()
+nt.comm.close()
+hvd.shutdown()
+if rank == 0:
+    print("DP_OK", loss.tolist(), {k: round(v, 3) for k, v in ph.items() if isinstance(v, float)})
 dist.destroy_process_group()

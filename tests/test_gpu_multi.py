@@ -43,3 +43,9 @@ def test_single_process_towers():
                        timeout=420, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "TOWERS_OK" in r.stdout
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+def test_flag_barrier_times_out_when_a_rank_is_missing():
+    out = _run("barrier_timeout.py", 2, timeout=180)
+    assert "TIMEOUT_OK" in out
