@@ -63,6 +63,13 @@ while size <= MAXB:
         comm.prescale_local.fill_(1.0)
         bucket.normal_()
     best = min(v for k, v in row.items() if k.endswith("_us"))
+    # staged path (the engine's default): the scatter runs beside backward; what stays on the critical path is the
+    # flag barrier + local weighted reduce + all-gather through the switch.  Receives (N-1)/N * S per GPU.
+    comm.scatter(n, 0, n)
+    row["staged_scatter_us_hidden"] = timeit(lambda: comm.scatter(n, 0, n), iters) * 1e3
+    fg = timeit(lambda: comm.allreduce_staged_avg(n, prescale=True), iters) * 1e3
+    row["staged_foreground_us"] = fg
+    row["staged_foreground_frac_of_nvlink_roofline"] = (world - 1) / world * size / LINK * 1e6 / fg
     ms_n = timeit(lambda: dist.all_reduce(nccl_buf[:n]), iters)
     row["nccl_us"] = ms_n * 1e3
     row["p2p_algbw_GBs"] = size / best / 1e3
