@@ -3,8 +3,6 @@
 // FilterDetections as built into the prediction graph at reference train.py:95
 // (SURVEY.md B6-B8, G17, G18).  In the reference this is a TF map_fn over images with a CPU NMS
 // kernel per class; here it is a handful of launches for the whole batch.
-#include <cub/device/device_segmented_radix_sort.cuh>
-
 #include "../include/b200_ops.h"
 #include "common.cuh"
 #include "ptx_sm100.cuh"
@@ -20,79 +18,124 @@ struct LevelTable {
   int num_levels;
 };
 
-// Threshold + compaction.  Slots are claimed with ONE atomic per warp (prefix sum over the lanes'
-// pass counts) whenever the warp sits inside a single image, which is almost always: with an
-// untrained network millions of scores can pass and per-element atomics on one counter serialise.
-__global__ void collect_kernel(const __nv_bfloat16* __restrict__ logits, long long pixels_total, int HW, int K, int ld,
-                               int a_off, float logit_thr, int max_cand, int* __restrict__ count,
-                               unsigned long long* __restrict__ keys) {
+// Candidate selection.  Every score above the threshold is a candidate (keras-retinanet keeps them all per class);
+// the bitmask NMS takes the kNmsCap best of an image.  WHICH ones must not depend on thread timing, so the cut is an
+// exact top-k on the 64-bit key (score bits << 32 | ~id, ids are unique): a 4-pass radix select over 16-bit digits
+// finds the k-th largest key of every image (pass p histograms digit p of the keys that match the digits chosen so
+// far), then one more pass over the logits compacts the keys >= that one -- exactly min(k, #candidates) of them --
+// and a bitonic sort in shared memory orders them.  No library sort, no arrival-order truncation.
+constexpr int kDigitBins = 1 << 16;
+
+__device__ __forceinline__ unsigned long long det_key(float logit, unsigned int id) {
+  const float score = 1.f / (1.f + __expf(-logit));
+  return (static_cast<unsigned long long>(__float_as_uint(score)) << 32) | static_cast<unsigned int>(~id);
+}
+
+// mode 0: histogram of digit `pass` among keys whose higher digits equal prefix[b];  mode 1: compact keys >= kth[b]
+template <int kMode>
+__global__ void det_scan_kernel(const __nv_bfloat16* __restrict__ logits, long long pixels_total, int HW, int K, int ld,
+                                int a_off, float logit_thr, int pass, const unsigned long long* __restrict__ prefix,
+                                int* __restrict__ hist, int* __restrict__ count, unsigned long long* __restrict__ keys) {
   const int groups = (9 * K + 7) >> 3;
   const long long total = pixels_total * groups;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  const int lane = threadIdx.x & 31;
-  for (long long i0 = blockIdx.x * static_cast<long long>(blockDim.x) + (threadIdx.x & ~31); i0 < total; i0 += stride) {
-    const long long i = i0 + lane;
-    const bool in = i < total;
-    int g = 0, b = -1, p = 0;
-    float x[8];
-    uint32_t pass = 0;
-    if (in) {
-      g = static_cast<int>(i % groups);
-      const long long pix = i / groups;
-      b = static_cast<int>(pix / HW);
-      p = static_cast<int>(pix - static_cast<long long>(b) * HW);
-      const uint4 u = *reinterpret_cast<const uint4*>(logits + pix * ld + g * 8);
-      x[0] = bf16_lo(u.x); x[1] = bf16_hi(u.x); x[2] = bf16_lo(u.y); x[3] = bf16_hi(u.y);
-      x[4] = bf16_lo(u.z); x[5] = bf16_hi(u.z); x[6] = bf16_lo(u.w); x[7] = bf16_hi(u.w);
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int g = static_cast<int>(i % groups);
+    const long long pix = i / groups;
+    const int b = static_cast<int>(pix / HW);
+    const int p = static_cast<int>(pix - static_cast<long long>(b) * HW);
+    const uint4 u = *reinterpret_cast<const uint4*>(logits + pix * ld + g * 8);
+    const float x[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
+                        bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
+    const unsigned long long want = prefix[b];
 #pragma unroll
-      for (int e = 0; e < 8; ++e)
-        if (g * 8 + e < 9 * K && x[e] > logit_thr) pass |= 1u << e;
-    }
-    const int mine = __popc(pass);
-    const int b0 = __shfl_sync(0xffffffffu, b, 0);
-    const bool uniform = __all_sync(0xffffffffu, !in || b == b0);
-    int slot;
-    if (uniform && b0 >= 0) {
-      int incl = mine;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += t;
-      }
-      const int tot = __shfl_sync(0xffffffffu, incl, 31);
-      int base = 0;
-      if (lane == 0 && tot) base = atomicAdd(count + b0, tot);
-      base = __shfl_sync(0xffffffffu, base, 0);
-      slot = base + incl - mine;
-    } else {
-      slot = (in && mine) ? atomicAdd(count + b, mine) : 0;
-    }
-    if (in && mine) {
-#pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        if ((pass >> e) & 1u) {
-          if (slot < max_cand) {
-            const int ch = g * 8 + e;
-            const int j = ch / K, k = ch - j * K;
-            const float score = 1.f / (1.f + __expf(-x[e]));
-            const unsigned int id = static_cast<unsigned int>((a_off + p * 9 + j)) * static_cast<unsigned int>(K) + k;
-            keys[static_cast<long long>(b) * max_cand + slot] =
-                (static_cast<unsigned long long>(__float_as_uint(score)) << 32) | static_cast<unsigned int>(~id);
-          }
-          ++slot;
+    for (int e = 0; e < 8; ++e) {
+      const int ch = g * 8 + e;
+      if (ch >= 9 * K || !(x[e] > logit_thr)) continue;
+      const int j = ch / K, k = ch - j * K;
+      const unsigned int id = static_cast<unsigned int>((a_off + p * 9 + j)) * static_cast<unsigned int>(K) + k;
+      const unsigned long long key = det_key(x[e], id);
+      if (kMode == 0) {
+        if (pass == 0 || (key >> (64 - 16 * pass)) == want)
+          atomicAdd(hist + static_cast<long long>(b) * kDigitBins + static_cast<int>((key >> (48 - 16 * pass)) & 0xffffull), 1);
+      } else {
+        if (key >= want) {
+          const int slot = atomicAdd(count + b, 1);            // order is fixed by the sort that follows
+          if (slot < kNmsCap) keys[static_cast<long long>(b) * kNmsCap + slot] = key;
         }
       }
     }
   }
 }
 
-__global__ void segments_kernel(const int* __restrict__ count, int B, int max_cand, int* __restrict__ seg_begin,
-                                int* __restrict__ seg_end) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b < B) {
-    seg_begin[b] = b * max_cand;
-    seg_end[b] = b * max_cand + min(count[b], max_cand);
+// One block per image: walk the digit histogram from the top until `remaining` keys are covered; extend the prefix.
+__global__ void __launch_bounds__(1024) det_select_kernel(int* __restrict__ hist, unsigned long long* __restrict__ prefix,
+                                                          int* __restrict__ remaining, int pass) {
+  __shared__ int part[1024];
+  __shared__ int s_bin, s_above;
+  const int b = blockIdx.x, t = threadIdx.x;
+  int* h = hist + static_cast<long long>(b) * kDigitBins;
+  // thread t owns bins [hi - 63, hi], hi = 65535 - 64 t  (descending order of value)
+  const int hi = kDigitBins - 1 - 64 * t;
+  int sum = 0;
+  for (int q = 0; q < 64; ++q) sum += h[hi - q];
+  part[t] = sum;
+  __syncthreads();
+  if (t == 0) {
+    const int need = remaining[b];
+    int acc = 0, owner = -1;
+    for (int q = 0; q < 1024; ++q) {
+      if (acc + part[q] >= need) { owner = q; break; }
+      acc += part[q];
+    }
+    int bin = 0;                 // fewer candidates than needed: everything passes (k-th key = 0)
+    if (owner >= 0 && need > 0) {
+      const int ohi = kDigitBins - 1 - 64 * owner;
+      for (int q = 0; q < 64; ++q) {
+        if (acc + h[ohi - q] >= need) { bin = ohi - q; break; }
+        acc += h[ohi - q];
+      }
+    } else {
+      acc = 0;
+    }
+    s_bin = bin;
+    s_above = (owner >= 0 && need > 0) ? acc : 0;
   }
+  __syncthreads();
+  if (t == 0) {
+    prefix[b] = (prefix[b] << 16) | static_cast<unsigned long long>(s_bin);
+    remaining[b] = remaining[b] - s_above;          // keys still to take inside the chosen bin
+  }
+  for (int q = t; q < kDigitBins; q += 1024) h[q] = 0;     // ready for the next pass
+}
+
+// Descending bitonic sort of one image's <= kNmsCap keys in shared memory (unused slots hold 0 and sink to the end).
+__global__ void __launch_bounds__(1024) det_sort_kernel(const unsigned long long* __restrict__ keys, const int* __restrict__ count,
+                                                        unsigned long long* __restrict__ sorted) {
+  extern __shared__ unsigned long long sk[];
+  const int b = blockIdx.x;
+  const int n = min(count[b], kNmsCap);
+  int m = 64;
+  while (m < n) m <<= 1;                                   // power of two >= n
+  for (int i = threadIdx.x; i < m; i += blockDim.x) sk[i] = i < n ? keys[static_cast<long long>(b) * kNmsCap + i] : 0ull;
+  __syncthreads();
+  for (int k = 2; k <= m; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < m; i += blockDim.x) {
+        const int l = i ^ j;
+        if (l > i) {
+          const unsigned long long a = sk[i], c = sk[l];
+          const bool desc = (i & k) == 0;
+          if (desc ? a < c : a > c) {
+            sk[i] = c;
+            sk[l] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int i = threadIdx.x; i < n; i += blockDim.x) sorted[static_cast<long long>(b) * kNmsCap + i] = sk[i];
 }
 
 __global__ void decode_kernel(const unsigned long long* __restrict__ keys_sorted, const int* __restrict__ count,
@@ -216,22 +259,21 @@ __global__ void nms_scan_kernel(const unsigned long long* __restrict__ mask, con
 
 struct DetWorkspace {
   int* count;
-  int* seg_begin;
-  int* seg_end;
+  int* remaining;
+  unsigned long long* prefix;
+  int* hist;
   unsigned long long* keys;
   unsigned long long* keys_sorted;
   float* boxes;
   float* scores;
   int* labels;
   unsigned long long* mask;
-  void* cub_temp;
-  size_t cub_bytes;
   long long total;
 };
 
 static size_t align_up(size_t v) { return (v + 255) & ~static_cast<size_t>(255); }
 
-static DetWorkspace carve(void* base, int B, int max_cand) {
+static DetWorkspace carve(void* base, int B) {
   DetWorkspace w;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -240,22 +282,26 @@ static DetWorkspace carve(void* base, int B, int max_cand) {
     return p;
   };
   w.count = static_cast<int*>(take(sizeof(int) * B));
-  w.seg_begin = static_cast<int*>(take(sizeof(int) * B));
-  w.seg_end = static_cast<int*>(take(sizeof(int) * B));
-  w.keys = static_cast<unsigned long long*>(take(8ull * B * max_cand));
-  w.keys_sorted = static_cast<unsigned long long*>(take(8ull * B * max_cand));
+  w.remaining = static_cast<int*>(take(sizeof(int) * B));
+  w.prefix = static_cast<unsigned long long*>(take(8ull * B));
+  w.hist = static_cast<int*>(take(4ull * B * kDigitBins));
+  w.keys = static_cast<unsigned long long*>(take(8ull * B * kNmsCap));
+  w.keys_sorted = static_cast<unsigned long long*>(take(8ull * B * kNmsCap));
   w.boxes = static_cast<float*>(take(16ull * B * kNmsCap));
   w.scores = static_cast<float*>(take(4ull * B * kNmsCap));
   w.labels = static_cast<int*>(take(4ull * B * kNmsCap));
   w.mask = static_cast<unsigned long long*>(take(8ull * B * kNmsCap * (kNmsCap / 64)));
-  size_t cub_bytes = 0;
-  cub::DeviceSegmentedRadixSort::SortKeysDescending(nullptr, cub_bytes, static_cast<unsigned long long*>(nullptr),
-                                                    static_cast<unsigned long long*>(nullptr), B * max_cand, B,
-                                                    static_cast<int*>(nullptr), static_cast<int*>(nullptr));
-  w.cub_bytes = cub_bytes;
-  w.cub_temp = take(cub_bytes);
   w.total = static_cast<long long>(off);
   return w;
+}
+
+__global__ void det_init_kernel(int* count, int* remaining, unsigned long long* prefix, int B) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) {
+    count[b] = 0;
+    remaining[b] = kNmsCap;
+    prefix[b] = 0ull;
+  }
 }
 
 }  // namespace b200
@@ -264,7 +310,10 @@ using namespace b200;
 
 extern "C" {
 
-long long b200_filter_detections_workspace(int B, int max_cand) { return carve(nullptr, B, max_cand).total; }
+long long b200_filter_detections_workspace(int B, int max_cand) {
+  (void)max_cand;       // candidates are no longer capped before the selection (see det_scan_kernel)
+  return carve(nullptr, B).total;
+}
 
 int b200_filter_detections(const void* const* cls_levels, const void* const* reg_levels, const int* level_anchors,
                            int num_levels, int ld_cls, int ld_reg, int K, const float* anchors, int A_total, int B,
@@ -273,37 +322,57 @@ int b200_filter_detections(const void* const* cls_levels, const void* const* reg
                            int* out_labels, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (num_levels < 1 || num_levels > 5) return set_error(-1, "filter_detections: 1..5 levels");
-  DetWorkspace w = carve(workspace, B, max_cand);
+  DetWorkspace w = carve(workspace, B);
   if (w.total > workspace_bytes) return set_error(-1, "filter_detections: workspace too small (%lld < %lld)", workspace_bytes, w.total);
-  B200_CUDA_OK(cudaMemsetAsync(w.count, 0, sizeof(int) * B, stream));
+  max_cand = kNmsCap;       // stride of the key arrays
+  static std::atomic<unsigned long long> attr{0};   // per device
+  if (device_needs_setup(attr)) {
+    B200_CUDA_OK(cudaFuncSetAttribute(det_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNmsCap * 8));
+    device_setup_done(attr);
+  }
+  B200_CUDA_OK(cudaMemsetAsync(w.hist, 0, 4ull * B * kDigitBins, stream));
+  det_init_kernel<<<(B + 63) / 64, 64, 0, stream>>>(w.count, w.remaining, w.prefix, B);
   LevelTable lt;
   lt.num_levels = num_levels;
-  int off = 0;
   const float logit_thr = logf(score_thr / (1.f - score_thr));
+  int off = 0;
   for (int l = 0; l < num_levels; ++l) {
     lt.cls[l] = cls_levels[l];
     lt.reg[l] = reg_levels[l];
     lt.anchor_begin[l] = off;
-    const int hw = level_anchors[l] / 9;
-    const long long pixels = static_cast<long long>(B) * hw;
-    const long long total = pixels * ((9 * K + 7) / 8);
-    long long g = (total + 255) / 256;
-    if (g > num_sms() * 8LL) g = num_sms() * 8LL;
-    collect_kernel<<<static_cast<unsigned>(g < 1 ? 1 : g), 256, 0, stream>>>(
-        static_cast<const __nv_bfloat16*>(cls_levels[l]), pixels, hw, K, ld_cls, off, logit_thr, max_cand, w.count, w.keys);
-    int rc = check_launch("collect_kernel");
-    if (rc) return rc;
     off += level_anchors[l];
   }
   lt.anchor_begin[num_levels] = off;
   if (off != A_total) return set_error(-1, "filter_detections: level anchors sum %d != A_total %d", off, A_total);
-  segments_kernel<<<(B + 63) / 64, 64, 0, stream>>>(w.count, B, max_cand, w.seg_begin, w.seg_end);
-  int rc = check_launch("segments_kernel");
-  if (rc) return rc;
-  size_t cub_bytes = w.cub_bytes;
-  B200_CUDA_OK(cub::DeviceSegmentedRadixSort::SortKeysDescending(w.cub_temp, cub_bytes, w.keys, w.keys_sorted,
-                                                                 B * max_cand, B, w.seg_begin, w.seg_end, 0, 64, stream));
-  g_launch_count.fetch_add(1);
+  auto scan = [&](int mode, int pass) -> int {
+    for (int l = 0; l < num_levels; ++l) {
+      const int hw = level_anchors[l] / 9;
+      const long long pixels = static_cast<long long>(B) * hw;
+      const long long total = pixels * ((9 * K + 7) / 8);
+      long long g = (total + 255) / 256;
+      if (g > num_sms() * 8LL) g = num_sms() * 8LL;
+      const unsigned grid = static_cast<unsigned>(g < 1 ? 1 : g);
+      const __nv_bfloat16* lg = static_cast<const __nv_bfloat16*>(cls_levels[l]);
+      if (mode == 0)
+        det_scan_kernel<0><<<grid, 256, 0, stream>>>(lg, pixels, hw, K, ld_cls, lt.anchor_begin[l], logit_thr, pass, w.prefix,
+                                                     w.hist, w.count, w.keys);
+      else
+        det_scan_kernel<1><<<grid, 256, 0, stream>>>(lg, pixels, hw, K, ld_cls, lt.anchor_begin[l], logit_thr, pass, w.prefix,
+                                                     w.hist, w.count, w.keys);
+      int rc = check_launch("det_scan_kernel");
+      if (rc) return rc;
+    }
+    return 0;
+  };
+  int rc = 0;
+  for (int pass = 0; pass < 4; ++pass) {
+    if ((rc = scan(0, pass))) return rc;
+    det_select_kernel<<<B, 1024, 0, stream>>>(w.hist, w.prefix, w.remaining, pass);
+    if ((rc = check_launch("det_select_kernel"))) return rc;
+  }
+  if ((rc = scan(1, 0))) return rc;
+  det_sort_kernel<<<B, 1024, kNmsCap * 8, stream>>>(w.keys, w.count, w.keys_sorted);
+  if ((rc = check_launch("det_sort_kernel"))) return rc;
   dim3 dgrid((kNmsCap + 255) / 256, B);
   decode_kernel<<<dgrid, 256, 0, stream>>>(w.keys_sorted, w.count, max_cand, K, lt, ld_reg, anchors, img_h, img_w,
                                            w.boxes, w.scores, w.labels);

@@ -241,3 +241,35 @@ def test_filter_detections_levels():
         same = sum(1 for g_, w_ in zip(got, want) if g_[:2] == w_[:2] and max(abs(a - c) for a, c in zip(g_[2:], w_[2:])) < 0.2)
         assert same >= k - 2, f"{k - same} of {k} detections differ"
 
+
+
+def test_filter_detections_is_deterministic_past_the_nms_cap():
+    """Far more candidates than the 8192 the bitmask NMS takes per image (an untrained network): the selection is an
+    exact top-k on (score, anchor id), so two runs give identical outputs, every kept score is >= the 8192nd best
+    score of the image, and the best candidate of the image always survives."""
+    K = 80
+    H, W = 256, 320
+    shapes = A.guess_shapes((H, W))
+    anchors = A.anchors_for_shape((H, W)).to(DEV)
+    torch.manual_seed(1)
+    B = 2
+    cls_l, reg_l = [], []
+    for (h, w) in shapes:
+        lg = (torch.randn(B, h, w, 9 * K, device=DEV) * 1.0 - 1.5).to(torch.bfloat16)      # ~10 % above the threshold
+        rg = torch.zeros(B, h, w, 40, device=DEV, dtype=torch.bfloat16)
+        rg[..., :36] = (torch.randn(B, h, w, 36, device=DEV) * 0.3).to(torch.bfloat16)
+        cls_l.append(lg); reg_l.append(rg)
+    logits = torch.cat([t.float().reshape(B, -1) for t in cls_l], dim=1)
+    probs = torch.sigmoid(logits)
+    assert int((probs[0] > 0.05).sum()) > 3 * 8192
+    runs = [native.filter_detections_levels(cls_l, reg_l, K, anchors, (H, W)) for _ in range(3)]
+    torch.cuda.synchronize()
+    for r in runs[1:]:
+        for a, b in zip(runs[0], r):
+            assert torch.equal(a, b), "filter_detections is not run-to-run deterministic"
+    boxes, scores, labels = runs[0]
+    for b in range(B):
+        kth = torch.topk(probs[b], 8192).values[-1].item()
+        kept = scores[b][labels[b] >= 0]
+        assert kept.numel() == 300 and float(kept.min()) >= kth - 1e-6
+        assert abs(float(kept.max()) - float(probs[b].max())) < 1e-6
