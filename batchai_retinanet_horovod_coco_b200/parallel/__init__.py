@@ -42,10 +42,18 @@ class Compression:
             return t
 
     class fp16:
+        """Half-width wire.  CUDA tensors: the peers' slices really cross NVLink in 16 bits (bf16, same width as
+        Horovod's fp16, wider exponent: ``P2PComm.allreduce_range(half_wire=True)``); the reduction stays fp32.
+        Host tensors travel through shared memory on one node, where there is no wire to narrow: values are rounded
+        to fp16 and back so that results match a compressed run."""
+        half_wire = True
+
         @staticmethod
         def compress(t):
+            if t.is_cuda:
+                return t, None
             if t.dtype in (torch.float32, torch.float64):
-                return t.to(torch.float16).to(torch.float32), t.dtype  # value-rounded; wire stays fp32 on host
+                return t.to(torch.float16).to(torch.float32), t.dtype
             return t, None
 
         @staticmethod
@@ -182,17 +190,115 @@ def _allgather_bytes(b: bytes):
     return res
 
 
+# ---------------------------------------------------------------------------------- GPU tensor fusion
+class _GpuGroup:
+    """Tensors fused into one range of the symmetric bucket; one collective, one completion event."""
+
+    def __init__(self):
+        self.items = []          # (tensor, offset, numel)
+        self.floats = 0
+        self.event = None        # recorded on the comm stream once results are back in the tensors
+        self.average = True
+        self.half = False
+
+
+class _GpuFusion:
+    """Horovod's tensor fusion for CUDA tensors without its memcpy round trip through a host thread:
+    ``allreduce_async_`` copies the tensor into the next free range of the peer-mapped bucket ON A SIDE STREAM (after an
+    event on the producer's stream), and when the fused range reaches the fusion threshold -- or someone waits -- ONE
+    P2P kernel reduces it and the results are copied back, all on the side stream, so collectives overlap whatever
+    the caller keeps launching (backward).  Every rank must enqueue the same tensors in the same order (autograd hooks
+    of identical models do); there is no negotiation on this path."""
+
+    def __init__(self, comm):
+        self.comm = comm
+        self.stream = torch.cuda.Stream(device=comm.device)
+        self.threshold = int(os.environ.get("HOROVOD_FUSION_THRESHOLD", os.environ.get("B200RT_FUSION_THRESHOLD", 64 << 20))) // 4
+        self.threshold = max(1024, min(self.threshold, comm.bucket_elems))
+        self.open = None
+        self.done_prev = None    # the bucket is one buffer: the next group starts after the previous one finished
+
+    def add(self, tensor, average, half):
+        n = tensor.numel()
+        n4 = (n + 3) // 4 * 4
+        if n4 > self.comm.bucket_elems:
+            raise ValueError(f"tensor of {n} elements exceeds the P2P bucket ({self.comm.bucket_elems}); "
+                             "create the communicator with a larger bucket_floats")
+        g = self.open
+        if g is not None and (g.floats + n4 > self.threshold or g.average != average or g.half != half):
+            self.flush()
+            g = None
+        if g is None:
+            g = self.open = _GpuGroup()
+            g.average, g.half = average, half
+            if self.done_prev is not None:
+                self.stream.wait_event(self.done_prev)
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(tensor.device))
+        self.stream.wait_event(ready)
+        with torch.cuda.stream(self.stream):
+            self.comm.bucket[g.floats:g.floats + n].copy_(tensor.reshape(-1), non_blocking=True)
+            if n4 > n:
+                self.comm.bucket[g.floats + n:g.floats + n4].zero_()
+        g.items.append((tensor, g.floats, n))
+        g.floats += n4
+        return g
+
+    def flush(self):
+        g, self.open = self.open, None
+        if g is None or g.event is not None:
+            return
+        with torch.cuda.stream(self.stream):
+            self.comm.allreduce_range(0, g.floats, g.average, half_wire=g.half)
+            for t, off, n in g.items:
+                t.reshape(-1).copy_(self.comm.result[off:off + n], non_blocking=True)
+            g.event = torch.cuda.Event()
+            g.event.record(self.stream)
+        self.done_prev = g.event
+
+
+class _GpuHandle:
+    def __init__(self, fusion, group, tensor):
+        self.f, self.g, self.result = fusion, group, tensor
+
+    def poll(self) -> bool:
+        if self.g.event is None:
+            self.f.flush()
+        return self.g.event.query()
+
+    def wait(self):
+        """Make the result visible to the CURRENT stream (no host sync), like a stream-ordered Horovod handle."""
+        if self.g.event is None:
+            self.f.flush()
+        torch.cuda.current_stream(self.result.device).wait_event(self.g.event)
+        return self.result
+
+
+def _gpu_fusion(device):
+    comm = p2p_comm(device)
+    if _state.get("gpu_fusion") is None or _state["gpu_fusion"].comm is not comm:
+        _state["gpu_fusion"] = _GpuFusion(comm)
+    return _state["gpu_fusion"]
+
+
 # ---------------------------------------------------------------------------------- collectives
-def allreduce_async_(tensor: torch.Tensor, average: bool = True, name: str | None = None):
-    """In-place asynchronous allreduce.  Returns a handle with ``.wait()``."""
+def allreduce_async_(tensor: torch.Tensor, average: bool = True, name: str | None = None, compression=None):
+    """In-place asynchronous allreduce.  Returns a handle with ``.wait()`` / ``.poll()``.  CUDA fp32 tensors go
+    through the fused P2P path (``_GpuFusion``); ``compression=Compression.fp16`` halves their wire."""
     _need()
     name = name or _auto_name("allreduce")
     if tensor.is_cuda:
-        comm = p2p_comm(tensor.device)
-        t32 = tensor if tensor.dtype == torch.float32 else tensor.float()
-        comm.allreduce_sum_(t32, average=average)
-        if t32 is not tensor:
-            tensor.copy_(t32)
+        if size() == 1:
+            return _Done(tensor)
+        half = bool(getattr(compression, "half_wire", False))
+        if tensor.dtype == torch.float32 and tensor.is_contiguous():
+            f = _gpu_fusion(tensor.device)
+            return _GpuHandle(f, f.add(tensor, average, half), tensor)
+        t32 = tensor.float().contiguous()
+        f = _gpu_fusion(tensor.device)
+        h = _GpuHandle(f, f.add(t32, average, half), t32)
+        h.wait()
+        tensor.copy_(t32)
         return _Done(tensor)
     if not tensor.is_contiguous():
         raise ValueError("allreduce_ needs a contiguous tensor")
@@ -217,7 +323,7 @@ def allreduce_(tensor, average=True, name=None):
 
 def allreduce(tensor, average=True, name=None, compression=Compression.none):
     t, ctx = compression.compress(tensor.detach().clone().contiguous())
-    allreduce_(t, average, name)
+    allreduce_async_(t, average, name, compression=compression).wait()
     return compression.decompress(t, ctx)
 
 

@@ -106,11 +106,14 @@ class DistributedOptimizer:
       allreduce as soon as autograd produces it (overlapping backward), ``step()`` waits for them.
     """
 
-    def __init__(self, optimizer, named_parameters=None, average: bool = True):
+    def __init__(self, optimizer, named_parameters=None, average: bool = True, compression=None):
         from . import allreduce_async_, is_initialized, size
         self._optimizer = optimizer
         self._average = average
-        self._allreduce_async_ = allreduce_async_
+        if compression is None:
+            self._allreduce_async_ = allreduce_async_
+        else:       # hvd.Compression.fp16: CUDA gradients cross NVLink in 16 bits
+            self._allreduce_async_ = lambda t, avg, name=None: allreduce_async_(t, avg, name=name, compression=compression)
         self._size = size if is_initialized() else (lambda: 1)
         params = [p for g in optimizer.param_groups for p in g["params"]]
         if named_parameters is not None:

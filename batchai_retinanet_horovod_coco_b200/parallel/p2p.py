@@ -301,6 +301,25 @@ class P2PComm:
         a = self._args(self.result, 0, n4, 1.0 / self.world, prescale, 0, push=True)
         native.ar_reduce_staged(a)
 
+    def allreduce_range(self, offset: int, n: int, average: bool, half_wire: bool = False):
+        """result[offset:offset+n] = sum (or mean) over ranks of bucket[offset:offset+n], launched on the current
+        stream.  ``half_wire``: the peers' slices cross NVLink as bf16 (scatter + staged reduce), which is what
+        ``hvd.Compression.fp16`` selects for CUDA tensors; otherwise the auto-chosen fused kernel."""
+        n4 = (n + 3) // 4 * 4
+        post = (1.0 / self.world) if average else 1.0
+        if half_wire and self.can_stage():
+            a = self._args(self.result, offset, n4, post, False, 0, push=True, advance=False)
+            a.wire_bf16 = 1
+            native.ar_scatter(a, 0, n4)
+            a = self._args(self.result, offset, n4, post, False, 0, push=True)
+            a.wire_bf16 = 1
+            native.ar_reduce_staged(a)
+            return
+        a = self._args(self.result, offset, n4, post, False, 0, push=True)
+        self._before_collective()
+        native.allreduce_host(a)
+        self._after_collective()
+
     def allreduce_sum_(self, t: torch.Tensor, average: bool = False):
         """Generic in-place allreduce of an arbitrary fp32 CUDA tensor, staged through the bucket."""
         flat = t.reshape(-1)

@@ -49,3 +49,13 @@ def test_single_process_towers():
 def test_flag_barrier_times_out_when_a_rank_is_missing():
     out = _run("barrier_timeout.py", 2, timeout=180)
     assert "TIMEOUT_OK" in out
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+def test_horovod_style_api_on_cuda_tensors():
+    """DistributedOptimizer over torch.optim.SGD, fused async GPU allreduce, Compression.fp16 (reference train.py:103)."""
+    cmd = [sys.executable, "-m", "batchai_retinanet_horovod_coco_b200.parallel.launcher", "-np", "2", sys.executable,
+           os.path.join(ROOT, "tests", "multi", "hvd_gpu.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("HVD_GPU_OK") == 2
