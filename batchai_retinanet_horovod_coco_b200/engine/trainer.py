@@ -134,6 +134,9 @@ class NativeTrainer:
         self._prof = None  # list of (name, cuda event) when profiling
         self._comm_prof = None   # [(lo, hi, start event, end event)] of the scatter pieces when tracing
         self._nvtx = os.environ.get("B200_NVTX", "0") == "1"
+        # the store-warp column sums merge per-CTA partials with atomics: the deterministic mode uses the ordered
+        # column-sum kernel instead
+        self._fused_bias = not native.deterministic()
         self.mean_t = torch.tensor(CAFFE_MEAN_BGR, device=self.device)
         if distributed and comm is None:
             from ..parallel.p2p import P2PComm
@@ -440,10 +443,12 @@ class NativeTrainer:
         ph, pw, _, _ = c.pads(h, w)
         native.wgrad_raw(list(zip(xs, dys)), c.wview(self.G), c.cin, xs[0].shape[-1], c.cout, dys[0].shape[-1], c.kh,
                          c.kw, c.stride, ph, pw, rowscale=c.scale,
-                         dbias=c.bview(self.G) if (c.has_bias and dbias) else None)
+                         dbias=c.bview(self.G) if (c.has_bias and (dbias or not self._fused_bias)) else None)
 
     def _bias_grad(self, c: Conv):
-        return c.bview(self.G) if (c.has_bias and c.trainable) else None
+        """Target of the fused column sums, or None (then ``_wgrad(..., dbias=False)`` must not be used: see
+        ``_fused_bias``)."""
+        return c.bview(self.G) if (c.has_bias and c.trainable and self._fused_bias) else None
 
     # ------------------------------------------------------------------ forward
     def _forward(self, p, images_u8, img_hw=None):

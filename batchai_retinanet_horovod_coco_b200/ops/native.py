@@ -113,6 +113,11 @@ def _ptr(t) -> C.c_void_p:
     return C.c_void_p(0 if t is None else t.data_ptr())
 
 
+def deterministic() -> bool:
+    """B200_DETERMINISTIC=1 at load time: bit-reproducible (slow) accumulation order in every kernel."""
+    return bool(_load().b200_deterministic())
+
+
 def launch_count() -> int:
     return int(_load().b200_launch_count())
 

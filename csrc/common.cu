@@ -65,6 +65,15 @@ bool pdl_enabled() {
   return on == 1;
 }
 
+bool deterministic() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("B200_DETERMINISTIC");
+    on = (e && e[0] == '1') ? 1 : 0;
+  }
+  return on == 1;
+}
+
 static unsigned long long device_bit() {
   int dev = 0;
   cudaGetDevice(&dev);
@@ -77,7 +86,8 @@ void device_setup_done(std::atomic<unsigned long long>& mask) { mask.fetch_or(de
 
 extern "C" {
 const char* b200_last_error(void) { return b200::g_last_error; }
-int b200_ops_abi_version(void) { return 1; }
+int b200_ops_abi_version(void) { return 2; }
+int b200_deterministic(void) { return b200::deterministic() ? 1 : 0; }
 long long b200_launch_count(void) { return b200::g_launch_count.load(); }
 void b200_reset_launch_count(void) { b200::g_launch_count.store(0); }
 /* Kernels executed by replaying a captured CUDA graph never pass through the launch wrappers: the owner of the

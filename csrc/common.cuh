@@ -53,6 +53,10 @@ int num_sms();
 //   if (device_needs_setup(done)) { ...cudaFuncSetAttribute...; device_setup_done(done); }
 // Launch with the programmatic-dependent-launch attribute (see pdl_wait in ptx_sm100.cuh); B200_PDL=0 turns it off.
 bool pdl_enabled();
+// B200_DETERMINISTIC=1: every floating-point accumulation that is normally split over CTAs and merged with atomics
+// (weight gradients, bias column sums, the stem filter gradient, sum of squares, loss sums) runs in ONE CTA per output
+// element instead, so two runs from the same state are bit-identical.  Slow; meant for tests and debugging.
+bool deterministic();
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                               Args&&... args) {

@@ -314,6 +314,16 @@ __global__ void __launch_bounds__(256) colsum_kernel(ColsumArgs a, int cols, int
   }
 }
 
+// deterministic variant: one thread per column walks every row of every matrix in order
+__global__ void colsum_det_kernel(ColsumArgs a, int cols, int ld, float* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float acc = 0.f;
+  for (int pi = 0; pi < a.n; ++pi)
+    for (long long r = 0; r < a.rows[pi]; ++r) acc += __bfloat162float(a.x[pi][r * ld + c]);
+  out[c] += acc;
+}
+
 // ------------------------------------------------------------------ image normalise + pad
 __global__ void preprocess_kernel(const uint8_t* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long pixels,
                                   int H, int W, int C, int ldc, float m0, float m1, float m2, float m3,
@@ -536,6 +546,10 @@ int b200_colsum_multi(const void* const* xs, const long long* rows, int n, int c
   a.block_begin[5] = blocks;
   a.n = n;
   if (blocks == 0) return 0;
+  if (deterministic()) {
+    colsum_det_kernel<<<(cols + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(a, cols, ld, out_accum);
+    return check_launch("colsum_det");
+  }
   dim3 grid(static_cast<unsigned>(blocks), (cols + 255) / 256);
   launch_pdl(colsum_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream), a, cols, ld, out_accum);
   return check_launch("colsum");

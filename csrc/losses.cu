@@ -285,7 +285,7 @@ int b200_focal_loss(const void* logits, void* dlogits, int B, int A_l, int K, in
   const int HW = A_l / 9;
   const long long pixels = static_cast<long long>(B) * HW;
   const long long total = pixels * ((9 * K + 7) / 8);
-  focal_kernel<<<grid_cap(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  focal_kernel<<<deterministic() ? 1 : grid_cap(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(logits), static_cast<__nv_bfloat16*>(dlogits), pixels, HW, K, ld, state, cls,
       A_total, a_off, num_pos, alpha, gamma, loss_scale, loss_accum);
   return check_launch("focal_kernel");
@@ -296,7 +296,7 @@ int b200_smooth_l1(const void* pred, void* dpred, int B, int A_l, int ld, const 
                    void* stream) {
   if (A_l % 9 || ld % 4 || ld < 36) return set_error(-1, "smooth_l1: bad layout");
   const long long total = static_cast<long long>(B) * A_l;
-  smooth_l1_kernel<<<grid_cap(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  smooth_l1_kernel<<<deterministic() ? 1 : grid_cap(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(pred), static_cast<__nv_bfloat16*>(dpred), total, A_l / 9, ld, state,
       reg_target, A_total, a_off, num_pos, sigma * sigma, loss_scale, loss_accum);
   return check_launch("smooth_l1_kernel");

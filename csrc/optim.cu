@@ -87,6 +87,7 @@ int b200_sumsq(const float* x, long long n, float* out, void* stream) {
   const long long cap = static_cast<long long>(num_sms()) * 8;
   if (g > cap) g = cap;
   if (g < 1) g = 1;
+  if (deterministic()) g = 1;
   sumsq_kernel<<<static_cast<unsigned>(g), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, n, out);
   return check_launch("sumsq_kernel");
 }

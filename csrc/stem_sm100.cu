@@ -455,7 +455,7 @@ extern "C" int b200_stem_wgrad(const void* x, const void* dy, const float* scale
   const unsigned int box[4] = {64u, 16u, 4u, 1u};
   int rc = make_tmap_bf16(&p.dy_map, dy, 4, dims, strides, box);
   if (rc) return rc;
-  const int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
+  const int grid = deterministic() ? 1 : (p.total_tiles < num_sms() ? p.total_tiles : num_sms());
   stem_wgrad_kernel<<<grid, kSwThreads, kSwSmem, static_cast<cudaStream_t>(stream)>>>(p);
   return check_launch("stem_wgrad_kernel");
 }

@@ -360,6 +360,7 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
   const long long max_ks = (p.num_pixel_tiles + 7) / 8;
   if (ks > max_ks) ks = max_ks;
   if (ks < 1) ks = 1;
+  if (deterministic()) ks = 1;          // one CTA per output block: no cross-CTA atomic order
   p.chunk = static_cast<int>((p.num_pixel_tiles + ks - 1) / ks);
   p.ksplit = (p.num_pixel_tiles + p.chunk - 1) / p.chunk;
   const long long grid = units * p.ksplit;

@@ -19,6 +19,8 @@ extern "C" {
 
 const char* b200_last_error(void);
 int b200_ops_abi_version(void);
+/* 1 when B200_DETERMINISTIC=1 was set at load time: split accumulations run in one CTA per output (bit-reproducible). */
+int b200_deterministic(void);
 /* Number of kernel launches issued by this library in this process (bench.py gpu_launches). */
 long long b200_launch_count(void);
 void b200_reset_launch_count(void);

@@ -192,3 +192,13 @@ def test_async_step_handle_returns_the_same_loss_early():
     h2 = nt.train_step_async(*batch)
     assert torch.equal(h1.loss_cpu(), h1.loss.cpu())         # stale handle: falls back to its own device tensor
     assert torch.equal(h2.loss_cpu(), h2.loss.cpu())
+
+
+def test_deterministic_mode_gives_bit_identical_trajectories():
+    """B200_DETERMINISTIC=1 (read when the library loads, hence a subprocess): six optimisation steps, eager twice and
+    with CUDA-graph replay, must end in bit-identical parameters and losses."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "workers", "deterministic_run.py")],
+                       capture_output=True, text=True, timeout=600, cwd=root, env=dict(os.environ, B200_DETERMINISTIC="1"))
+    assert r.returncode == 0 and "DETERMINISTIC_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
