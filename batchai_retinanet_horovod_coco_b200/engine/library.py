@@ -38,14 +38,15 @@ def assign_targets_batched(anchors: torch.Tensor, gt: torch.Tensor, gt_count: to
     valid = torch.arange(G, device=gt.device).view(1, 1, G) < gt_count.view(B, 1, 1)
     iou = torch.where(valid, iou, torch.full_like(iou, -1.0))
     best, idx = iou.max(dim=2)
-    state = torch.full((B, A), -1, dtype=torch.int8, device=gt.device)
-    state[best < neg_thr] = 0
-    state[best >= pos_thr] = 1
-    state[(gt_count == 0).view(B, 1).expand(B, A)] = 0
+    # torch.where throughout (no boolean-mask indexing): no host sync, so the step can be captured in a CUDA graph
+    m1 = torch.full((B, A), -1, dtype=torch.int8, device=gt.device)
+    state = torch.where(best < neg_thr, torch.zeros_like(m1), m1)
+    state = torch.where(best >= pos_thr, torch.ones_like(m1), state)
+    state = torch.where((gt_count == 0).view(B, 1), torch.zeros_like(m1), state)
     cx = (anchors[:, 0] + anchors[:, 2]) / 2
     cy = (anchors[:, 1] + anchors[:, 3]) / 2
     outside = (cx.view(1, A) >= img_hw[:, 1].view(B, 1)) | (cy.view(1, A) >= img_hw[:, 0].view(B, 1))
-    state[outside] = -1
+    state = torch.where(outside, m1, state)
     matched = torch.gather(gt, 1, idx.unsqueeze(-1).expand(B, A, 5))
     aw = (anchors[:, 2] - anchors[:, 0]).view(1, A)
     ah = (anchors[:, 3] - anchors[:, 1]).view(1, A)
@@ -59,8 +60,15 @@ class LibraryTrainer:
 
     def __init__(self, backbone: str = "resnet50", num_classes: int = 80, device="cuda", dtype=torch.bfloat16,
                  lr: float = 1e-5, clipnorm: float = 0.001, distributed: bool = False, model: RetinaNet | None = None,
-                 freeze_backbone: bool = False):
+                 freeze_backbone: bool = False, use_graph: bool | None = None):
         self.device = torch.device(device)
+        # single-process CUDA runs replay the whole step (forward, losses, backward, clip, fused Adam) as ONE CUDA graph
+        # after three eager steps per input shape: the baseline should not lose to launch overhead what it does not
+        # lose to its kernels
+        if use_graph is None:
+            use_graph = torch.device(device).type == "cuda" and not distributed
+        self.use_graph = bool(use_graph)
+        self._graphs = {}
         self.dtype = dtype
         self.num_classes = num_classes
         self.clipnorm = clipnorm
@@ -76,7 +84,7 @@ class LibraryTrainer:
             ids = [self.device.index] if self.device.type == "cuda" else None
             self.train_model = DDP(self.model, device_ids=ids, bucket_cap_mb=64, gradient_as_bucket_view=True)
         params = [p for p in self.model.parameters() if p.requires_grad]
-        kw = {"fused": True} if self.device.type == "cuda" else {}
+        kw = {"fused": True, "capturable": True} if self.device.type == "cuda" else {}
         self.opt = torch.optim.Adam(params, lr=lr, betas=(0.9, 0.999), eps=1e-7, **kw)
         self.mean = torch.tensor(CAFFE_MEAN_BGR, device=self.device).view(1, 3, 1, 1)
         self._anchors = {}
@@ -103,15 +111,50 @@ class LibraryTrainer:
         return lc + lr_, lc, lr_
 
     def train_step(self, images_u8, gt, gt_count, img_hw):
+        if self.use_graph:
+            return self._graph_step(images_u8, gt, gt_count, img_hw)
+        return self._eager_step(images_u8, gt, gt_count, img_hw, set_to_none=True)
+
+    def _graph_step(self, images_u8, gt, gt_count, img_hw):
+        key = (tuple(images_u8.shape), tuple(gt.shape))
+        st = self._graphs.get(key)
+        if st is None:
+            st = self._graphs[key] = {"warm": 0}
+        if "graph" not in st:
+            st["warm"] += 1
+            if st["warm"] <= 3:
+                return self._eager_step(images_u8, gt, gt_count, img_hw, set_to_none=False)
+            dev = self.device
+            st["in"] = [torch.empty_like(t, device=dev) for t in (images_u8, gt, gt_count, img_hw)]
+            for d, t in zip(st["in"], (images_u8, gt, gt_count, img_hw)):
+                d.copy_(t, non_blocking=True)
+            torch.cuda.synchronize(dev)
+            g = torch.cuda.CUDAGraph()
+            try:
+                with torch.cuda.graph(g):
+                    st["out"] = self._eager_step(*st["in"], set_to_none=False)
+                st["graph"] = g
+            except Exception as e:  # noqa: BLE001 - capture is an optimisation of the baseline
+                import warnings
+                warnings.warn(f"library baseline: CUDA-graph capture failed ({e}); staying eager")
+                self.use_graph = False
+                return self._eager_step(images_u8, gt, gt_count, img_hw, set_to_none=True)
+        for d, t in zip(st["in"], (images_u8, gt, gt_count, img_hw)):
+            d.copy_(t, non_blocking=True)
+        st["graph"].replay()
+        return st["out"].clone()
+
+    def _eager_step(self, images_u8, gt, gt_count, img_hw, set_to_none=True):
         dev = self.device
         images_u8 = images_u8.to(dev, non_blocking=True)
         gt = gt.to(dev, non_blocking=True)
         gt_count = gt_count.to(dev, non_blocking=True)
         img_hw = img_hw.to(dev, non_blocking=True)
-        self.opt.zero_grad(set_to_none=True)
+        self.opt.zero_grad(set_to_none=set_to_none)
         total, lc, lr_ = self.loss(images_u8, gt, gt_count, img_hw)
         total.backward()
         if self.clipnorm:
-            torch.nn.utils.clip_grad_norm_([p for p in self.model.parameters() if p.requires_grad], self.clipnorm)
+            torch.nn.utils.clip_grad_norm_([p for p in self.model.parameters() if p.requires_grad], self.clipnorm,
+                                           foreach=True if self.device.type == "cuda" else None)
         self.opt.step()
         return torch.stack([total.detach(), lr_.detach(), lc.detach()])

@@ -43,6 +43,9 @@ def parse():
     ap.add_argument("--classes", type=int, default=80)
     ap.add_argument("--boxes", type=int, default=12, help="synthetic GT boxes per image")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--with-library", action="store_true",
+                    help="also time the library stand-in (PyTorch + cuDNN, CUDA-graphed on 1 GPU, DDP/NCCL on N) in the "
+                         "same process on the same box and report value / library as vs_library")
     return ap.parse_args()
 
 
@@ -217,6 +220,20 @@ def main():
         else:
             replicas_equal = True
 
+    library = None
+    if args.with_library and args.impl == "b200":
+        from batchai_retinanet_horovod_coco_b200.engine.library import LibraryTrainer
+        del trainer
+        torch.cuda.empty_cache()
+        trainer = LibraryTrainer(args.backbone, args.classes, device=dev, distributed=world > 1)
+        step_async = None
+        lsteps = max(5, args.steps // 4)
+        run(6, dev_sets, False)
+        ms_l, _ = timed(lsteps, dev_sets, False)
+        library = {"value": args.batch * world * lsteps / (ms_l / 1e3), "ms_per_step": ms_l / lsteps, "steps": lsteps,
+                   "what": "same model in PyTorch (cuDNN bf16 autocast, channels-last, fused capturable Adam, whole-step "
+                           "CUDA graph on 1 GPU / DDP+NCCL on N); same box, same process"}
+
     if rank == 0:
         value = args.batch * world * args.steps / (ms / 1e3)
         line = {
@@ -230,6 +247,7 @@ def main():
                        "l2_policy": "inputs+activations per step (>2 GB) exceed the 126 MB L2; 4 rotating input sets"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "loss": loss_val,
             "replicas_equal": replicas_equal,
+            "library": library, "vs_library": (value / library["value"]) if library else None,
         }
         print(json.dumps(line))
     if world > 1:
