@@ -243,6 +243,10 @@ def parse_args(args):
     parser.add_argument("--cpu", help="(extension) force the CPU spec engine.", action="store_true")
     parser.add_argument("--workers", help="(extension) background threads producing batches (Keras fit_generator "
                         "uses 1); 0 loads in the training thread.", type=int, default=min(8, os.cpu_count() or 1))
+    parser.add_argument("--host-augment", dest="gpu_augment", action="store_false",
+                        help="(extension) warp / resize images on the host with OpenCV like the reference; by default, "
+                             "on a GPU, workers only decode and the warp + resize run as CUDA kernels with the same "
+                             "fixed-point arithmetic.")
     parser.add_argument("--max-queue-size", help="(extension) batches kept ready ahead of the training step "
                         "(Keras default 10).", type=int, default=10)
     parser.add_argument("--engine", help="(extension) auto | native | spec", default="auto")
@@ -254,7 +258,7 @@ def parse_args(args):
 
 
 def fit_generator(trainer, generator, steps_per_epoch, epochs, callbacks, initial_epoch=0, verbose=1, workers=1,
-                  max_queue_size=10):
+                  max_queue_size=10, gpu_augment=False):
     """Keras ``fit_generator`` over the compact batches (reference train.py:444-450): batches are produced ahead of
     the training step by ``workers`` background threads into a queue of ``max_queue_size`` (Keras defaults 1 / 10)."""
     from ..preprocessing.prefetch import BatchPrefetcher
@@ -266,7 +270,11 @@ def fit_generator(trainer, generator, steps_per_epoch, epochs, callbacks, initia
     history = []
     cl.on_train_begin({})
     pin = trainer.device.type == "cuda"
-    batches = BatchPrefetcher(generator, workers=workers, max_queue_size=max_queue_size, pin=pin)
+    assembler = None
+    if gpu_augment and pin and hasattr(generator, "next_raw"):
+        from ..preprocessing.gpu_batch import GpuBatchAssembler
+        assembler = GpuBatchAssembler(trainer.device, pad_bgr=trainer._pad_bgr() if hasattr(trainer, "_pad_bgr") else (104, 117, 124))
+    batches = BatchPrefetcher(generator, workers=workers, max_queue_size=max_queue_size, pin=pin, assembler=assembler)
     for epoch in range(initial_epoch, epochs):
         cl.on_epoch_begin(epoch, {})
         sums = torch.zeros(3, device=trainer.device)
@@ -339,7 +347,7 @@ def main(args=None):
     callbacks = create_callbacks(model, model, prediction_model, validation_generator, args)
     history = fit_generator(trainer, train_generator, steps_per_epoch=args.steps, epochs=args.epochs, callbacks=callbacks,
                             initial_epoch=initial_epoch, verbose=1, workers=args.workers,
-                            max_queue_size=args.max_queue_size)
+                            max_queue_size=args.max_queue_size, gpu_augment=args.gpu_augment)
     if args.timeline:
         hvd.timeline_stop()
     return history

@@ -900,9 +900,10 @@ class NativeTrainer:
             torch.cuda.synchronize(self.device)
             k0 = native.launch_count()
             ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-            with torch.cuda.graph(ga):
+            # thread_local: prefetch workers keep allocating / launching on their own streams while this thread captures
+            with torch.cuda.graph(ga, capture_error_mode="thread_local"):
                 self._step_front(p, p["in_img"], p["in_gt"], p["in_cnt"], p["in_hw"])
-            with torch.cuda.graph(gb):
+            with torch.cuda.graph(gb, capture_error_mode="thread_local"):
                 self._step_back(p)
             p["graph_kernels"] = native.launch_count() - k0     # capture counted them once: that is the first replay
         except Exception as e:  # noqa: BLE001 - capture is an optimisation: fall back to eager launches

@@ -292,6 +292,40 @@ def generate_anchors(out, H, W, stride, size):
     _check(_load().b200_generate_anchors(_ptr(out), H, W, stride, C.c_float(size), _stream()), "generate_anchors")
 
 
+def resize_linear_u8(src, dst, scale_x: float, scale_y: float):
+    """src uint8 [sh, sw, 3] (device, row pitch = stride(0)) -> dst uint8 view [dh, dw, 3] (e.g. a slot of the batch
+    tensor).  scale_* = source pixels per destination pixel (1 / fx of cv2.resize)."""
+    _check(_load().b200_resize_linear_u8(_ptr(src), src.shape[0], src.shape[1], C.c_longlong(src.stride(0)), _ptr(dst),
+                                         dst.shape[0], dst.shape[1], C.c_longlong(dst.stride(0)), C.c_double(scale_x),
+                                         C.c_double(scale_y), _stream()), "resize_linear_u8")
+
+
+def invert_affine_like_cv2(m2x3):
+    """The dst -> src map cv2.warpAffine derives from the forward matrix it is given (same float64 operations)."""
+    import numpy as np
+    M = np.asarray(m2x3, dtype=np.float64).reshape(2, 3).copy()
+    D = M[0, 0] * M[1, 1] - M[0, 1] * M[1, 0]
+    D = 1.0 / D if D != 0 else 0.0
+    A11, A22 = M[1, 1] * D, M[0, 0] * D
+    M[0, 0] = A11
+    M[0, 1] *= -D
+    M[1, 0] *= -D
+    M[1, 1] = A22
+    b1 = -M[0, 0] * M[0, 2] - M[0, 1] * M[1, 2]
+    b2 = -M[1, 0] * M[0, 2] - M[1, 1] * M[1, 2]
+    M[0, 2], M[1, 2] = b1, b2
+    return M
+
+
+def warp_affine_u8(src, dst, forward_2x3, border_replicate: bool = True, cval: int = 0):
+    """cv2.warpAffine(src, forward_2x3, (dw, dh), INTER_LINEAR, BORDER_REPLICATE | BORDER_CONSTANT) on the device."""
+    inv = invert_affine_like_cv2(forward_2x3).reshape(-1)
+    arr = (C.c_double * 6)(*[float(v) for v in inv])
+    _check(_load().b200_warp_affine_u8(_ptr(src), src.shape[0], src.shape[1], C.c_longlong(src.stride(0)), _ptr(dst),
+                                       dst.shape[0], dst.shape[1], C.c_longlong(dst.stride(0)), arr,
+                                       int(border_replicate), int(cval), _stream()), "warp_affine_u8")
+
+
 def anchors_for_shape_gpu(feature_shapes, device) -> torch.Tensor:
     from .anchors import SIZES, STRIDES
     total = sum(h * w * 9 for h, w in feature_shapes)

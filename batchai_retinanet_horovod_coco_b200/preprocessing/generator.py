@@ -26,7 +26,8 @@ import numpy as np
 import torch
 
 from ..ops.anchors import anchor_targets_bbox, anchors_for_shape
-from ..utils.image import (TransformParameters, adjust_transform_for_image, apply_transform, preprocess_image,
+from ..utils.image import (TransformParameters, adjust_transform_for_image, apply_transform, compute_resize_scale,
+                           preprocess_image,
                            resize_image)
 from ..utils.transform import transform_aabb
 
@@ -171,6 +172,43 @@ class Generator:
     def next(self):
         image_group, annotations_group = self._load_group(self._next_group(), keras_form=True)
         return self.compute_inputs(image_group), self.compute_targets(image_group, annotations_group)
+
+    def next_raw(self):
+        """The batch BEFORE any pixel work: decoded images, augmentation matrices, resize scales, transformed boxes.
+        ``preprocessing.gpu_batch.GpuBatchAssembler`` turns it into the engine's compact batch with the warp and the
+        resize running on the GPU (same OpenCV arithmetic), so worker threads only decode."""
+        group = self._next_group()
+        image_group = self.load_image_group(group)
+        annotations_group = self.load_annotations_group(group)
+        image_group, annotations_group = self.filter_annotations(image_group, annotations_group, group)
+        matrices, out_hw, scales = [], [], []
+        for i, (image, ann) in enumerate(zip(image_group, annotations_group)):
+            ann = ann.copy()
+            m = None
+            if self.transform_generator:
+                with self.lock:
+                    matrix = next(self.transform_generator)
+                m = adjust_transform_for_image(matrix, image, self.transform_parameters.relative_translation)
+                for k in range(ann.shape[0]):
+                    ann[k, :4] = transform_aabb(m, ann[k, :4])
+            scale = compute_resize_scale(image.shape, self.image_min_side, self.image_max_side)
+            # cv2.resize(img, None, fx=scale, fy=scale): dsize = round(size * scale); source step = 1 / scale
+            h, w = int(round(image.shape[0] * scale)), int(round(image.shape[1] * scale))
+            ann[:, :4] *= scale
+            annotations_group[i] = ann
+            matrices.append(m)
+            out_hw.append((h, w))
+            scales.append((1.0 / scale, 1.0 / scale))
+        b = len(image_group)
+        g = max(1, max(a.shape[0] for a in annotations_group))
+        gt = torch.zeros(b, g, 5)
+        cnt = torch.zeros(b, dtype=torch.int32)
+        for i, a in enumerate(annotations_group):
+            gt[i, :a.shape[0]] = torch.from_numpy(a.astype(np.float32))
+            cnt[i] = a.shape[0]
+        tp = self.transform_parameters
+        return {"images": image_group, "matrices": matrices, "out_hw": out_hw, "scales": scales, "gt": gt, "count": cnt,
+                "border_replicate": tp.fill_mode == "nearest", "cval": int(tp.cval)}
 
     def next_compact(self, pin: bool = False):
         image_group, annotations_group = self._load_group(self._next_group(), keras_form=False)

@@ -20,9 +20,13 @@ class BatchPrefetcher:
 
     _STOP = object()
 
-    def __init__(self, generator, workers: int = 4, max_queue_size: int = 10, pin: bool = False):
+    def __init__(self, generator, workers: int = 4, max_queue_size: int = 10, pin: bool = False, assembler=None):
+        """``assembler`` (``preprocessing.gpu_batch.GpuBatchAssembler``): the workers then only DECODE
+        (``generator.next_raw()``; OpenCV's decoder releases the GIL, so threads scale), upload the raw pixels and
+        launch the warp / resize kernels on their own CUDA stream; the consumer only waits for an event."""
         self.generator = generator
         self.pin = pin
+        self.assembler = assembler
         self.workers = max(0, int(workers))
         self._q: "queue.Queue" = queue.Queue(maxsize=max(1, int(max_queue_size)))
         self._stop = threading.Event()
@@ -35,7 +39,10 @@ class BatchPrefetcher:
     def _work(self):
         while not self._stop.is_set():
             try:
-                item = self.generator.next_compact(pin=self.pin)
+                if self.assembler is not None:
+                    item = self.assembler.assemble_async(self.generator.next_raw())
+                else:
+                    item = self.generator.next_compact(pin=self.pin)
             except BaseException as e:  # noqa: BLE001 - handed to the consumer, which re-raises it
                 item = e
             while not self._stop.is_set():
@@ -49,12 +56,14 @@ class BatchPrefetcher:
 
     def next(self):
         if self.workers == 0:                  # synchronous mode: the caller's thread does the work
+            if self.assembler is not None:
+                return self.assembler.assemble(self.generator.next_raw())
             return self.generator.next_compact(pin=self.pin)
         item = self._q.get()
         if isinstance(item, BaseException):
             self.close()
             raise item
-        return item
+        return self.assembler.finish(item) if self.assembler is not None else item
 
     __next__ = next
 

@@ -203,6 +203,16 @@ int b200_nms_sorted_noalloc(const float* boxes, const int* cls_or_null, int n, f
                             void* stream);
 int b200_nms_sorted_noalloc_max(void);
 
+/* ------------------------------------------------------------------ image geometry (real-data path)
+ * uint8 BGR interleaved images, pitches in bytes.  Bilinear resize and affine warp with OpenCV's fixed-point
+ * arithmetic (cv2.resize INTER_LINEAR / cv2.warpAffine INTER_LINEAR), so a batch assembled on the GPU matches the
+ * reference generator's host pipeline to +-1 LSB.  inverse_2x3: the dst -> src map (cv2 inverts the matrix it is
+ * given; pass that inverse).  Replaces: OpenCV resize / warpAffine in keras-retinanet's Generator (G19). */
+int b200_resize_linear_u8(const uint8_t* src, int sh, int sw, long long src_pitch, uint8_t* dst, int dh, int dw,
+                          long long dst_pitch, double scale_x, double scale_y, void* stream);
+int b200_warp_affine_u8(const uint8_t* src, int sh, int sw, long long src_pitch, uint8_t* dst, int dh, int dw,
+                        long long dst_pitch, const double* inverse_2x3, int border_replicate, int cval, void* stream);
+
 /* ------------------------------------------------------------------ peer-to-peer collectives
  * Allreduce over NVLink peer mappings: every rank passes the table of all ranks' bucket
  * pointers (mapped with CUDA IPC) and flag pads (host arrays, copied into kernel params).  Fused: per-rank pre-scale (global-norm clip

@@ -273,3 +273,63 @@ def test_filter_detections_is_deterministic_past_the_nms_cap():
         kept = scores[b][labels[b] >= 0]
         assert kept.numel() == 300 and float(kept.min()) >= kth - 1e-6
         assert abs(float(kept.max()) - float(probs[b].max())) < 1e-6
+
+
+def test_gpu_resize_and_warp_match_opencv():
+    """b200_resize_linear_u8 / b200_warp_affine_u8 vs cv2.resize / cv2.warpAffine (the reference generator's calls):
+    at most 1 LSB apart on every pixel."""
+    import cv2
+    import numpy as np
+    rng = np.random.default_rng(0)
+    img = rng.integers(0, 256, (197, 263, 3), dtype=np.uint8)
+    src = torch.from_numpy(img).to(DEV)
+    for f in (1.37, 0.61, 3.04):
+        want = cv2.resize(img, None, fx=f, fy=f)
+        out = torch.zeros(want.shape, dtype=torch.uint8, device=DEV)
+        native.resize_linear_u8(src, out, 1.0 / f, 1.0 / f)
+        d = (out.cpu().numpy().astype(int) - want.astype(int))
+        assert np.abs(d).max() <= 1, (f, np.abs(d).max())
+    th = 0.08
+    M = np.array([[np.cos(th) * 1.05, -np.sin(th) + 0.03, 4.3], [np.sin(th) + 0.02, np.cos(th) * 0.95, -3.1]])
+    for rep, mode in ((True, cv2.BORDER_REPLICATE), (False, cv2.BORDER_CONSTANT)):
+        want = cv2.warpAffine(img, M, (img.shape[1], img.shape[0]), flags=cv2.INTER_LINEAR, borderMode=mode, borderValue=0)
+        out = torch.zeros_like(src)
+        native.warp_affine_u8(src, out, M, border_replicate=rep, cval=0)
+        d = (out.cpu().numpy().astype(int) - want.astype(int))
+        assert np.abs(d).max() <= 1, (rep, np.abs(d).max())
+
+
+def test_gpu_batch_assembly_matches_the_host_pipeline(tmp_path):
+    """Generator.next_raw() + GpuBatchAssembler == Generator.next_compact() (decode, random transform, resize, pad)."""
+    import cv2
+    import numpy as np
+    from batchai_retinanet_horovod_coco_b200.preprocessing.csv_generator import CSVGenerator
+    from batchai_retinanet_horovod_coco_b200.preprocessing.gpu_batch import GpuBatchAssembler
+    from batchai_retinanet_horovod_coco_b200.utils.transform import random_transform_generator
+    rng = np.random.default_rng(1)
+    rows = []
+    for i, (h, w) in enumerate([(120, 160), (150, 110), (96, 200), (130, 130)]):
+        img = cv2.GaussianBlur(rng.integers(0, 256, (h, w, 3), dtype=np.uint8), (7, 7), 2.0)
+        path = str(tmp_path / f"im{i}.png")
+        cv2.imwrite(path, img)
+        rows.append(f"{path},10,12,{w - 20},{h - 15},thing")
+    (tmp_path / "ann.csv").write_text("\n".join(rows) + "\n")
+    (tmp_path / "cls.csv").write_text("thing,0\n")
+
+    def make():
+        tg = random_transform_generator(min_rotation=-0.1, max_rotation=0.1, min_translation=(-0.1, -0.1),
+                                        max_translation=(0.1, 0.1), min_shear=-0.1, max_shear=0.1, min_scaling=(0.9, 0.9),
+                                        max_scaling=(1.1, 1.1), flip_x_chance=0.5, flip_y_chance=0.5,
+                                        prng=np.random.RandomState(5))
+        return CSVGenerator(str(tmp_path / "ann.csv"), str(tmp_path / "cls.csv"), transform_generator=tg, batch_size=2,
+                            image_min_side=200, image_max_side=300, shuffle_groups=False, seed=3)
+
+    ga, gb = make(), make()
+    asm = GpuBatchAssembler(DEV)
+    for _ in range(2):
+        himg, hgt, hcnt, hhw = ga.next_compact()
+        dimg, dgt, dcnt, dhw = asm.assemble(gb.next_raw())
+        assert tuple(dimg.shape) == tuple(himg.shape) and torch.equal(hhw, dhw) and torch.equal(hcnt, dcnt)
+        assert torch.allclose(hgt, dgt, atol=1e-3)
+        d = (dimg.cpu().int() - himg.int()).abs()
+        assert int(d.max()) <= 2 and float((d > 1).float().mean()) < 1e-3, (int(d.max()), float((d > 1).float().mean()))
