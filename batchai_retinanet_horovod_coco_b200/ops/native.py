@@ -292,6 +292,47 @@ def generate_anchors(out, H, W, stride, size):
     _check(_load().b200_generate_anchors(_ptr(out), H, W, stride, C.c_float(size), _stream()), "generate_anchors")
 
 
+# ------------------------------------------------------------------------------ MobileNet / DenseNet layers
+def dwconv3x3(mode: int, a, b, out, in_hw, out_hw, stride: int, pad):
+    """mode 0: y = dw(x, w); 1: dx = dw^T(dy, w); 2: dw += x (*) dy.  w / dw fp32 [C][9]; in_hw = (H, W) of x."""
+    n, c = (a.shape[0], a.shape[-1])
+    _check(_load().b200_dwconv3x3(mode, _ptr(a), _ptr(b), _ptr(out), n, in_hw[0], in_hw[1], c, out_hw[0], out_hw[1], stride,
+                                  pad[0], pad[1], _stream()), "b200_dwconv3x3")
+
+
+def bn_stats(x, channels, sums, mean, var, moving_mean=None, moving_var=None, momentum=0.99):
+    rows = x.numel() // x.shape[-1]
+    import ctypes
+    _check(_load().b200_bn_stats(_ptr(x), ctypes.c_longlong(rows), int(channels), x.shape[-1], _ptr(sums), _ptr(mean), _ptr(var),
+                                 _ptr(moving_mean), _ptr(moving_var), ctypes.c_float(momentum), _stream()), "b200_bn_stats")
+
+
+def bn_act_fwd(x, mean, var, gamma, beta, eps, y, channels, act):
+    rows = x.numel() // x.shape[-1]
+    _check(_load().b200_bn_act_fwd(_ptr(x), _ptr(mean), _ptr(var), _ptr(gamma), _ptr(beta), C.c_float(eps), _ptr(y),
+                                   C.c_longlong(rows), channels, x.shape[-1], y.shape[-1], act, _stream()), "b200_bn_act_fwd")
+
+
+def bn_act_bwd(x, dy, mean, var, gamma, beta, eps, sums, channels, act, dx, dgamma, dbeta, accumulate=False):
+    rows = x.numel() // x.shape[-1]
+    _check(_load().b200_bn_act_bwd(_ptr(x), _ptr(dy), _ptr(mean), _ptr(var), _ptr(gamma), _ptr(beta), C.c_float(eps), _ptr(sums),
+                                   C.c_longlong(rows), channels, x.shape[-1], dy.shape[-1], dx.shape[-1], act, int(accumulate),
+                                   _ptr(dx), _ptr(dgamma), _ptr(dbeta), _stream()), "b200_bn_act_bwd")
+
+
+def avgpool2(x, y, backward=False):
+    """forward: x [N,H,W,C] -> y [N,H/2,W/2,C]; backward: x = dy [N,H/2,W/2,C] -> y = dx [N,H,W,C]."""
+    big = y if backward else x
+    n, h, w, c = big.shape
+    _check(_load().b200_avgpool2(int(backward), _ptr(x), _ptr(y), n, h, w, c, _stream()), "b200_avgpool2")
+
+
+def wgrad_small(x, dy, dw, cin, cout, kh, kw, stride, pad):
+    n, h, w, ldx = x.shape
+    _check(_load().b200_wgrad_small(_ptr(x), _ptr(dy), _ptr(dw), n, h, w, cin, ldx, dy.shape[1], dy.shape[2], cout,
+                                    dy.shape[-1], kh, kw, stride, pad[0], pad[1], _stream()), "b200_wgrad_small")
+
+
 def resize_linear_u8(src, dst, scale_x: float, scale_y: float):
     """src uint8 [sh, sw, 3] (device, row pitch = stride(0)) -> dst uint8 view [dh, dw, 3] (e.g. a slot of the batch
     tensor).  scale_* = source pixels per destination pixel (1 / fx of cv2.resize)."""

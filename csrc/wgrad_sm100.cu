@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   const int tap0 = tap_group * p.taps_per_unit;
   const int ntaps_here = min(p.taps_per_unit, p.num_taps - tap0);
   // packed B chunks of this unit
-  const int n_chunks = (p.taps_per_unit > 1) ? ntaps_here * p.chunks_per_tap : min(4, (p.Cin - n_tile * 256) >> 6);
+  const int n_chunks = (p.taps_per_unit > 1) ? ntaps_here * p.chunks_per_tap : min(4, (p.Cin - n_tile * 256 + 63) >> 6);
   const int N = n_chunks * 64;
   // A chunks: MT tiles x 2 halves of 64 output channels, loaded only where co < Cout
   const int co_base = m_group * p.mt * 128;
@@ -225,6 +225,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
             float* row = p.dw + (static_cast<long long>(t) * p.Cout + co) * p.Cin + ci + (c & 63);
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
+              if (ci + (c & 63) + j >= p.Cin) break;      // Cin need not fill its last 64-channel chunk (zero-filled by TMA)
               asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(row + j),
                            "f"(__uint_as_float(r[j]) * rs), "f"(__uint_as_float(r[j + 1]) * rs),
                            "f"(__uint_as_float(r[j + 2]) * rs), "f"(__uint_as_float(r[j + 3]) * rs)
@@ -270,7 +271,7 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
   if (a->stride == 2 && a->num_problems > 2) return set_error(-1, "b200_wgrad: at most 2 problems with stride 2");
   if (a->KH * a->KW > kWMaxTaps) return set_error(-1, "b200_wgrad: too many taps");
   if ((a->ldx % 8) || (a->ldy % 8)) return set_error(-1, "b200_wgrad: ld* must be multiples of 8");
-  if (a->Cin % 64) return set_error(-1, "b200_wgrad: Cin must be a multiple of 64");
+  if (a->Cin % 8) return set_error(-1, "b200_wgrad: Cin must be a multiple of 8");
 
   static std::atomic<unsigned long long> attr_set{0};   // per device
   if (device_needs_setup(attr_set)) {
@@ -285,7 +286,7 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
   p.num_problems = a->num_problems;
   p.Cin = a->Cin;
   p.Cout = a->Cout;
-  p.chunks_per_tap = a->Cin >= 256 ? 4 : a->Cin / 64;
+  p.chunks_per_tap = a->Cin >= 256 ? 4 : (a->Cin + 63) / 64;
   p.taps_per_unit = a->Cin >= 256 ? 1 : 4 / p.chunks_per_tap;   // pack taps into N when Cin is small
   p.num_n_tiles = a->Cin >= 256 ? (a->Cin + 255) / 256 : 1;
   p.mt = a->Cout > 128 ? 2 : 1;

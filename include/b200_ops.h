@@ -203,6 +203,29 @@ int b200_nms_sorted_noalloc(const float* boxes, const int* cls_or_null, int n, f
                             void* stream);
 int b200_nms_sorted_noalloc_max(void);
 
+/* ------------------------------------------------------------------ MobileNet / DenseNet layer types
+ * (csrc/mobile_sm100.cu; reachable from the reference through --backbone, train.py:323-324,390).  NHWC bf16.
+ * Depthwise 3x3, TF `same` padding: mode 0 forward (a = x, b = w fp32 [C][9], out = y), 1 input gradient (a = dy, b = w,
+ * out = dx [N,H,W,C]), 2 filter gradient (a = x, b = dy, out = dw fp32 [C][9], accumulated).  H, W: input; OH, OW: output. */
+int b200_dwconv3x3(int mode, const void* a, const void* b, void* out, int N, int H, int W, int C, int OH, int OW, int stride,
+                   int pad_h, int pad_w, void* stream);
+/* Batch statistics of x [rows, C] (channel stride ld): mean, biased variance; optional Keras moving-statistics update
+ * (moving = moving * momentum + batch * (1 - momentum)).  sums2C: zeroed fp32 scratch [2C], left zeroed. */
+int b200_bn_stats(const void* x, long long rows, int C, int ld, float* sums2C, float* mean, float* var, float* moving_mean,
+                  float* moving_var, float momentum, void* stream);
+/* y = act(gamma * (x - mean) / sqrt(var + eps) + beta); act 0 none, 1 ReLU, 2 ReLU6.  Also the inference form (moving stats). */
+int b200_bn_act_fwd(const void* x, const float* mean, const float* var, const float* gamma, const float* beta, float eps,
+                    void* y, long long rows, int C, int ldx, int ldy, int act, void* stream);
+/* Backward of the same through batch statistics: dx (optionally accumulated), dgamma += , dbeta += . */
+int b200_bn_act_bwd(const void* x, const void* dy, const float* mean, const float* var, const float* gamma, const float* beta,
+                    float eps, float* sums2C, long long rows, int C, int ldx, int lddy, int lddx, int act, int accumulate,
+                    void* dx, float* dgamma, float* dbeta, void* stream);
+/* 2x2 / 2 average pool (floor sizes): forward in [N,H,W,C] -> out [N,H/2,W/2,C]; backward in = dy -> out = dx [N,H,W,C]. */
+int b200_avgpool2(int backward, const void* in, void* out, int N, int H, int W, int C, void* stream);
+/* Filter gradient of a dense 3x3 / 1x1 convolution with Cin <= 8 (first layers): dw fp32 [KH*KW][Cout][Cin] += . */
+int b200_wgrad_small(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int ldx, int OH, int OW, int Cout,
+                     int ldy, int KH, int KW, int stride, int pad_h, int pad_w, void* stream);
+
 /* ------------------------------------------------------------------ image geometry (real-data path)
  * uint8 BGR interleaved images, pitches in bytes.  Bilinear resize and affine warp with OpenCV's fixed-point
  * arithmetic (cv2.resize INTER_LINEAR / cv2.warpAffine INTER_LINEAR), so a batch assembled on the GPU matches the
