@@ -6,7 +6,7 @@ DDP/NCCL measured baseline)."""
 
 
 def native_engine_class(model):
-    """ResNet and VGG run entirely on the native kernels; MobileNet / DenseNet keep an autograd backbone."""
+    """ResNet, VGG and MobileNet run entirely on the native kernels; DenseNet keeps an autograd backbone."""
     from ..models.resnet import ResNet
     from ..models.vgg import VGG
     if isinstance(model.backbone, ResNet):
@@ -15,6 +15,10 @@ def native_engine_class(model):
     if isinstance(model.backbone, VGG):
         from .vgg_native import VGGTrainer
         return VGGTrainer
+    from ..models.mobilenet import MobileNet
+    if isinstance(model.backbone, MobileNet):
+        from .mobilenet_native import MobileNetTrainer
+        return MobileNetTrainer
     from .hybrid import HybridTrainer
     return HybridTrainer
 

@@ -278,13 +278,13 @@ def colsum(x2d, cols, out_accum):
     _check(_load().b200_colsum(_ptr(x2d), C.c_longlong(rows), cols, x2d.shape[-1], _ptr(out_accum), _stream()), "colsum")
 
 
-def preprocess(src_u8, dst, mean, img_hw=None):
+def preprocess(src_u8, dst, mean, img_hw=None, scale: float = 1.0):
     """uint8 [N,H,W,C] -> bf16 [N,H,W,ld] minus mean; pixels outside each image's (h, w) (int32 [N,2], optional)
     become exactly 0, like the reference's zero padding after normalisation."""
     n, h, w, c = src_u8.shape
     m = (C.c_float * 4)(*([float(v) for v in mean] + [0.0] * (4 - len(mean))))
-    _check(_load().b200_preprocess(_ptr(src_u8), _ptr(dst), n, h, w, c, dst.shape[-1], m, _ptr(img_hw), _stream()),
-           "preprocess")
+    _check(_load().b200_preprocess_scaled(_ptr(src_u8), _ptr(dst), n, h, w, c, dst.shape[-1], m, _ptr(img_hw),
+                                          C.c_float(scale), _stream()), "preprocess")
 
 
 # ------------------------------------------------------------------------------ targets / losses

@@ -145,9 +145,11 @@ def main():
         from batchai_retinanet_horovod_coco_b200.engine.library import LibraryTrainer
         trainer = LibraryTrainer(args.backbone, args.classes, device=dev, distributed=world > 1)
     else:
-        from batchai_retinanet_horovod_coco_b200.engine.trainer import NativeTrainer
-        trainer = NativeTrainer(args.backbone, args.classes, device=dev, batch=args.batch,
-                                image_hw=(args.height, args.width), distributed=world > 1)
+        from batchai_retinanet_horovod_coco_b200 import models
+        from batchai_retinanet_horovod_coco_b200.engine import native_engine_class
+        model = models.backbone(args.backbone).retinanet(args.classes)
+        trainer = native_engine_class(model)(model=model, device=dev, batch=args.batch,
+                                            image_hw=(args.height, args.width), distributed=world > 1)
 
     from batchai_retinanet_horovod_coco_b200.ops import native
     host_sets = synth_batches(args, n_sets=4, seed=1234 + rank)

@@ -327,7 +327,7 @@ __global__ void colsum_det_kernel(ColsumArgs a, int cols, int ld, float* __restr
 // ------------------------------------------------------------------ image normalise + pad
 __global__ void preprocess_kernel(const uint8_t* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long pixels,
                                   int H, int W, int C, int ldc, float m0, float m1, float m2, float m3,
-                                  const int* __restrict__ img_hw) {
+                                  const int* __restrict__ img_hw, float scale) {
   const float mean[4] = {m0, m1, m2, m3};
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < pixels;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -339,7 +339,7 @@ __global__ void preprocess_kernel(const uint8_t* __restrict__ src, __nv_bfloat16
       inside = y < img_hw[2 * n] && x < img_hw[2 * n + 1];
     }
     for (int c = 0; c < ldc; ++c) {
-      const float v = (c < C && inside) ? static_cast<float>(src[i * C + c]) - mean[c & 3] : 0.f;
+      const float v = (c < C && inside) ? (static_cast<float>(src[i * C + c]) - mean[c & 3]) * scale : 0.f;
       dst[i * ldc + c] = __float2bfloat16(v);
     }
   }
@@ -559,13 +559,18 @@ int b200_colsum(const void* x, long long rows, int cols, int ld, float* out_accu
   return b200_colsum_multi(&x, &rows, 1, cols, ld, out_accum, stream);
 }
 
-int b200_preprocess(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean,
-                    const int* img_hw, void* stream) {
+int b200_preprocess_scaled(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean,
+                           const int* img_hw, float scale, void* stream) {
   const long long pixels = static_cast<long long>(N) * H * W;
   preprocess_kernel<<<grid_for(pixels, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       src, static_cast<__nv_bfloat16*>(dst), pixels, H, W, C, ldc, mean[0], C > 1 ? mean[1] : 0.f, C > 2 ? mean[2] : 0.f,
-      C > 3 ? mean[3] : 0.f, img_hw);
+      C > 3 ? mean[3] : 0.f, img_hw, scale);
   return check_launch("preprocess");
+}
+
+int b200_preprocess(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean,
+                    const int* img_hw, void* stream) {
+  return b200_preprocess_scaled(src, dst, N, H, W, C, ldc, mean, img_hw, 1.f, stream);
 }
 
 }  // extern "C"

@@ -146,6 +146,9 @@ int b200_colsum_multi(const void* const* xs, const long long* rows, int n, int c
 /* Image normalise + pad (G19): uint8 HWC (BGR) -> bf16 NHWC with Caffe mean subtraction. */
 int b200_preprocess(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean,
                     const int* img_hw /* optional device int32 [N,2]: pixels outside (h,w) are zeroed */, void* stream);
+/* Same with a scale after the mean: dst = (src - mean) * scale ("tf" mode of MobileNet / DenseNet: mean 127.5, scale 1/127.5). */
+int b200_preprocess_scaled(const uint8_t* src, void* dst, int N, int H, int W, int C, int ldc, const float* mean,
+                           const int* img_hw, float scale, void* stream);
 
 /* Anchor generation (G15): 9 anchors per location, level l, written at anchors[offset..]. */
 int b200_generate_anchors(float* anchors, int H, int W, int stride, float size, void* stream);
