@@ -38,7 +38,7 @@ def makedirs(path):
 
 
 MINIMUM_TORCH = (2, 4)
-OPS_ABI = 1
+OPS_ABI = 2
 
 
 def check_versions(device=None):

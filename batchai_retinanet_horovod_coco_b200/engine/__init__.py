@@ -6,7 +6,8 @@ DDP/NCCL measured baseline)."""
 
 
 def native_engine_class(model):
-    """ResNet, VGG and MobileNet run entirely on the native kernels; DenseNet keeps an autograd backbone."""
+    """Every backbone family runs entirely on the native kernels; HybridTrainer (autograd backbone) remains as the
+    fallback for backbone classes this function does not know."""
     from ..models.resnet import ResNet
     from ..models.vgg import VGG
     if isinstance(model.backbone, ResNet):
@@ -19,6 +20,10 @@ def native_engine_class(model):
     if isinstance(model.backbone, MobileNet):
         from .mobilenet_native import MobileNetTrainer
         return MobileNetTrainer
+    from ..models.densenet import DenseNet
+    if isinstance(model.backbone, DenseNet):
+        from .densenet_native import DenseNetTrainer
+        return DenseNetTrainer
     from .hybrid import HybridTrainer
     return HybridTrainer
 

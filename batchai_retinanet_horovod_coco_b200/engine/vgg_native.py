@@ -10,8 +10,8 @@ Details that differ from ResNet:
 
 * the image is preprocessed into an 8-channel NHWC buffer (TMA needs a 16-byte pixel stride); ``block1_conv1``
   runs with Cin = 3 inside a zero-filled 64-wide K tile;
-* the weight gradient of that one layer (Cin = 3 cannot be a 64-channel MN-major operand) is the only library
-  call of the step (``torch.nn.grad.conv2d_weight``, 0.1 % of the FLOPs);
+* the weight gradient of that one layer (Cin = 3 cannot be a 64-channel MN-major operand) comes from the small-Cin
+  CUDA-core kernel ``b200_wgrad_small``: no library call is left in the step;
 * pools floor, so the pyramid shapes come from ``VGG.feature_hw``; C3 / C4 / C5 are ``block{3,4,5}_pool``
   (keras-retinanet's VGG backbone, reachable through ``--backbone vgg16`` at reference ``train.py:390``).
 """
@@ -101,10 +101,9 @@ class VGGTrainer(NativeTrainer):
         self._mark("bwd_backbone")
 
     def _wgrad_first(self, c: Conv, x8, g):
-        """block1_conv1: Cin = 3 is below the 64-channel granularity of the MN-major wgrad operand."""
+        """block1_conv1: Cin = 3 is below the granularity of the tensor-core wgrad operand (95 % padding): a small
+        CUDA-core kernel (``b200_wgrad_small``) accumulates straight into the gradient bucket."""
         if not c.trainable:
             return
-        x = x8[..., :3].permute(0, 3, 1, 2)
-        dw = torch.nn.grad.conv2d_weight(x, (c.cout, 3, 3, 3), g.permute(0, 3, 1, 2), padding=1)
-        c.wview(self.G).add_(dw.float().permute(2, 3, 0, 1).reshape(9, c.cout, 3))
+        native.wgrad_small(x8, g, c.wview(self.G), 3, c.cout, 3, 3, 1, (1, 1))
         native.colsum(g, c.cout, c.bview(self.G))

@@ -186,11 +186,12 @@ def wgrad_raw(problems, dw: torch.Tensor, Cin: int, ldx: int, Cout: int, ldy: in
     _check(lib.b200_wgrad(C.byref(a), _stream()), "b200_wgrad")
 
 
-def stem_conv(x4, w_packed, shift, y):
-    """x4 bf16 [N,H,W,4] -> y bf16 [N,ceil(H/2),ceil(W/2),64] = relu(conv7x7/2(x) + shift)."""
+def stem_conv(x4, w_packed, shift, y, relu=True):
+    """x4 bf16 [N,H,W,4] -> y bf16 [N,ceil(H/2),ceil(W/2),64] = relu(conv7x7/2(x) + shift)  (relu optional)."""
     n, h, w, c = x4.shape
     assert c == 4 and w_packed.shape == (64, 256)
-    _check(require().b200_stem_conv(_ptr(x4), _ptr(w_packed), _ptr(shift), _ptr(y), n, h, w, _stream()), "b200_stem_conv")
+    _check(require().b200_stem_conv_ex(_ptr(x4), _ptr(w_packed), _ptr(shift), _ptr(y), n, h, w, int(relu), _stream()),
+           "b200_stem_conv")
 
 
 def stem_wgrad(x4, dy, scale, dw):
@@ -301,30 +302,34 @@ def dwconv3x3(mode: int, a, b, out, in_hw, out_hw, stride: int, pad):
 
 
 def bn_stats(x, channels, sums, mean, var, moving_mean=None, moving_var=None, momentum=0.99):
+    """x [..., C] may be a channel slice of a wider buffer: the channel stride is x.stride(-2)."""
     rows = x.numel() // x.shape[-1]
     import ctypes
-    _check(_load().b200_bn_stats(_ptr(x), ctypes.c_longlong(rows), int(channels), x.shape[-1], _ptr(sums), _ptr(mean), _ptr(var),
+    _check(_load().b200_bn_stats(_ptr(x), ctypes.c_longlong(rows), int(channels), x.stride(-2), _ptr(sums), _ptr(mean), _ptr(var),
                                  _ptr(moving_mean), _ptr(moving_var), ctypes.c_float(momentum), _stream()), "b200_bn_stats")
 
 
 def bn_act_fwd(x, mean, var, gamma, beta, eps, y, channels, act):
     rows = x.numel() // x.shape[-1]
     _check(_load().b200_bn_act_fwd(_ptr(x), _ptr(mean), _ptr(var), _ptr(gamma), _ptr(beta), C.c_float(eps), _ptr(y),
-                                   C.c_longlong(rows), channels, x.shape[-1], y.shape[-1], act, _stream()), "b200_bn_act_fwd")
+                                   C.c_longlong(rows), channels, x.stride(-2), y.stride(-2), act, _stream()), "b200_bn_act_fwd")
 
 
 def bn_act_bwd(x, dy, mean, var, gamma, beta, eps, sums, channels, act, dx, dgamma, dbeta, accumulate=False):
     rows = x.numel() // x.shape[-1]
     _check(_load().b200_bn_act_bwd(_ptr(x), _ptr(dy), _ptr(mean), _ptr(var), _ptr(gamma), _ptr(beta), C.c_float(eps), _ptr(sums),
-                                   C.c_longlong(rows), channels, x.shape[-1], dy.shape[-1], dx.shape[-1], act, int(accumulate),
+                                   C.c_longlong(rows), channels, x.stride(-2), dy.stride(-2), dx.stride(-2), act, int(accumulate),
                                    _ptr(dx), _ptr(dgamma), _ptr(dbeta), _stream()), "b200_bn_act_bwd")
 
 
-def avgpool2(x, y, backward=False):
-    """forward: x [N,H,W,C] -> y [N,H/2,W/2,C]; backward: x = dy [N,H/2,W/2,C] -> y = dx [N,H,W,C]."""
+def avgpool2(x, y, backward=False, channels=None):
+    """forward: x [N,H,W,C] -> y [N,H/2,W/2,C]; backward: x = dy [N,H/2,W/2,C] -> y = dx [N,H,W,C].  Either tensor may
+    be a channel slice of a wider buffer (its stride(2) is the channel stride)."""
     big = y if backward else x
     n, h, w, c = big.shape
-    _check(_load().b200_avgpool2(int(backward), _ptr(x), _ptr(y), n, h, w, c, _stream()), "b200_avgpool2")
+    c = channels or min(x.shape[-1], y.shape[-1])
+    _check(_load().b200_avgpool2(int(backward), _ptr(x), _ptr(y), n, h, w, c, x.stride(2), y.stride(2), _stream()),
+           "b200_avgpool2")
 
 
 def wgrad_small(x, dy, dw, cin, cout, kh, kw, stride, pad):

@@ -31,6 +31,7 @@ struct StemParams {
   __nv_bfloat16* y;         // [N, OH, OW, 64]
   int N, H, W, OH, OW;
   int tiles_h, tiles_w, total_tiles;
+  int relu;                 // 0: raw conv + shift (a trainable batch norm follows: DenseNet)
 };
 
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
@@ -189,13 +190,14 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_conv_kernel(const StemPa
         if (valid) {
 #pragma unroll
           for (int j = 0; j < 32; j += 8) {
+            const float lo = p.relu ? 0.f : -3.0e38f;      // ReLU as a lower clamp that can be switched off
             const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.shift + c + j));
             const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.shift + c + j + 4));
             uint4 o;
-            o.x = pack_bf16x2(fmaxf(__uint_as_float(r[j]) + s0.x, 0.f), fmaxf(__uint_as_float(r[j + 1]) + s0.y, 0.f));
-            o.y = pack_bf16x2(fmaxf(__uint_as_float(r[j + 2]) + s0.z, 0.f), fmaxf(__uint_as_float(r[j + 3]) + s0.w, 0.f));
-            o.z = pack_bf16x2(fmaxf(__uint_as_float(r[j + 4]) + s1.x, 0.f), fmaxf(__uint_as_float(r[j + 5]) + s1.y, 0.f));
-            o.w = pack_bf16x2(fmaxf(__uint_as_float(r[j + 6]) + s1.z, 0.f), fmaxf(__uint_as_float(r[j + 7]) + s1.w, 0.f));
+            o.x = pack_bf16x2(fmaxf(__uint_as_float(r[j]) + s0.x, lo), fmaxf(__uint_as_float(r[j + 1]) + s0.y, lo));
+            o.y = pack_bf16x2(fmaxf(__uint_as_float(r[j + 2]) + s0.z, lo), fmaxf(__uint_as_float(r[j + 3]) + s0.w, lo));
+            o.z = pack_bf16x2(fmaxf(__uint_as_float(r[j + 4]) + s1.x, lo), fmaxf(__uint_as_float(r[j + 5]) + s1.y, lo));
+            o.w = pack_bf16x2(fmaxf(__uint_as_float(r[j + 6]) + s1.z, lo), fmaxf(__uint_as_float(r[j + 7]) + s1.w, lo));
             *reinterpret_cast<uint4*>(dst + c + j) = o;
           }
         }
@@ -214,8 +216,8 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_conv_kernel(const StemPa
 
 }  // namespace b200
 
-extern "C" int b200_stem_conv(const void* x, const void* w_packed, const float* shift, void* y, int N, int H, int W,
-                              void* stream) {
+extern "C" int b200_stem_conv_ex(const void* x, const void* w_packed, const float* shift, void* y, int N, int H, int W,
+                              int relu, void* stream) {
   using namespace b200;
   static std::atomic<unsigned long long> attr{0};   // per device
   if (device_needs_setup(attr)) {
@@ -226,6 +228,7 @@ extern "C" int b200_stem_conv(const void* x, const void* w_packed, const float* 
   p.x = static_cast<const __nv_bfloat16*>(x);
   p.w = static_cast<const __nv_bfloat16*>(w_packed);
   p.shift = shift;
+  p.relu = relu;
   p.y = static_cast<__nv_bfloat16*>(y);
   p.N = N;
   p.H = H;
@@ -458,4 +461,9 @@ extern "C" int b200_stem_wgrad(const void* x, const void* dy, const float* scale
   const int grid = deterministic() ? 1 : (p.total_tiles < num_sms() ? p.total_tiles : num_sms());
   stem_wgrad_kernel<<<grid, kSwThreads, kSwSmem, static_cast<cudaStream_t>(stream)>>>(p);
   return check_launch("stem_wgrad_kernel");
+}
+
+extern "C" int b200_stem_conv(const void* x, const void* w_packed, const float* shift, void* y, int N, int H, int W,
+                              void* stream) {
+  return b200_stem_conv_ex(x, w_packed, shift, y, N, H, W, 1, stream);
 }

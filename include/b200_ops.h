@@ -97,6 +97,9 @@ int b200_wgrad(const B200WgradArgs* args, void* stream);
  * swizzled smem tile (Cin=3 cannot feed TMA).  Replaces cuDNN conv1 forward (G1). */
 int b200_stem_conv(const void* x, const void* w_packed, const float* shift, void* y, int N, int H, int W,
                    void* stream);
+/* Same with the ReLU optional (relu = 0: raw conv + shift, for a stem followed by a trainable batch norm: DenseNet). */
+int b200_stem_conv_ex(const void* x, const void* w_packed, const float* shift, void* y, int N, int H, int W, int relu,
+                      void* stream);
 /* Stem weight gradient: dw fp32 [49][64][3] (tap, co, ci) += scale[co] * dY^T * im2col(x).
  * dy bf16 [N,ceil(H/2),ceil(W/2),64].  Replaces cuDNN backward-filter for conv1 (G12). */
 int b200_stem_wgrad(const void* x, const void* dy, const float* scale, float* dw, int N, int H, int W, void* stream);
@@ -223,8 +226,9 @@ int b200_bn_act_fwd(const void* x, const float* mean, const float* var, const fl
 int b200_bn_act_bwd(const void* x, const void* dy, const float* mean, const float* var, const float* gamma, const float* beta,
                     float eps, float* sums2C, long long rows, int C, int ldx, int lddy, int lddx, int act, int accumulate,
                     void* dx, float* dgamma, float* dbeta, void* stream);
-/* 2x2 / 2 average pool (floor sizes): forward in [N,H,W,C] -> out [N,H/2,W/2,C]; backward in = dy -> out = dx [N,H,W,C]. */
-int b200_avgpool2(int backward, const void* in, void* out, int N, int H, int W, int C, void* stream);
+/* 2x2 / 2 average pool (floor sizes): forward in [N,H,W,C] -> out [N,H/2,W/2,C]; backward in = dy -> out = dx [N,H,W,C].
+ * ld_in / ld_out: channel strides (either side may be a slice of a wider concatenation buffer). */
+int b200_avgpool2(int backward, const void* in, void* out, int N, int H, int W, int C, int ld_in, int ld_out, void* stream);
 /* Filter gradient of a dense 3x3 / 1x1 convolution with Cin <= 8 (first layers): dw fp32 [KH*KW][Cout][Cin] += . */
 int b200_wgrad_small(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int ldx, int OH, int OW, int Cout,
                      int ldy, int KH, int KW, int stride, int pad_h, int pad_w, void* stream);

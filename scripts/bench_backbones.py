@@ -1,5 +1,5 @@
-"""Non-ResNet backbones (reference train.py:323-324 `--backbone`): HybridTrainer (native FPN / heads / losses /
-optimizer, autograd backbone) vs the library baseline, one GPU, 800x1333, batch 8, device-timed."""
+"""Non-ResNet backbones (reference train.py:323-324 `--backbone`): the native engine of each family (VGGTrainer,
+MobileNetTrainer, DenseNetTrainer) vs the library baseline (CUDA-graphed), one GPU, 800x1333, batch 8, device-timed."""
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -19,7 +19,7 @@ for bb in sys.argv[1:] or ("vgg16", "mobilenet224_1.0", "densenet121"):
             model = RetinaNet(80, bb)
             tr = native_engine_class(model)(model=model, device=dev, batch=B, image_hw=(H, W))
             impl = "b200-" + type(tr).__name__
-        ms = timeit(lambda: tr.train_step(*b), 6)
+        ms = timeit(lambda: tr.train_step(*b), 10, warm=6)          # graph capture (4th call of the library arm) stays out of the timed region
         row = {"backbone": bb, "impl": impl, "batch": B, "image": [H, W], "train_ms_per_step": round(ms, 3),
                "train_img_per_s": round(B / ms * 1e3, 1)}
         if impl != "library":

@@ -14,6 +14,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("backbone,steps,hw", [("resnet50", 300, (256, 320)), ("vgg16", 300, (256, 320)),
                                                ("mobilenet224_1.0", 500, (256, 320)),   # native depthwise / batch-norm path
+                                               ("densenet121", 500, (256, 320)),        # native concat / BN / avg-pool path
                                                ("resnet50", 300, (250, 310))])   # last: padded up to the 64-px shape bucket
 def test_overfit_then_detect(backbone, steps, hw):
     from batchai_retinanet_horovod_coco_b200.engine import create_trainer

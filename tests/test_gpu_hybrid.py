@@ -32,7 +32,7 @@ def test_hybrid_matches_autograd(name):
     ref_model = copy.deepcopy(model)
     img, gt, cnt, hw = _inputs(B, H, W)
 
-    if not name.startswith("vgg"):          # VGG has a fully native engine (tests/test_gpu_vgg.py); hybrid still works
+    if not name.startswith("vgg"):          # every family has a native engine now; the hybrid one is exercised directly
         assert isinstance(create_trainer(copy.deepcopy(model), "cuda", batch=B, image_hw=(H, W)), HybridTrainer)
     ht = HybridTrainer(model=model, device="cuda", batch=B, image_hw=(H, W), shape_bucket=1)   # exact shapes
     loss_h, _ = ht.forward_loss(img, gt, cnt, hw)
