@@ -95,6 +95,13 @@ struct ConvParams {
   int mode, gsz, tap_groups, kgroups;
   int a_stages, b_stages, slots, a_stage_bytes, b_stage_bytes, smem_bytes;
   int widx3[3][3];      // halo mode: [dw + 1][dh + 1] -> weight tap index
+  // pair mode (streamed weights): the launch runs as clusters of two CTAs that work on neighbouring pixel tiles of the
+  // same N tile in lock step and share the weight stream -- each CTA fetches HALF of every weight tile and TMA
+  // multicasts it into both shared memories, so a weight tile crosses L2 -> SM once per pair instead of once per CTA
+  // (ncu on the res4 1x1 layers: 7.5-10 TB/s of L2 -> SM traffic, two thirds of it identical weight tiles, tensor
+  // pipe 30-46 % active).  num_m_tiles is then padded to an even count; real_m_tiles is the true one and the extra
+  // tile only keeps the shared ring moving.
+  int pair, real_m_tiles;
 };
 
 __device__ __forceinline__ void decode_tile(const ConvParams& p, int tile, int& pi, int& n, int& y0, int& x0,
@@ -165,6 +172,10 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = p.num_m_tiles * p.num_n_tiles;
+  const bool pair = p.pair != 0;
+  const uint32_t crank = pair ? cluster_ctarank() : 0u;
+  // pair mode: the odd CTA's last tile may lie past the end (every role but the weight ring skips it)
+  auto is_dummy = [&](int tile) { return pair && (tile % p.num_m_tiles) >= p.real_m_tiles; };
   const int gsz = p.gsz, kgroups = p.kgroups;
   const int num_groups = p.tap_groups * kgroups;          // activation boxes per tile
   const int num_substeps = p.num_taps * p.num_kc;         // weight tiles per tile
@@ -191,7 +202,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
     for (int s = 0; s < kMaxBStages; ++s) {
       mbar_init(bfull_bar(s), 1);
-      mbar_init(bempty_bar(s), 1);
+      mbar_init(bempty_bar(s), pair ? 2 : 1);       // pair mode: both CTAs' MMA warps release a stage
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
@@ -210,6 +221,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   }
   tc_fence_before();
   __syncthreads();
+  if (pair) cluster_sync_all();          // the partner's barriers exist before anything is multicast into them
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
@@ -225,6 +237,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       int sa = 0;
       uint32_t pa = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        if (is_dummy(tile)) continue;
         int pi, n, y0, x0, n_tile;
         decode_tile(p, tile, pi, n, y0, x0, n_tile);
         const DevProblem& q = p.prob[pi];
@@ -260,6 +273,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     if (elect_one()) {
       int sb = 0;
       uint32_t pb = 0;
+      const uint32_t half_off = crank * (b_bytes >> 1);
+      const int half_row = static_cast<int>(crank) * (p.BN >> 1);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int row0 = (tile / p.num_m_tiles) * p.BN;
         for (int t = 0; t < p.tap_groups; ++t) {
@@ -269,8 +284,12 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
               const int widx = p.mode == 1 ? p.widx3[t][j] : p.taps[t].widx;
               const int kc = p.mode == 2 ? kg * gsz + j : kg;
               mbar_wait(bempty_bar(sb), pb ^ 1);
-              mbar_expect_tx(bfull_bar(sb), b_bytes);
-              tma_load_3d(b_smem + sb * p.b_stage_bytes, &p.w_map, bfull_bar(sb), kc * kBK, row0, widx);
+              mbar_expect_tx(bfull_bar(sb), b_bytes);     // both halves: mine and the partner's
+              if (pair)
+                tma_load_3d_mc(b_smem + sb * p.b_stage_bytes + half_off, &p.w_map, bfull_bar(sb), kc * kBK, row0 + half_row,
+                               widx, static_cast<uint16_t>(3));
+              else
+                tma_load_3d(b_smem + sb * p.b_stage_bytes, &p.w_map, bfull_bar(sb), kc * kBK, row0, widx);
               if (++sb == b_stages) {
                 sb = 0;
                 pb ^= 1;
@@ -279,6 +298,16 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           }
         }
         if (weights_resident) break;      // one pass filled every stage for good
+      }
+      if (pair) {
+        // every release the partner still owes my barriers has landed before either CTA may exit
+        for (int i = 0; i < b_stages; ++i) {
+          mbar_wait(bempty_bar(sb), pb ^ 1);
+          if (++sb == b_stages) {
+            sb = 0;
+            pb ^= 1;
+          }
+        }
       }
     }
   } else if (warp == 1) {
@@ -301,8 +330,29 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       uint32_t acc_phase = 0;
       const bool one_problem = p.num_problems == 1;
       uint32_t sub_step = static_cast<uint32_t>(p.prob[0].sub_stride) >> 4;
+      auto next_b = [&]() {
+        b_cur += b_step;
+        bfull += 8;
+        bempty += 8;
+        if (++sb == b_stages) {
+          sb = 0;
+          pb ^= 1;
+          b_cur = b_first;
+          bfull = bfull_bar(0);
+          bempty = bempty_bar(0);
+          if (weights_resident) b_wait = false;
+        }
+      };
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int n_tile = tile / p.num_m_tiles;
+        if (is_dummy(tile)) {             // no pixels here: receive and release the shared weight tiles only
+          for (int j = 0; j < num_substeps; ++j) {
+            mbar_wait(bfull, pb);
+            umma_commit_mc(bempty, static_cast<uint16_t>(3));
+            next_b();
+          }
+          continue;
+        }
         if (!one_problem) {               // halo tiles differ per pyramid level
           int pi, n, y0, x0, nt2;
           decode_tile(p, tile, pi, n, y0, x0, nt2);
@@ -333,20 +383,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
               // advance 16 bf16 = 32 bytes along K inside the 128B swizzle row: +2 in (addr >> 4) units
               umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, accumulate | k);
             }
-            if (!weights_resident) umma_commit(bempty);
+            if (pair) umma_commit_mc(bempty, static_cast<uint16_t>(3));
+            else if (!weights_resident) umma_commit(bempty);
             accumulate = 1;
             a_sub += sub_step;
-            b_cur += b_step;
-            bfull += 8;
-            bempty += 8;
-            if (++sb == b_stages) {
-              sb = 0;
-              pb ^= 1;
-              b_cur = b_first;
-              bfull = bfull_bar(0);
-              bempty = bempty_bar(0);
-              if (weights_resident) b_wait = false;
-            }
+            next_b();
           }
           umma_commit(aempty);
           if (g == num_groups - 1) umma_commit(tfull_bar(acc));
@@ -398,6 +439,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       };
       const uint32_t cs_off = (static_cast<uint32_t>(lane & 3) << 2);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        if (is_dummy(tile)) continue;
         int pi, n, y0, x0, n_tile;
         decode_tile(p, tile, pi, n, y0, x0, n_tile);
         const int nch = tile_chunks(p, n_tile);
@@ -453,6 +495,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       if (elect_one()) {
         SlotCursor cur{0, 0u};
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+          if (is_dummy(tile)) continue;
           int pi, n, y0, x0, n_tile;
           decode_tile(p, tile, pi, n, y0, x0, n_tile);
           const int nch = tile_chunks(p, n_tile);
@@ -498,6 +541,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      if (is_dummy(tile)) continue;
       const int n_tile = tile / p.num_m_tiles;
       const int col0 = n_tile * BN;
       const int col_end = min(Nrows, col0 + BN);
@@ -622,6 +666,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 
   tc_fence_before();
   __syncthreads();
+  if (pair) cluster_sync_all();          // my shared memory stays alive until the partner has stopped writing into it
   if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
 }
 
@@ -656,6 +701,33 @@ static int launch_variant(const ConvParams& p, int grid, cudaStream_t stream) {
   if (device_needs_setup(attr_set)) {
     B200_CUDA_OK(cudaFuncSetAttribute(conv_igemm_kernel<kAdd, kMask>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     device_setup_done(attr_set);
+  }
+  if (p.pair) {
+    // clusters of two need both SMs free in one GPC: ask once how many fit at the same time (every layout of this
+    // kernel is one CTA per SM, so the answer does not depend on the shared-memory size)
+    static std::atomic<int> fit{0};
+    int clusters = fit.load();
+    if (clusters == 0) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(static_cast<unsigned>(num_sms() & ~1));
+      cfg.blockDim = dim3(kConvThreads);
+      cfg.dynamicSmemBytes = static_cast<size_t>(p.smem_bytes);
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 2;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      if (cudaOccupancyMaxActiveClusters(&clusters, conv_igemm_kernel<kAdd, kMask>, &cfg) != cudaSuccess || clusters < 1) {
+        cudaGetLastError();
+        clusters = num_sms() / 2 - 2;
+      }
+      fit.store(clusters);
+    }
+    if (grid > 2 * clusters) grid = 2 * clusters;
+    launch_pdl_cluster(conv_igemm_kernel<kAdd, kMask>, grid, kConvThreads, static_cast<size_t>(p.smem_bytes), stream, 2u, p);
+    return check_launch("conv_igemm_kernel (pairs)");
   }
   launch_pdl(conv_igemm_kernel<kAdd, kMask>, grid, kConvThreads, static_cast<size_t>(p.smem_bytes), stream, p);
   return check_launch("conv_igemm_kernel");
@@ -875,13 +947,21 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
       }
     }
   }
-  p.num_m_tiles = tile_begin;
+  p.num_m_tiles = p.real_m_tiles = tile_begin;
+  static int pair_env = -1;
+  if (pair_env < 0) {
+    const char* e = getenv("B200_CONV_PAIRS");       // 0: every CTA streams its own weights (A/B arm for profiles)
+    pair_env = (e && e[0] == '0') ? 0 : 1;
+  }
+  const bool streamed = !(p.num_n_tiles == 1 && b_st == num_substeps);
+  p.pair = (pair_env && streamed && (p.BN % 16) == 0 && num_sms() >= 4) ? 1 : 0;
+  if (p.pair) p.num_m_tiles = (p.real_m_tiles + 1) & ~1;
   {
     unsigned long long dims[3] = {static_cast<unsigned long long>(a->K), static_cast<unsigned long long>(a->Nrows),
                                   static_cast<unsigned long long>(a->KH * a->KW)};
     unsigned long long strides[2] = {static_cast<unsigned long long>(a->ldw) * 2ull,
                                      static_cast<unsigned long long>(a->Nrows) * a->ldw * 2ull};
-    const unsigned int box[3] = {static_cast<unsigned>(kBK), static_cast<unsigned>(p.BN), 1u};
+    const unsigned int box[3] = {static_cast<unsigned>(kBK), static_cast<unsigned>(p.pair ? p.BN / 2 : p.BN), 1u};
     int rc = make_tmap_bf16(&p.w_map, a->weight, 3, dims, strides, box);
     if (rc) return rc;
   }
@@ -891,8 +971,9 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   // ---- shared-memory split between the operand ring and the epilogue chunk slots.
   // Short K loops (the memory-bound 1x1 layers) need few ring stages -- the weights stay resident and one stage is one
   // whole tile -- and give the rest to chunk slots = bytes of residual / mask / result in flight per SM.
-  const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles;
-  const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
+  const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles;      // even in pair mode
+  const int sms = p.pair ? (num_sms() & ~1) : num_sms();
+  const int grid = static_cast<int>(total < sms ? total : sms);
   if (has_add && has_mask) return launch_variant<true, true>(p, grid, stream);
   if (has_add) return launch_variant<true, false>(p, grid, stream);
   if (has_mask) return launch_variant<false, true>(p, grid, stream);

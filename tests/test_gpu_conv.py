@@ -71,6 +71,11 @@ CASES = [
     (2, 26, 42, 256, 128, 1, 2),
     (1, 25, 42, 128, 256, 3, 2),
     (1, 32, 32, 2048, 256, 3, 2),
+    # streamed weights -> CTA pairs sharing the weight ring by TMA multicast: odd tile counts (the odd CTA of the last
+    # pair only forwards weight tiles), more tiles than CTAs, several N tiles
+    (1, 24, 40, 256, 256, 3, 1),
+    (8, 50, 84, 1024, 256, 1, 1),
+    (5, 50, 75, 256, 1024, 1, 1),
 ]
 
 
