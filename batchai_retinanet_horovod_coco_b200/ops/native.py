@@ -167,6 +167,14 @@ def conv_raw(mode: int, problems, weight: torch.Tensor, K: int, ldi: int, Nrows:
     _check(lib.b200_conv(C.byref(a), _stream()), "b200_conv")
 
 
+def conv_set_trace(buf):
+    """buf: int64 device tensor [>= SMs * 16] receiving the conv kernel's in-kernel timeline, or None (off)."""
+    lib = require()
+    lib.b200_conv_set_trace.restype = None
+    lib.b200_conv_set_trace.argtypes = [C.c_void_p]
+    lib.b200_conv_set_trace(C.c_void_p(0 if buf is None else buf.data_ptr()))
+
+
 def wgrad_raw(problems, dw: torch.Tensor, Cin: int, ldx: int, Cout: int, ldy: int, KH: int, KW: int, stride: int,
               pad_h: int, pad_w: int, rowscale=None, dbias=None):
     """problems: list of (x NHWC, dy NHWC).  dw fp32 [taps, Cout, Cin] accumulated into."""

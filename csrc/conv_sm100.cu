@@ -102,6 +102,7 @@ struct ConvParams {
   // pipe 30-46 % active).  num_m_tiles is then padded to an even count; real_m_tiles is the true one and the extra
   // tile only keeps the shared ring moving.
   int pair, real_m_tiles;
+  long long* trace;     // optional in-kernel timeline: 16 clock64 stamps per CTA (b200_conv_set_trace)
 };
 
 __device__ __forceinline__ void decode_tile(const ConvParams& p, int tile, int& pi, int& n, int& y0, int& x0,
@@ -176,6 +177,14 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   const uint32_t crank = pair ? cluster_ctarank() : 0u;
   // pair mode: the odd CTA's last tile may lie past the end (every role but the weight ring skips it)
   auto is_dummy = [&](int tile) { return pair && (tile % p.num_m_tiles) >= p.real_m_tiles; };
+  long long* const tr = p.trace ? p.trace + static_cast<size_t>(blockIdx.x) * 16 : nullptr;
+#define B200_TR(i) do { if (tr) tr[i] = clock64(); } while (0)
+  if (tr && threadIdx.x == 0) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    tr[0] = static_cast<long long>(gt);
+    tr[1] = clock64();
+  }
   const int gsz = p.gsz, kgroups = p.kgroups;
   const int num_groups = p.tap_groups * kgroups;          // activation boxes per tile
   const int num_substeps = p.num_taps * p.num_kc;         // weight tiles per tile
@@ -228,6 +237,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   // set-up done: let the next kernel start its own set-up, then wait for the previous kernel's results
   pdl_launch_dependents();
   pdl_wait();
+  if (threadIdx.x == 0) B200_TR(2);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ activation producer (one elected thread)
@@ -260,6 +270,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             const uint32_t dst = a_smem + sa * p.a_stage_bytes;
             if (p.mode == 2) tma_load_5d(dst, amap, afull_bar(sa), 0, x, y, n, kg * gsz);
             else tma_load_4d(dst, amap, afull_bar(sa), kg * kBK, x, y, n);
+            if (tile == static_cast<int>(blockIdx.x) && t == 0 && kg == 0) B200_TR(3);
             if (++sa == a_stages) {
               sa = 0;
               pa ^= 1;
@@ -371,11 +382,14 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           if (++kg == kgroups) kg = 0;
           mbar_wait(afull, pa);
           tc_fence_after();
+          if (tile == static_cast<int>(blockIdx.x) && g == 0) B200_TR(4);
+          if (tile == static_cast<int>(blockIdx.x) && g == num_groups - 1) B200_TR(13);
           uint32_t a_sub = a_cur;
           for (int j = 0; j < ns; ++j) {
             if (b_wait) {
               mbar_wait(bfull, pb);
               tc_fence_after();
+              if (tile == static_cast<int>(blockIdx.x) && g == 0 && j == 0) B200_TR(5);
             }
             const uint64_t adesc = desc_hi | a_sub, bdesc = desc_hi | b_cur;
 #pragma unroll
@@ -390,7 +404,10 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             next_b();
           }
           umma_commit(aempty);
-          if (g == num_groups - 1) umma_commit(tfull_bar(acc));
+          if (g == num_groups - 1) {
+            umma_commit(tfull_bar(acc));
+            B200_TR(tile == static_cast<int>(blockIdx.x) ? 6 : 9);
+          }
           a_cur += a_step;
           afull += 8;
           aempty += 8;
@@ -488,6 +505,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         }
       }
       flush();
+      if (lane == 0) B200_TR(10);
     }
   } else if (warp == 3) {
     // ------------------------------------------------------------------ epilogue-operand loader (one thread)
@@ -563,6 +581,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       }
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
+      if (ew == 0 && lane == 0) B200_TR(tile == static_cast<int>(blockIdx.x) ? 7 : 14);
       if (my_last < 0) {
         tc_fence_before();
         mbar_arrive(tempty_bar(acc));
@@ -661,6 +680,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       g += nch;
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
+      if (ew == 0 && lane == 0 && tile == static_cast<int>(blockIdx.x)) B200_TR(8);
     }
   }
 
@@ -668,6 +688,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   __syncthreads();
   if (pair) cluster_sync_all();          // my shared memory stays alive until the partner has stopped writing into it
   if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+  if (tr && threadIdx.x == 0) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    tr[11] = clock64();
+    tr[12] = static_cast<long long>(gt);
+  }
+#undef B200_TR
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -735,6 +762,10 @@ static int launch_variant(const ConvParams& p, int grid, cudaStream_t stream) {
 
 }  // namespace b200
 
+static std::atomic<long long*> g_conv_trace{nullptr};
+
+extern "C" void b200_conv_set_trace(void* buf) { g_conv_trace.store(static_cast<long long*>(buf)); }
+
 extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   using namespace b200;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -751,6 +782,7 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
 
   ConvParams p;
   memset(&p, 0, sizeof(p));
+  p.trace = g_conv_trace.load();
   p.num_problems = a->num_problems;
   p.Nrows = a->Nrows;
   p.BN = pick_bn(a->Nrows);
@@ -880,7 +912,18 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   int map_count = 0;
   const unsigned long long c8 = static_cast<unsigned long long>((a->Nrows + 7) / 8 * 8);   // stored channels
   for (int i = 0; i < a->num_problems; ++i) {
-    const B200ConvProblem& q = a->prob[i];
+    B200ConvProblem q = a->prob[i];
+    // 1x1 / stride 1: pixels are independent, so the problem is a flat list of N*H*W pixels and a tile is any 128
+    // consecutive ones -- no partly filled tiles at row ends or image ends (8x50x84: 263 tiles instead of 312, and two
+    // waves on 148 SMs instead of three; 25x42 maps were 46 % padding)
+    if (a->KH == 1 && a->KW == 1 && s == 1 && a->pad_h == 0 && a->pad_w == 0 && q.OHo == q.H && q.OWo == q.W) {
+      const long long px = static_cast<long long>(q.N) * q.H * q.W;
+      if (px < (1LL << 31)) {
+        q.N = 1;
+        q.H = q.OHo = 1;
+        q.W = q.OWo = static_cast<int>(px);
+      }
+    }
     DevProblem& d = p.prob[i];
     int OH, OW;   // GEMM pixel grid
     if (a->mode == 1 && s == 2) {

@@ -309,7 +309,16 @@ extern "C" int b200_wgrad(const B200WgradArgs* a, void* stream_) {
 
   int tile_begin = 0, map_count = 0;
   for (int i = 0; i < a->num_problems; ++i) {
-    const B200WgradProblem& q = a->prob[i];
+    B200WgradProblem q = a->prob[i];
+    // 1x1 / stride 1: a flat list of pixels, tiles of any 64 consecutive ones (no partly filled tiles at row / image ends)
+    if (a->KH == 1 && a->KW == 1 && s == 1 && a->pad_h == 0 && a->pad_w == 0 && q.OH == q.H && q.OW == q.W) {
+      const long long px = static_cast<long long>(q.N) * q.H * q.W;
+      if (px < (1LL << 31)) {
+        q.N = 1;
+        q.H = q.OH = 1;
+        q.W = q.OW = static_cast<int>(px);
+      }
+    }
     WProblem& d = p.prob[i];
     d.N = q.N;
     d.OH = q.OH;

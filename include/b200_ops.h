@@ -67,6 +67,12 @@ typedef struct {
   int add_after_mask; /* 0: (acc+add)*mask ; 1: acc*mask + add */
 } B200ConvArgs;
 
+/* In-kernel timeline of the conv kernel: buf = device array of 16 int64 per CTA (>= 148 * 16), or NULL to switch it
+ * off.  Per CTA: [0] globaltimer ns at entry, [1] clock at entry, [2] set-up done, [3] first activation box issued,
+ * [4] first activation box landed, [5] first weight tile landed, [6] tile 0: last MMA issued, [13] tile 0: last
+ * activation box landed, [7] tile 0: accumulator complete, [8] tile 0: epilogue done, [9] / [14] same as 6 / 7 for the
+ * CTA's last tile, [10] last store read out, [11] clock at exit, [12] globaltimer at exit.  Profiling aid. */
+void b200_conv_set_trace(void* buf);
 int b200_conv(const B200ConvArgs* args, void* stream);
 
 /* Weight gradient: dW[t][co][ci] += rowscale[co] * sum_pixels dY[p, co] * X[p + tap, ci]
