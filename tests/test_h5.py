@@ -112,3 +112,68 @@ def test_full_model_with_optimizer_state(tmp_path, model):
         tc = json.loads(bytes(f.attr("/", "training_config")).decode())
         assert tc["loss"] == {"regression": "_smooth_l1", "classification": "_focal"}
         assert bytes(f.attr("/optimizer_weights", "weight_names")[0]) == b"Adam/iterations:0"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# A file this package's writer did NOT produce: tests/fixtures/keras_resnet50_stem_libhdf5.h5 is assembled byte by byte
+# from the HDF5 format specification in libhdf5 1.8's layout (tests/fixtures/libhdf5_layout.py lists what that means:
+# header continuation blocks, NIL messages, 8-byte padded v1 attributes, fixed-length string arrays, dataspaces with
+# maximum dimensions, fill-value / mtime messages, several symbol-table leaves, cached group entries).
+def _fixture():
+    import os, sys
+    d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "fixtures")
+    sys.path.insert(0, d)
+    import make_keras_fixture as mk
+    return mk
+
+
+def test_foreign_layout_fixture_structure():
+    mk = _fixture()
+    raw = open(mk.PATH, "rb").read()
+    assert raw == mk.build(), "committed fixture is out of date: python tests/fixtures/make_keras_fixture.py"
+    # the features the fixture exists for are really in the bytes
+    root_oh = struct.unpack_from("<Q", raw, 64)[0]
+    assert root_oh == 96 and raw[root_oh] == 1
+    nmsg, _, size = struct.unpack_from("<HII", raw, root_oh + 2)
+    types, pos = [], root_oh + 16
+    while pos < root_oh + 16 + size:
+        t, n = struct.unpack_from("<HH", raw, pos)
+        types.append(t)
+        if t == 0x10:
+            cont, clen = struct.unpack_from("<QQ", raw, pos + 8)
+        pos += 8 + n
+    assert types == [0x11, 0x00, 0x10], types                 # symbol table, NIL filler, continuation
+    assert cont > root_oh + 16 + size and cont + clen <= len(raw)
+    t0, n0 = struct.unpack_from("<HH", raw, cont)
+    assert t0 == 0x0C                                         # the attributes live in the continuation block
+    name_size, = struct.unpack_from("<H", raw, cont + 8 + 2)
+    assert raw[cont + 16:cont + 16 + 12] == b"layer_names\0" and name_size == 12      # 12 bytes, padded to 16
+    assert nmsg == 3 + 3 + 1
+    with H5File(mk.PATH, "r") as f:
+        assert f.keys("/") == sorted(n for n, _ in mk.LAYERS)
+        assert [bytes(x).decode() for x in f.attr("/", "layer_names")] == [n for n, _ in mk.LAYERS]
+        assert f.attr("/", "backend") == b"tensorflow" and f.attr("/", "keras_version") == b"2.1.6"
+        assert len(f.attr("/pool1", "weight_names")) == 0
+        for layer, weights in mk.LAYERS:
+            assert [bytes(x).decode() for x in np.atleast_1d(f.attr("/" + layer, "weight_names"))] == [w for w, _ in weights]
+            for w, shape in weights:
+                assert np.array_equal(f.dataset(f"/{layer}/{w}"), mk.values(w, shape))
+
+
+def test_foreign_layout_fixture_loads_by_name():
+    mk = _fixture()
+    torch.manual_seed(1)
+    m = RetinaNet(80, "resnet50")
+    before = m.keras_layers()["res2a_branch2b"].weight.detach().clone()
+    with pytest.warns(UserWarning, match="mismatch in shape"):
+        rep = keras_h5.load_weights(m, mk.PATH, by_name=True, skip_mismatch=True)
+    assert set(rep["loaded"]) == {"conv1/kernel:0", "res2a_branch2a/kernel:0"} | {
+        f"{bn}/{k}:0" for bn in ("bn_conv1", "bn2a_branch2a") for k in ("gamma", "beta", "moving_mean", "moving_variance")}
+    assert rep["skipped"] == ["res2a_branch2b/kernel:0"]      # (3, 3, 64, 32) in the file, (3, 3, 64, 64) in the model
+    assert "res2b_branch2a/kernel:0" in rep["missing"] and not any(w.startswith("fc1000") for w in rep["missing"])
+    layers = m.keras_layers()
+    k = mk.values("conv1/kernel:0", (7, 7, 3, 64))             # Keras HWIO -> OIHW
+    assert torch.equal(layers["conv1"].weight.detach(), torch.from_numpy(k.transpose(3, 2, 0, 1).copy()))
+    assert torch.equal(layers["bn_conv1"].moving_variance.detach(),
+                       torch.from_numpy(mk.values("bn_conv1/moving_variance:0", (64,))))
+    assert torch.equal(layers["res2a_branch2b"].weight.detach(), before)
