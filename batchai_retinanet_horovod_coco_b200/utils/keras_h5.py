@@ -98,11 +98,12 @@ def save_weights(model, path: str):
 
 
 def model_config(model) -> dict:
-    return {"class_name": "Model",
-            "config": {"name": "retinanet", "backbone": model.backbone_name, "num_classes": model.num_classes,
-                       "layers": [{"name": n, "class_name": type(m).__name__} for n, m in model.keras_layers().items()],
-                       "input_layers": [["input_1", 0, 0]],
-                       "output_layers": [["regression", 0, 0], ["classification", 0, 0]]}}
+    """``model.to_json()`` content: a Keras 2.1.6 functional ``Model`` configuration (every layer with its constructor
+    arguments and inbound nodes, ``utils/keras_config.py``).  ``b200`` is an extra top-level key Keras ignores; it lets
+    ``load_full_model`` rebuild the model without parsing the graph."""
+    from .keras_config import retinanet_config
+    return {"class_name": "Model", "config": retinanet_config(model), "keras_version": KERAS_VERSION.decode(),
+            "backend": BACKEND.decode(), "b200": {"backbone": model.backbone_name, "num_classes": model.num_classes}}
 
 
 def trainable_weight_list(model):
@@ -223,7 +224,7 @@ def load_full_model(path: str, backbone_name: str = "resnet50", num_classes: int
     with H5File(path, "r") as f:
         names = f.attr_names("/")
         cfg = json.loads(bytes(f.attr("/", "model_config")).decode()) if "model_config" in names else {}
-        c = cfg.get("config", {})
+        c = cfg.get("b200") or cfg.get("config", {})          # "config" held these keys in files written before round 2
         backbone_name = c.get("backbone", backbone_name)
         if num_classes is None:
             num_classes = c.get("num_classes")

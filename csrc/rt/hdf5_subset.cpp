@@ -126,8 +126,34 @@ void add_message(std::vector<uint8_t>& body, uint16_t type, const std::vector<ui
   ++count;
 }
 
-std::vector<uint8_t> encode_attr(const Attr& a) {
-  std::vector<uint8_t> dt = encode_datatype(a.type), ds = encode_dataspace(a.dims), m;
+// Scalar byte strings are stored the way h5py stores a Python `bytes` / `str` attribute (Keras' keras_version, backend,
+// model_config, training_config): a VARIABLE-LENGTH string whose characters live in a global heap collection and whose
+// attribute message holds a 16-byte reference.  That is also the only way a 100 KB model_config fits: a version-1
+// header message cannot exceed 64 KiB.
+struct VlenRef {
+  uint64_t heap_addr = 0;
+  uint32_t index = 0;
+};
+
+bool is_vlen_scalar(const Attr& a) { return a.type.cls == 2 && a.dims.empty(); }
+
+std::vector<uint8_t> encode_vlen_string_type() {
+  std::vector<uint8_t> m;
+  put8(m, 0x10 | 9);   // version 1, class 9 variable-length
+  put8(m, 0x01);       // type: string; padding: null-terminated
+  put8(m, 0x00);       // character set: ASCII
+  put8(m, 0);
+  put32(m, 16);        // size of the in-file descriptor: length, heap address, object index
+  put8(m, 0x10 | 3);   // base type: 1-byte null-terminated ASCII string
+  put8(m, 0);
+  put8(m, 0);
+  put8(m, 0);
+  put32(m, 1);
+  return m;
+}
+
+std::vector<uint8_t> encode_attr(const Attr& a, const VlenRef* ref = nullptr) {
+  std::vector<uint8_t> dt = ref ? encode_vlen_string_type() : encode_datatype(a.type), ds = encode_dataspace(a.dims), m;
   put8(m, 1);
   put8(m, 0);
   put16(m, static_cast<uint16_t>(a.name.size() + 1));
@@ -139,7 +165,13 @@ std::vector<uint8_t> encode_attr(const Attr& a) {
   pad8(m);
   put(m, ds.data(), ds.size());
   pad8(m);
-  put(m, a.data.data(), a.data.size());
+  if (ref) {
+    put32(m, static_cast<uint32_t>(a.data.size()));
+    put64(m, ref->heap_addr);
+    put32(m, ref->index);
+  } else {
+    put(m, a.data.data(), a.data.size());
+  }
   return m;
 }
 
@@ -169,9 +201,54 @@ struct Writer {
     return a;
   }
 
+  // ---- global heap: one collection with every variable-length string of the file, allocated before the objects
+  std::map<const Attr*, VlenRef> vlen;
+
+  void collect_vlen(const Node& n, std::vector<const Attr*>& out) {
+    for (const Attr& a : n.attrs)
+      if (is_vlen_scalar(a)) out.push_back(&a);
+    for (auto& kv : n.children) collect_vlen(*kv.second, out);
+  }
+
+  void write_global_heap(const Node& root) {
+    std::vector<const Attr*> all;
+    collect_vlen(root, all);
+    if (all.empty()) return;
+    size_t need = 16 + 16;                       // collection header + the free-space object
+    for (const Attr* a : all) need += 16 + ((a->data.size() + 7) & ~size_t(7));
+    const size_t size = need < 4096 ? 4096 : ((need + 4095) & ~size_t(4095));     // libhdf5's minimum collection size
+    std::vector<uint8_t> g;
+    put(g, "GCOL", 4);
+    put8(g, 1); put8(g, 0); put8(g, 0); put8(g, 0);
+    put64(g, size);
+    const uint64_t addr = alloc(size);
+    uint16_t idx = 1;
+    for (const Attr* a : all) {
+      put16(g, idx);
+      put16(g, 1);                               // reference count
+      put32(g, 0);
+      put64(g, a->data.size());
+      put(g, a->data.data(), a->data.size());
+      pad8(g);
+      vlen[a] = VlenRef{addr, idx};
+      ++idx;
+    }
+    const size_t free_bytes = size - g.size();
+    put16(g, 0);                                 // object 0: the free space, its size counts its own header
+    put16(g, 0);
+    put32(g, 0);
+    put64(g, free_bytes);
+    write_at(addr, g);
+  }
+
+  std::vector<uint8_t> attr_message(const Attr& a) {
+    auto it = vlen.find(&a);
+    return encode_attr(a, it == vlen.end() ? nullptr : &it->second);
+  }
+
   bool attrs_fit(const Node& n, std::string& why) {
     for (const Attr& a : n.attrs)
-      if (encode_attr(a).size() + 8 > 65000) {
+      if (attr_message(a).size() + 8 > 65000) {
         why = "attribute '" + a.name + "' exceeds the 64 KiB object-header message limit (split it, as Keras does for layer_names)";
         return false;
       }
@@ -199,7 +276,7 @@ struct Writer {
       put64(lay, daddr);
       put64(lay, n.data.size());
       add_message(body, 0x0008, lay, cnt);
-      for (const Attr& a : n.attrs) add_message(body, 0x000C, encode_attr(a), cnt);
+      for (const Attr& a : n.attrs) add_message(body, 0x000C, attr_message(a), cnt);
       return n.header_addr = write_header(body, cnt);
     }
     // children first
@@ -286,7 +363,7 @@ struct Writer {
     put64(st, bt_addr);
     put64(st, heap_addr);
     add_message(body, 0x0011, st, cnt);
-    for (const Attr& a : n.attrs) add_message(body, 0x000C, encode_attr(a), cnt);
+    for (const Attr& a : n.attrs) add_message(body, 0x000C, attr_message(a), cnt);
     n.header_addr = write_header(body, cnt);
     btree_of[n.header_addr] = {bt_addr, heap_addr};
     return n.header_addr;
@@ -296,6 +373,7 @@ struct Writer {
 
   bool write_file(Node& root, const std::string& path) {
     file.assign(96, 0);
+    write_global_heap(root);
     const uint64_t root_addr = write_node(root);
     if (root_addr == UNDEF) return false;
     while (file.size() % 8) file.push_back(0);

@@ -18,6 +18,9 @@ What is reproduced of libhdf5's habits (each one a place where a reader written 
 * "old-style" groups: symbol-table message -> v1 B-tree node (``TREE``, 2K+1 keys) -> symbol-table nodes (``SNOD``, at
   most 2 * leaf K = 8 entries each, so 9+ links give several leaves) -> names in a local heap (``HEAP``) with a free
   block at the end; group entries carry cache type 1, dataset entries cache type 0;
+* Python ``bytes`` attributes (``backend``, ``keras_version``: h5py maps a bytes scalar to a VARIABLE-LENGTH string) as
+  class-9 datatypes whose characters sit in a global heap collection (``GCOL``, 4096 bytes, free-space object last) and
+  whose attribute data is the 16-byte (length, collection address, object index) reference;
 * datasets allocated AFTER all metadata of their group, 8-byte aligned, little-endian IEEE floats with the full
   12-byte floating-point property block.
 """
@@ -59,6 +62,15 @@ def _space_msg(shape) -> bytes:
     out += b"".join(struct.pack("<Q", d) for d in shape)
     out += b"".join(struct.pack("<Q", d) for d in shape)
     return out
+
+
+def _vlen_attr_msg(name: str, length: int, heap_addr: int, index: int) -> bytes:
+    nm = name.encode() + b"\0"
+    # class 9 (variable length), type = string, null-terminated, ASCII; descriptor size 16; base type: 1-byte string
+    dt = struct.pack("<BBBBI", 0x19, 0x01, 0x00, 0, 16) + struct.pack("<BBBBI", 0x13, 0x00, 0, 0, 1)
+    sp = _space_msg(())
+    body = struct.pack("<BBHHH", 1, 0, len(nm), len(dt), len(sp))
+    return body + _pad8(nm) + _pad8(dt) + _pad8(sp) + struct.pack("<IQI", length, heap_addr, index)
 
 
 def _attr_msg(name: str, value) -> bytes:
@@ -112,8 +124,35 @@ class LibHdf5File:
         parent.children[parts[-1]] = _Node(False, np.ascontiguousarray(value))
 
     # ------------------------------------------------------------------ layout
+    def _vlen(self, data: bytes):
+        """Store ``data`` in the file's global heap collection (created on first use); returns (address, index)."""
+        if self._gcol is None:
+            self._gcol = self._alloc(4096)
+            self._gcol_used, self._gcol_next = 16, 1
+        size = 16 + len(_pad8(data))
+        assert self._gcol_used + size + 16 <= 4096, "fixture builder: one global heap collection only"
+        at = self._gcol + self._gcol_used
+        self._put(at, struct.pack("<HHIQ", self._gcol_next, 1, 0, len(data)) + data)
+        self._gcol_used += size
+        idx, self._gcol_next = self._gcol_next, self._gcol_next + 1
+        free = 4096 - self._gcol_used
+        self._put(self._gcol, b"GCOL" + struct.pack("<B3xQ", 1, 4096))
+        self._put(self._gcol + self._gcol_used, struct.pack("<HHIQ", 0, 0, 0, free))
+        return self._gcol, idx
+
+    def _attr_messages(self, node):
+        out = []
+        for n, v in node.attrs:
+            if isinstance(v, bytes):             # what h5py does with a Python bytes scalar
+                addr, idx = self._vlen(v)
+                out.append(_msg(0x000C, _vlen_attr_msg(n, len(v), addr, idx)))
+            else:
+                out.append(_msg(0x000C, _attr_msg(n, v)))
+        return out
+
     def tobytes(self) -> bytes:
         self.buf = bytearray(96)                 # superblock v0 is 96 bytes; the root object header follows it
+        self._gcol = None
         self._emit_group(self.root)
         eof = len(self.buf)
         sb = b"\x89HDF\r\n\x1a\n" + struct.pack("<BBBBBBBB", 0, 0, 0, 0, 0, 8, 8, 0)
@@ -163,9 +202,8 @@ class LibHdf5File:
 
     def _emit_group(self, g: _Node):
         names = sorted(g.children)                           # symbol-table entries are kept in name order
-        attr_msgs = [_msg(0x000C, _attr_msg(n, v)) for n, v in g.attrs]
         # a fresh group header has room for the symbol-table message (24 bytes) and little else
-        g.addr, finish = self._object_header(24, bool(attr_msgs), spare=16)
+        g.addr, finish = self._object_header(24, bool(g.attrs), spare=16)
         # B-tree node: 2K + 1 keys and 2K children are always allocated
         g.btree = self._alloc(24 + (2 * INTERNAL_K + 1) * 8 + 2 * INTERNAL_K * 8)
         # local heap: header, then the data segment (empty name at offset 0, names 8-byte aligned, free block last)
@@ -206,7 +244,7 @@ class LibHdf5File:
         node += struct.pack("<Q", keys[len(leaves)])
         self._put(g.btree, node)
         # the attributes were added last (Keras writes them after the weights): continuation block at the end
-        finish([_msg(0x0011, struct.pack("<QQ", g.btree, g.heap))], attr_msgs)
+        finish([_msg(0x0011, struct.pack("<QQ", g.btree, g.heap))], self._attr_messages(g))
 
     def _emit_dataset(self, d: _Node):
         arr = d.value
@@ -214,7 +252,7 @@ class LibHdf5File:
         dtype = _msg(0x0003, _dtype_msg(arr.dtype), flags=1)         # constant message
         fill = _msg(0x0005, struct.pack("<BBBB", 2, 2, 2, 1) + struct.pack("<I", 0))
         mtime = _msg(0x0012, struct.pack("<B3xI", 1, 1541548800))
-        attr_msgs = [_msg(0x000C, _attr_msg(n, v)) for n, v in d.attrs]
+        attr_msgs = self._attr_messages(d)
         layout_len = len(_msg(0x0008, struct.pack("<BBQQ", 3, 1, 0, 0)))
         d.addr, finish = self._object_header(len(space) + len(dtype) + len(fill) + layout_len + len(mtime), bool(attr_msgs))
         data = self._alloc(arr.nbytes) if arr.nbytes else UNDEF      # raw data after the header, 8-byte aligned

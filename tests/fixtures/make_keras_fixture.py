@@ -37,8 +37,8 @@ def values(name: str, shape):
 def build() -> bytes:
     f = LibHdf5File()
     f.attr("/", "layer_names", np.array([n.encode() for n, _ in LAYERS]))
-    f.attr("/", "backend", np.bytes_(b"tensorflow"))
-    f.attr("/", "keras_version", np.bytes_(b"2.1.6"))
+    f.attr("/", "backend", b"tensorflow")            # Python bytes -> variable-length strings in the global heap
+    f.attr("/", "keras_version", b"2.1.6")
     for layer, weights in LAYERS:
         f.group("/" + layer)
         if weights:

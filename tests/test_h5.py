@@ -37,7 +37,7 @@ def test_raw_roundtrip_and_structure(tmp_path):
         assert [bytes(x) for x in f.attr("/", "layer_names")] == [b"conv1", b"bn_conv1_long_name"]
         assert np.allclose(f.attr("/", "vec"), [1.5, 2.5])
         assert np.array_equal(f.dataset("/conv1/conv1/kernel:0"), a)
-        assert int(f.dataset("/opt/iterations:0")) == 7
+        assert int(np.asarray(f.dataset("/opt/iterations:0")).reshape(-1)[0]) == 7
         assert len(f.keys("/many")) == 70 and f.keys("/many")[0] == "d000"
         assert np.array_equal(f.dataset("/many/d069"), np.full((3,), 69.0))
         assert f.is_group("/conv1/conv1") and not f.is_group("/conv1/conv1/kernel:0")
@@ -149,6 +149,8 @@ def test_foreign_layout_fixture_structure():
     name_size, = struct.unpack_from("<H", raw, cont + 8 + 2)
     assert raw[cont + 16:cont + 16 + 12] == b"layer_names\0" and name_size == 12      # 12 bytes, padded to 16
     assert nmsg == 3 + 3 + 1
+    at = raw.index(b"GCOL")                                   # backend / keras_version: variable-length strings
+    assert struct.unpack_from("<Q", raw, at + 8)[0] == 4096 and raw[at + 16 + 16:at + 16 + 26] == b"tensorflow"
     with H5File(mk.PATH, "r") as f:
         assert f.keys("/") == sorted(n for n, _ in mk.LAYERS)
         assert [bytes(x).decode() for x in f.attr("/", "layer_names")] == [n for n, _ in mk.LAYERS]
