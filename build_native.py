@@ -48,12 +48,14 @@ def build(verbose: bool = False) -> dict:
     cu = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
     jobs = []
     objs = []
+    trace = os.environ.get("B200_CONV_TRACE", "0") == "1"      # in-kernel timeline of the conv kernel (scripts/conv_timeline.py)
     for f in cu:
         src = os.path.join(CSRC, f)
-        obj = os.path.join(OBJ, f[:-3] + ".o")
+        traced = trace and f == "conv_sm100.cu"
+        obj = os.path.join(OBJ, f[:-3] + (".trace.o" if traced else ".o"))
         objs.append(obj)
         if _stale(src, obj, headers):
-            jobs.append(([NVCC] + NVCC_FLAGS + ["-c", src, "-o", obj], obj + ".log"))
+            jobs.append(([NVCC] + NVCC_FLAGS + (["-DB200_CONV_TRACE"] if traced else []) + ["-c", src, "-o", obj], obj + ".log"))
     rt_dir = os.path.join(CSRC, "rt")
     rt_objs = []
     if os.path.isdir(rt_dir):

@@ -177,6 +177,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   const uint32_t crank = pair ? cluster_ctarank() : 0u;
   // pair mode: the odd CTA's last tile may lie past the end (every role but the weight ring skips it)
   auto is_dummy = [&](int tile) { return pair && (tile % p.num_m_tiles) >= p.real_m_tiles; };
+  // in-kernel timeline (build with -DB200_CONV_TRACE: B200_CONV_TRACE=1 python build_native.py); compiled out by
+  // default, the pointer alone costs the epilogue warps two registers
+#ifdef B200_CONV_TRACE
   long long* const tr = p.trace ? p.trace + static_cast<size_t>(blockIdx.x) * 16 : nullptr;
 #define B200_TR(i) do { if (tr) tr[i] = clock64(); } while (0)
   if (tr && threadIdx.x == 0) {
@@ -185,6 +188,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     tr[0] = static_cast<long long>(gt);
     tr[1] = clock64();
   }
+#else
+#define B200_TR(i) do { } while (0)
+#endif
   const int gsz = p.gsz, kgroups = p.kgroups;
   const int num_groups = p.tap_groups * kgroups;          // activation boxes per tile
   const int num_substeps = p.num_taps * p.num_kc;         // weight tiles per tile
@@ -195,34 +201,46 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   // sub-steps of k group kg (the last group of a tap may be short in kc mode)
   auto nsub = [&](int kg) { return p.mode == 2 ? min(gsz, p.num_kc - kg * gsz) : gsz; };
 
-  if (warp == 0 && lane == 0) {
-    for (int i = 0; i < kMaxMaps; ++i) tma_prefetch_desc(&p.in_maps[i]);
-    tma_prefetch_desc(&p.w_map);
-    for (int i = 0; i < p.num_problems; ++i) {
-      tma_prefetch_desc(&p.out_maps[i]);
-      if (kAdd) tma_prefetch_desc(&p.add_maps[i]);
-      if (kMask) tma_prefetch_desc(&p.mask_maps[i]);
+  // Set-up is on the critical path of every launch (one CTA per SM with ~227 KB of shared memory: the next kernel's
+  // CTAs cannot become resident before this one's exit, so programmatic launch overlaps little of it).  The in-kernel
+  // timeline showed 1.8k cycles to the first __syncthreads and 2.2k more before the first TMA issue, most of it one
+  // thread initialising 76 barriers and dependent constant-bank misses in decode_tile: spread both over lanes / warps.
+  if (warp == 0) {
+    // one descriptor per lane: in_maps[0..7], w_map, then out / add / mask per problem
+    const void* d = nullptr;
+    if (lane < kMaxMaps) d = &p.in_maps[lane];
+    else if (lane == kMaxMaps) d = &p.w_map;
+    else if (lane < kMaxMaps + 1 + 3 * B200_MAX_PROBLEMS) {
+      const int k = lane - kMaxMaps - 1, i = k / 3, which = k - 3 * i;
+      if (i < p.num_problems) {
+        if (which == 0) d = &p.out_maps[i];
+        else if (which == 1 && kAdd) d = &p.add_maps[i];
+        else if (which == 2 && kMask) d = &p.mask_maps[i];
+      }
     }
+    if (d) tma_prefetch_desc(d);
   }
-  if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kMaxAStages; ++s) {
-      mbar_init(afull_bar(s), 1);
-      mbar_init(aempty_bar(s), 1);
-    }
-    for (int s = 0; s < kMaxBStages; ++s) {
-      mbar_init(bfull_bar(s), 1);
-      mbar_init(bempty_bar(s), pair ? 2 : 1);       // pair mode: both CTAs' MMA warps release a stage
-    }
-    for (int a = 0; a < 2; ++a) {
-      mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 32 * kEpiWarps);
-    }
-    for (int s = 0; s < kMaxSlots; ++s) {
-      mbar_init(ldfull_bar(s), 1);
-      mbar_init(free_bar(s), 1);
-      mbar_init(stfull_bar(s), 256);
+  if (warp == 1) {
+    // barrier k sits at bar_base + 8 k: [0,12) activation full / empty, [12,24) weight full, [24,36) weight empty,
+    // 36-37 accumulator full, 38-39 accumulator empty, [40,52) operand landed, [52,64) slot free, [64,76) chunk complete
+    for (int k = lane; k < 76; k += 32) {
+      uint32_t count = 1;
+      if (k >= 24 && k < 36) count = pair ? 2 : 1;      // pair mode: both CTAs' MMA warps release a weight stage
+      else if (k == 38 || k == 39) count = 32 * kEpiWarps;
+      else if (k >= 64) count = 256;
+      mbar_init(bar_base + 8u * k, count);
     }
     fence_barrier_init();
+  }
+  // first tile of this CTA, decoded by the producer warp while the other warps set up (warms the constant bank)
+  // (results parked in the spare bytes after the barriers, not in registers every warp would have to carry)
+  const uint32_t t0_smem = bar_base + 616u;
+  if (warp == 0 && lane == 0 && static_cast<int>(blockIdx.x) < total_tiles && !is_dummy(blockIdx.x)) {
+    int pi, n, y0, x0, nt;
+    decode_tile(p, blockIdx.x, pi, n, y0, x0, nt);
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(t0_smem), "r"(pi), "r"(n) : "memory");
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(t0_smem + 8u), "r"(y0), "r"(x0) : "memory");
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(t0_smem + 16u), "r"(nt) : "memory");
   }
   if (warp == 2) {
     tmem_alloc(tmem_ptr_smem, kTmemCols);
@@ -249,7 +267,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         if (is_dummy(tile)) continue;
         int pi, n, y0, x0, n_tile;
-        decode_tile(p, tile, pi, n, y0, x0, n_tile);
+        if (tile == static_cast<int>(blockIdx.x)) {
+          asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(pi), "=r"(n) : "r"(t0_smem) : "memory");
+          asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(y0), "=r"(x0) : "r"(t0_smem + 8u) : "memory");
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(n_tile) : "r"(t0_smem + 16u) : "memory");
+        } else {
+          decode_tile(p, tile, pi, n, y0, x0, n_tile);
+        }
         const DevProblem& q = p.prob[pi];
         const uint32_t a_bytes = static_cast<uint32_t>(q.a_bytes);
         for (int t = 0; t < p.tap_groups; ++t) {
@@ -688,12 +712,14 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   __syncthreads();
   if (pair) cluster_sync_all();          // my shared memory stays alive until the partner has stopped writing into it
   if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+#ifdef B200_CONV_TRACE
   if (tr && threadIdx.x == 0) {
     unsigned long long gt;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
     tr[11] = clock64();
     tr[12] = static_cast<long long>(gt);
   }
+#endif
 #undef B200_TR
 }
 

@@ -1,4 +1,5 @@
 """In-kernel timeline of one conv launch (b200_conv_set_trace): where a CTA's first tile spends its cycles.
+Needs the traced build: B200_CONV_TRACE=1 python build_native.py (the default build compiles the stamps out).
 Usage: python scripts/conv_timeline.py [n h w cin cout k]   (default: res4 1x1 1024->256 at 8x50x84)"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
