@@ -18,7 +18,7 @@ for line in txt.splitlines():
     if cur and re.match(r"\s+/\*[0-9a-f]{4,}\*/", line):
         funcs[cur].append(re.sub(r"\s*/\* 0x[0-9a-f]+ \*/\s*$", "", line).rstrip())
 keys = ("UTCHMMA", "UTMALDG", "UTMASTG", "UTMAPF", "LDTM", "UTCBAR", "UTCATOMSWS", "SYNCS", "ELECT", "REDG", "RED.", "LDGMC",
-        "STRONG.SYS", "HMMA", "ACQBULK", "PREEXIT", "UTMACMDFLUSH", "FENCE")
+        "STRONG.SYS", "HMMA", "ACQBULK", "PREEXIT", "UTMACMDFLUSH", "FENCE", "MULTICAST", "UCGABAR")
 index = []
 for mangled, lines in funcs.items():
     name = demangle(mangled)
