@@ -37,6 +37,8 @@
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 
+#include <type_traits>
+
 namespace b200 {
 
 constexpr int kBM = 128;
@@ -310,30 +312,35 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       uint32_t pb = 0;
       const uint32_t half_off = crank * (b_bytes >> 1);
       const int half_row = static_cast<int>(crank) * (p.BN >> 1);
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int row0 = (tile / p.num_m_tiles) * p.BN;
-        for (int t = 0; t < p.tap_groups; ++t) {
-          for (int kg = 0; kg < kgroups; ++kg) {
-            const int ns = nsub(kg);
-            for (int j = 0; j < ns; ++j) {
-              const int widx = p.mode == 1 ? p.widx3[t][j] : p.taps[t].widx;
-              const int kc = p.mode == 2 ? kg * gsz + j : kg;
-              mbar_wait(bempty_bar(sb), pb ^ 1);
-              mbar_expect_tx(bfull_bar(sb), b_bytes);     // both halves: mine and the partner's
-              if (pair)
-                tma_load_3d_mc(b_smem + sb * p.b_stage_bytes + half_off, &p.w_map, bfull_bar(sb), kc * kBK, row0 + half_row,
-                               widx, static_cast<uint16_t>(3));
-              else
-                tma_load_3d(b_smem + sb * p.b_stage_bytes, &p.w_map, bfull_bar(sb), kc * kBK, row0, widx);
-              if (++sb == b_stages) {
-                sb = 0;
-                pb ^= 1;
+      auto produce = [&](auto pair_c) {          // `pair` resolved once, outside the issue loop (see the MMA warp)
+        constexpr bool kPair = decltype(pair_c)::value;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+          const int row0 = (tile / p.num_m_tiles) * p.BN;
+          for (int t = 0; t < p.tap_groups; ++t) {
+            for (int kg = 0; kg < kgroups; ++kg) {
+              const int ns = nsub(kg);
+              for (int j = 0; j < ns; ++j) {
+                const int widx = p.mode == 1 ? p.widx3[t][j] : p.taps[t].widx;
+                const int kc = p.mode == 2 ? kg * gsz + j : kg;
+                mbar_wait(bempty_bar(sb), pb ^ 1);
+                mbar_expect_tx(bfull_bar(sb), b_bytes);     // pair mode: both halves, mine and the partner's
+                if constexpr (kPair)
+                  tma_load_3d_mc(b_smem + sb * p.b_stage_bytes + half_off, &p.w_map, bfull_bar(sb), kc * kBK,
+                                 row0 + half_row, widx, static_cast<uint16_t>(3));
+                else
+                  tma_load_3d(b_smem + sb * p.b_stage_bytes, &p.w_map, bfull_bar(sb), kc * kBK, row0, widx);
+                if (++sb == b_stages) {
+                  sb = 0;
+                  pb ^= 1;
+                }
               }
             }
           }
+          if (!kPair && weights_resident) break;      // one pass filled every stage for good
         }
-        if (weights_resident) break;      // one pass filled every stage for good
-      }
+      };
+      if (pair) produce(std::true_type{});
+      else produce(std::false_type{});
       if (pair) {
         // every release the partner still owes my barriers has landed before either CTA may exit
         for (int i = 0; i < b_stages; ++i) {
@@ -365,87 +372,98 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       uint32_t acc_phase = 0;
       const bool one_problem = p.num_problems == 1;
       uint32_t sub_step = static_cast<uint32_t>(p.prob[0].sub_stride) >> 4;
-      auto next_b = [&]() {
-        b_cur += b_step;
-        bfull += 8;
-        bempty += 8;
-        if (++sb == b_stages) {
-          sb = 0;
-          pb ^= 1;
-          b_cur = b_first;
-          bfull = bfull_bar(0);
-          bempty = bempty_bar(0);
-          if (weights_resident) b_wait = false;
+      // The loop exists twice, selected ONCE outside it: with `pair` tested at every sub-step the compiler reloaded it
+      // (and the ring size) from the constant bank inside the issue loop and every N <= 128 layer lost 30 %.
+      auto issue_loop = [&](auto pair_c) {
+        constexpr bool kPair = decltype(pair_c)::value;
+        auto next_b = [&]() {
+          b_cur += b_step;
+          bfull += 8;
+          bempty += 8;
+          if (++sb == b_stages) {
+            sb = 0;
+            pb ^= 1;
+            b_cur = b_first;
+            bfull = bfull_bar(0);
+            bempty = bempty_bar(0);
+            if (!kPair && weights_resident) b_wait = false;
+          }
+        };
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+          const int n_tile = tile / p.num_m_tiles;
+          if (kPair && (tile - n_tile * p.num_m_tiles) >= p.real_m_tiles) {
+            // no pixels here: receive and release the shared weight tiles only
+            for (int j = 0; j < num_substeps; ++j) {
+              mbar_wait(bfull, pb);
+              umma_commit_mc(bempty, static_cast<uint16_t>(3));
+              next_b();
+            }
+            continue;
+          }
+          if (!one_problem) {               // halo tiles differ per pyramid level
+            int pi, n, y0, x0, nt2;
+            decode_tile(p, tile, pi, n, y0, x0, nt2);
+            sub_step = static_cast<uint32_t>(p.prob[pi].sub_stride) >> 4;
+          }
+          // the last N tile may be narrower: do not multiply zero-filled weight rows
+          const int cols = min(p.Nrows - n_tile * p.BN, p.BN);
+          const uint32_t idesc = make_idesc_bf16(kBM, max(16, (cols + 15) & ~15), 0, 0);
+          mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * 256;
+          uint32_t accumulate = 0;
+          int kg = 0;
+          for (int g = 0; g < num_groups; ++g) {
+            const int ns = p.mode == 2 ? min(gsz, p.num_kc - kg * gsz) : gsz;
+            if (++kg == kgroups) kg = 0;
+            mbar_wait(afull, pa);
+            tc_fence_after();
+            if (tile == static_cast<int>(blockIdx.x) && g == 0) B200_TR(4);
+            if (tile == static_cast<int>(blockIdx.x) && g == num_groups - 1) B200_TR(13);
+            uint32_t a_sub = a_cur;
+            for (int j = 0; j < ns; ++j) {
+              if (kPair || b_wait) {
+                mbar_wait(bfull, pb);
+                tc_fence_after();
+                if (tile == static_cast<int>(blockIdx.x) && g == 0 && j == 0) B200_TR(5);
+              }
+              const uint64_t adesc = desc_hi | a_sub, bdesc = desc_hi | b_cur;
+#pragma unroll
+              for (int k = 0; k < kBK / 16; ++k) {
+                // advance 16 bf16 = 32 bytes along K inside the 128B swizzle row: +2 in (addr >> 4) units
+                umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, accumulate | k);
+              }
+              if constexpr (kPair) {
+                umma_commit_mc(bempty, static_cast<uint16_t>(3));
+              } else {
+                if (!weights_resident) umma_commit(bempty);
+              }
+              accumulate = 1;
+              a_sub += sub_step;
+              next_b();
+            }
+            umma_commit(aempty);
+            if (g == num_groups - 1) {
+              umma_commit(tfull_bar(acc));
+              B200_TR(tile == static_cast<int>(blockIdx.x) ? 6 : 9);
+            }
+            a_cur += a_step;
+            afull += 8;
+            aempty += 8;
+            if (++sa == a_stages) {
+              sa = 0;
+              pa ^= 1;
+              a_cur = a_first;
+              afull = afull_bar(0);
+              aempty = aempty_bar(0);
+            }
+          }
+          acc ^= 1;
+          if (acc == 0) acc_phase ^= 1;
         }
       };
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int n_tile = tile / p.num_m_tiles;
-        if (is_dummy(tile)) {             // no pixels here: receive and release the shared weight tiles only
-          for (int j = 0; j < num_substeps; ++j) {
-            mbar_wait(bfull, pb);
-            umma_commit_mc(bempty, static_cast<uint16_t>(3));
-            next_b();
-          }
-          continue;
-        }
-        if (!one_problem) {               // halo tiles differ per pyramid level
-          int pi, n, y0, x0, nt2;
-          decode_tile(p, tile, pi, n, y0, x0, nt2);
-          sub_step = static_cast<uint32_t>(p.prob[pi].sub_stride) >> 4;
-        }
-        // the last N tile may be narrower: do not multiply zero-filled weight rows
-        const int cols = min(p.Nrows - n_tile * p.BN, p.BN);
-        const uint32_t idesc = make_idesc_bf16(kBM, max(16, (cols + 15) & ~15), 0, 0);
-        mbar_wait(tempty_bar(acc), acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * 256;
-        uint32_t accumulate = 0;
-        int kg = 0;
-        for (int g = 0; g < num_groups; ++g) {
-          const int ns = p.mode == 2 ? min(gsz, p.num_kc - kg * gsz) : gsz;
-          if (++kg == kgroups) kg = 0;
-          mbar_wait(afull, pa);
-          tc_fence_after();
-          if (tile == static_cast<int>(blockIdx.x) && g == 0) B200_TR(4);
-          if (tile == static_cast<int>(blockIdx.x) && g == num_groups - 1) B200_TR(13);
-          uint32_t a_sub = a_cur;
-          for (int j = 0; j < ns; ++j) {
-            if (b_wait) {
-              mbar_wait(bfull, pb);
-              tc_fence_after();
-              if (tile == static_cast<int>(blockIdx.x) && g == 0 && j == 0) B200_TR(5);
-            }
-            const uint64_t adesc = desc_hi | a_sub, bdesc = desc_hi | b_cur;
-#pragma unroll
-            for (int k = 0; k < kBK / 16; ++k) {
-              // advance 16 bf16 = 32 bytes along K inside the 128B swizzle row: +2 in (addr >> 4) units
-              umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, accumulate | k);
-            }
-            if (pair) umma_commit_mc(bempty, static_cast<uint16_t>(3));
-            else if (!weights_resident) umma_commit(bempty);
-            accumulate = 1;
-            a_sub += sub_step;
-            next_b();
-          }
-          umma_commit(aempty);
-          if (g == num_groups - 1) {
-            umma_commit(tfull_bar(acc));
-            B200_TR(tile == static_cast<int>(blockIdx.x) ? 6 : 9);
-          }
-          a_cur += a_step;
-          afull += 8;
-          aempty += 8;
-          if (++sa == a_stages) {
-            sa = 0;
-            pa ^= 1;
-            a_cur = a_first;
-            afull = afull_bar(0);
-            aempty = aempty_bar(0);
-          }
-        }
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1;
-      }
+      if (pair) issue_loop(std::true_type{});
+      else issue_loop(std::false_type{});
     }
   } else if (warp == 2) {
     // ------------------------------------------------------------------ store issuer (one thread)
@@ -1023,7 +1041,16 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
     pair_env = (e && e[0] == '0') ? 0 : 1;
   }
   const bool streamed = !(p.num_n_tiles == 1 && b_st == num_substeps);
-  p.pair = (pair_env && streamed && (p.BN % 16) == 0 && num_sms() >= 4) ? 1 : 0;
+  // The two CTAs of a pair advance through the weight ring in lock step, so a stall of one stalls both; that coupling
+  // costs ~8 % on launches of two or three waves (measured on the res4 3x3 layers) and nothing on long ones.
+  static int pair_min_waves = -1;
+  if (pair_min_waves < 0) {
+    const char* e = getenv("B200_CONV_PAIR_MIN_WAVES");
+    pair_min_waves = e ? atoi(e) : 4;
+  }
+  const long long tiles_all = static_cast<long long>(p.real_m_tiles) * p.num_n_tiles;
+  p.pair = (pair_env && streamed && (p.BN % 16) == 0 && num_sms() >= 4 &&
+            tiles_all >= static_cast<long long>(pair_min_waves) * num_sms()) ? 1 : 0;
   if (p.pair) p.num_m_tiles = (p.real_m_tiles + 1) & ~1;
   {
     unsigned long long dims[3] = {static_cast<unsigned long long>(a->K), static_cast<unsigned long long>(a->Nrows),

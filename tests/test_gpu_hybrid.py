@@ -157,3 +157,51 @@ def test_mobilenet_native_forward_wiring():
     assert max(errs[:6]) < 1e-2, errs           # blocks 1-3, both strides
     assert errs[-1] < 0.5, errs                 # still the same function at the end (a wiring bug gives ~1.4)
     assert torch.allclose(model.backbone.conv1_bn.moving_mean.float(), ref.backbone.conv1_bn.moving_mean, atol=1e-3)
+
+
+def test_densenet_native_forward_wiring():
+    """DenseNetTrainer's forward (stem kernel without ReLU, batch-norm + ReLU kernels on channel-slice views, tcgen05
+    1x1 / 3x3 convs storing into slices of the concatenation buffer, average-pool transition) against a PyTorch
+    restatement with the engine's rounding points, on the first dense block and the first transition."""
+    import copy
+    import torch.nn.functional as F
+    from batchai_retinanet_horovod_coco_b200.engine.densenet_native import DenseNetTrainer
+    B, H, W = 2, 160, 224
+    model = _model("densenet121")
+    ref = copy.deepcopy(model).cuda().float()
+    img, gt, cnt, hw = _inputs(B, H, W)
+    nt = DenseNetTrainer(model=model, device="cuda", batch=B, image_hw=(H, W), shape_bucket=1, use_graph=False)
+    _, p = nt.forward_loss(img, gt, cnt, hw)
+    torch.cuda.synchronize()
+    bb = ref.backbone
+    bb.train()
+    R = lambda t: t.to(torch.bfloat16).float()
+
+    def conv(c, x):
+        return R(F.conv2d(x, R(c.weight.data), None, c.stride, c.padding))
+
+    def rel(a, b):
+        a, b = a.float(), b.float().permute(0, 2, 3, 1)
+        assert a.shape == b.shape, (a.shape, b.shape)
+        return ((a - b).norm() / (b.norm() + 1e-9)).item()
+
+    x = R((img.cuda().permute(0, 3, 1, 2).float() - 127.5) * (1.0 / 127.5))
+    raw = conv(bb.conv1, x)
+    assert rel(p["dn_raw0"], raw) < 1e-3
+    x = R(F.relu(bb.bn1(raw)))
+    assert rel(p["dn_act0"], x) < 2e-3
+    x = F.max_pool2d(F.pad(x, (1, 1, 1, 1)), 3, 2)
+    assert rel(p["dn_pool"], x) < 2e-3
+    errs = []
+    for li, l in enumerate(bb.dense[0]):
+        t0 = R(F.relu(l.bn0(x)))
+        y1 = conv(l.conv1, t0)
+        t1 = R(F.relu(l.bn1(y1)))
+        x = torch.cat([x, conv(l.conv2, t1)], dim=1)
+        errs.append(rel(p["dn"][0]["cat"][..., :x.shape[1]], x))
+    assert max(errs) < 1e-2, errs
+    t = bb.trans[0]
+    y = F.avg_pool2d(conv(t.conv, R(F.relu(t.bn(x)))), 2, 2)
+    c = y.shape[1]
+    assert rel(p["dn"][1]["cat"][..., :c], R(y)) < 1e-2
+    assert torch.allclose(model.backbone.bn1.moving_mean.float(), ref.backbone.bn1.moving_mean, atol=1e-3)
