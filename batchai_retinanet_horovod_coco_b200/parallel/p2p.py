@@ -284,7 +284,13 @@ class P2PComm:
 
     # ---- allreduce split around backward: scatter raw slices as they become final, reduce + gather at the end
     def can_stage(self) -> bool:
-        return self.world > 1 and not self.external_sync and os.environ.get("B200_AR_OVERLAP", "1") != "0"
+        """The staged (scatter-during-backward) path.  ``B200_AR_OVERLAP=1`` / ``0`` forces it on / off; by default it
+        is used from 4 ranks up: measured at per-GPU batch 16, it is worth 0.05 ms per step on 8 GPUs and costs
+        0.15 ms on 2 (one peer: the plain push allreduce is already only ~0.2 ms there)."""
+        if self.world < 2 or self.external_sync:
+            return False
+        env = os.environ.get("B200_AR_OVERLAP")
+        return self.world >= 4 if env is None else env != "0"
 
     def scatter(self, n: int, lo: int, hi: int, stream=None):
         """Send elements [lo, hi) of the bucket (final on this rank, NOT yet clipped) to the staging area of their
@@ -307,7 +313,7 @@ class P2PComm:
         ``hvd.Compression.fp16`` selects for CUDA tensors; otherwise the auto-chosen fused kernel."""
         n4 = (n + 3) // 4 * 4
         post = (1.0 / self.world) if average else 1.0
-        if half_wire and self.can_stage():
+        if half_wire and self.world > 1 and not self.external_sync:
             a = self._args(self.result, offset, n4, post, False, 0, push=True, advance=False)
             a.wire_bf16 = 1
             native.ar_scatter(a, 0, n4)

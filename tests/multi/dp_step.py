@@ -1,6 +1,7 @@
 """2-rank data-parallel native step == single-process step on the concatenated batch (same clip semantics
 are NOT expected: clipping is per-rank, so compare with clipnorm disabled)."""
 import os, sys
+os.environ.setdefault("B200_AR_OVERLAP", "1")     # exercised here at 2 ranks; the default switches it on from 4 ranks up
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch, torch.distributed as dist
 from batchai_retinanet_horovod_coco_b200.models.retinanet import RetinaNet
@@ -32,7 +33,7 @@ gavg = nt.Gavg[:nt.n_train].clone()
 ref = gavg.clone(); dist.broadcast(ref, 0)
 assert torch.equal(ref, gavg), "averaged gradients differ between ranks"
 # the overlapped (scatter during backward + staged reduce) result equals a plain allreduce of the same bucket
-assert nt._overlap(), "the distributed engine should use the overlapped allreduce by default"
+assert nt._overlap(), "B200_AR_OVERLAP=1 must select the overlapped allreduce"
 plain = torch.zeros(nt.n_train + 64, device=dev)
 nt.comm.allreduce_avg(nt.G, plain, nt.n_train, prescale=True, algo=2)
 torch.cuda.synchronize()
