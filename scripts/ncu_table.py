@@ -4,7 +4,7 @@ import csv, io, subprocess, sys
 rep = sys.argv[1]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
-hdr = rows[0]
+hdr, units = rows[0], rows[1]
 def col(name):
     for i, h in enumerate(hdr):
         if h == name or h.endswith("." + name):
@@ -16,10 +16,13 @@ last = {}
 for n, r in enumerate(rows[2:]):
     last[(n, r[ki]) if ALL else r[ki]] = r
 stall_cols = [(i, h.split("stalled_")[-1]) for i, h in enumerate(hdr) if "pcsamp_warps_issue_stalled" in h and "not_issued" not in h]
+_SCALE = {"ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "s": 1e6, "second": 1e6,
+          "byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}
 def f(r, name, scale=1.0, fmt="{:.1f}"):
     c = col(name)
     try:
-        return fmt.format(float(r[c].replace(",", "")) * scale)
+        # ncu picks the unit per column (us or ms, Mbyte or Gbyte): normalise times to us and sizes to MB
+        return fmt.format(float(r[c].replace(",", "")) * scale * _SCALE.get(units[c], 1.0))
     except Exception:
         return "-"
 print("| kernel | us | DRAM rd MB | DRAM wr MB | DRAM % | L2 % | tensor % | regs | smem KB | top stalls |")
