@@ -830,6 +830,22 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   p.num_problems = a->num_problems;
   p.Nrows = a->Nrows;
   p.BN = pick_bn(a->Nrows);
+  {
+    // Small problems (batch 1: res4 has 33 pixel tiles, res5 nine) leave most SMs idle and the K loop of one wide tile
+    // is the whole kernel: split the output channels over more CTAs (N tiles of 128 or 64 columns; activation tiles
+    // are re-read from L2, which is cheap at this size).  B200_CONV_SPLIT_N=0 keeps 256-column tiles.
+    const char* e = getenv("B200_CONV_SPLIT_N");
+    if (!(e && e[0] == '0') && a->Nrows >= 128) {
+      long long m_tiles = 0;
+      for (int i = 0; i < a->num_problems; ++i) {
+        const B200ConvProblem& q = a->prob[i];
+        long long px = static_cast<long long>(q.N) * q.OHo * q.OWo;
+        if (a->mode == 1 && a->stride == 2) px = (px + 3) / 4;          // one parity class per launch
+        m_tiles += (px + kBM - 1) / kBM;
+      }
+      while (p.BN > 64 && m_tiles * ((a->Nrows + p.BN - 1) / p.BN) * 2 < num_sms()) p.BN = p.BN > 128 ? 128 : 64;
+    }
+  }
   p.num_n_tiles = (a->Nrows + p.BN - 1) / p.BN;
   p.num_kc = (a->K + kBK - 1) / kBK;
   p.shift = a->shift;
@@ -1051,6 +1067,17 @@ extern "C" int b200_conv(const B200ConvArgs* a, void* stream_) {
   const long long tiles_all = static_cast<long long>(p.real_m_tiles) * p.num_n_tiles;
   p.pair = (pair_env && streamed && (p.BN % 16) == 0 && num_sms() >= 4 &&
             tiles_all >= static_cast<long long>(pair_min_waves) * num_sms()) ? 1 : 0;
+  if (p.pair) {
+    // TMA multicast loads here read only this GPU's memory: the weights must be a device allocation of the current
+    // device (a peer mapping, an IPC mapping or managed memory falls back to per-CTA weight streams)
+    cudaPointerAttributes at;
+    int cur = -1;
+    if (cudaPointerGetAttributes(&at, a->weight) != cudaSuccess || cudaGetDevice(&cur) != cudaSuccess ||
+        at.type != cudaMemoryTypeDevice || at.device != cur) {
+      cudaGetLastError();
+      p.pair = 0;
+    }
+  }
   if (p.pair) p.num_m_tiles = (p.real_m_tiles + 1) & ~1;
   {
     unsigned long long dims[3] = {static_cast<unsigned long long>(a->K), static_cast<unsigned long long>(a->Nrows),

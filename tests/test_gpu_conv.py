@@ -100,6 +100,16 @@ def test_fprop(n, h, w, cin, cout, k, stride):
     _close(y[..., :cout], ref)
 
 
+@pytest.mark.parametrize("case", [(1, 25, 42, 256, 256, 3, 1), (2, 7, 11, 256, 720, 3, 1), (2, 13, 21, 256, 512, 1, 1),
+                                  (1, 24, 40, 256, 256, 3, 1)])
+def test_fprop_and_dgrad_with_wide_tiles_on_small_problems(case, monkeypatch):
+    """Small problems split their output channels into 128- / 64-column tiles by default (more CTAs); the 256-column
+    path they would otherwise take (resident or streamed weights, four chunks per tile) stays covered here."""
+    monkeypatch.setenv("B200_CONV_SPLIT_N", "0")
+    test_fprop(*case)
+    test_dgrad(*case)
+
+
 def test_fprop_epilogue():
     n, h, w, cin, cout = 2, 20, 30, 128, 256
     x = _mk(n, h, w, cin)
