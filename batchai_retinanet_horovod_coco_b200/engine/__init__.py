@@ -1,6 +1,7 @@
-"""Training engines: ``NativeTrainer`` (hand-written sm_100a kernels, the product), ``HybridTrainer``
-(same kernels for FPN / heads / losses / optimizer / allreduce, autograd for a MobileNet / DenseNet backbone),
-``VGGTrainer`` (VGG backbone on the same conv kernels), ``SpecTrainer``
+"""Training engines: ``NativeTrainer`` (hand-written sm_100a kernels, ResNet: the product), ``VGGTrainer`` /
+``MobileNetTrainer`` / ``DenseNetTrainer`` (the other backbone families on the same and on their own layer kernels),
+``HybridTrainer`` (their base class; alone: native FPN / heads / losses / optimizer / allreduce + an autograd
+backbone, the fallback for unknown backbone modules), ``SpecTrainer``
 (PyTorch autograd + KerasAdam + Horovod-style optimizer; CPU capable), ``LibraryTrainer`` (cuDNN +
 DDP/NCCL measured baseline)."""
 

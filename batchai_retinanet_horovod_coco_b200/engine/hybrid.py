@@ -1,4 +1,9 @@
-"""Engine for the non-ResNet backbones (VGG, MobileNet, DenseNet).
+"""Base class of the non-ResNet engines and fallback for a backbone without a native engine.
+
+Since round 2 every backbone family keras-retinanet offers has its own engine on native kernels (``vgg_native.py``,
+``mobilenet_native.py``, ``densenet_native.py``); they derive from this class for the flat-buffer plumbing (backbone
+parameters and gradients as views of ``P`` / ``G``, batch-norm buffers in the broadcast state, checkpoint names).  Used
+directly, the class runs an arbitrary backbone module through autograd as described below.
 
 The reference only warns when ``--backbone`` is not a ResNet (``train.py:323-324``) and then trains
 it through the same Keras graph.  Here the part that is identical for every backbone, and that
