@@ -69,42 +69,59 @@ __device__ __forceinline__ float round_bf16(float x) { return __bfloat162float(_
 // Forward also records, per output element, which window position (r*3+s) won (first maximum in
 // scan order; 255 when the maximum is <= 0, i.e. no gradient flows), so that backward is a pure
 // gather over <= 4 windows per input position without re-reading the conv output.
-__global__ void bn_relu_maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ scale,
-                                           const float* __restrict__ shift, __nv_bfloat16* __restrict__ y,
-                                           uint8_t* __restrict__ idx, int N, int H, int W, int C, int OH, int OW,
-                                           int pad_h, int pad_w) {
-  const int cg = C >> 3;
-  const long long total = static_cast<long long>(N) * OH * OW * cg;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+// 32-bit index arithmetic (the host checks the element count) and per-channel constants reloaded only when the
+// thread's channel group changes (with C = 64 and 256-thread blocks it never does).
+__global__ void __launch_bounds__(256) bn_relu_maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x,
+                                                                  const float* __restrict__ scale,
+                                                                  const float* __restrict__ shift,
+                                                                  __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ idx,
+                                                                  int N, int H, int W, int C, int OH, int OW, int pad_h,
+                                                                  int pad_w) {
+  const unsigned cg = static_cast<unsigned>(C) >> 3;
+  const unsigned total = static_cast<unsigned>(N) * OH * OW * cg;
+  float sc[8], sh[8];
+  int c_have = -1;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int c = static_cast<int>(i % cg) * 8;
-    long long t = i / cg;
-    const int ow = static_cast<int>(t % OW);
-    t /= OW;
-    const int oh = static_cast<int>(t % OH);
-    const int n = static_cast<int>(t / OH);
-    float sc[8], sh[8], m[8];
+    unsigned t = i / cg;
+    const int ow = static_cast<int>(t % static_cast<unsigned>(OW));
+    t /= static_cast<unsigned>(OW);
+    const int oh = static_cast<int>(t % static_cast<unsigned>(OH));
+    const int n = static_cast<int>(t / static_cast<unsigned>(OH));
+    if (c != c_have) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; }
+      c_have = c;
+    }
+    float m[8];
     uint32_t am[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; m[e] = 0.f; am[e] = 255u; }
+    for (int e = 0; e < 8; ++e) { m[e] = 0.f; am[e] = 255u; }
+    const int h0 = oh * 2 - pad_h, w0 = ow * 2 - pad_w;
+    const __nv_bfloat16* xb = x + (static_cast<size_t>(n) * H * W) * C + c;
+    // all nine window loads are issued before the first compare
+    uint4 v[9];
 #pragma unroll
-    for (int r = 0; r < 3; ++r) {
-      const int h = oh * 2 - pad_h + r;
-      if (h < 0 || h >= H) continue;
+    for (int r = 0; r < 3; ++r)
 #pragma unroll
-      for (int s = 0; s < 3; ++s) {
-        const int w = ow * 2 - pad_w + s;
-        if (w < 0 || w >= W) continue;
-        float v[8];
-        load8(x + ((static_cast<long long>(n) * H + h) * W + w) * C + c, v);
+      for (int q = 0; q < 3; ++q) {
+        const int h = h0 + r, w = w0 + q;
+        const bool ok = h >= 0 && h < H && w >= 0 && w < W;
+        v[r * 3 + q] = ok ? *reinterpret_cast<const uint4*>(xb + (static_cast<size_t>(h) * W + w) * C) : make_uint4(0u, 0u, 0u, 0u);
+      }
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float z = fmaf(v[e], sc[e], sh[e]);
-          if (z > m[e]) { m[e] = z; am[e] = r * 3 + s; }
-        }
+    for (int k = 0; k < 9; ++k) {
+      const int h = h0 + k / 3, w = w0 + k % 3;
+      if (h < 0 || h >= H || w < 0 || w >= W) continue;
+      const float f[8] = {bf16_lo(v[k].x), bf16_hi(v[k].x), bf16_lo(v[k].y), bf16_hi(v[k].y),
+                          bf16_lo(v[k].z), bf16_hi(v[k].z), bf16_lo(v[k].w), bf16_hi(v[k].w)};
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float z = fmaf(f[e], sc[e], sh[e]);
+        if (z > m[e]) { m[e] = z; am[e] = k; }
       }
     }
-    const long long o = ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c;
+    const size_t o = static_cast<size_t>(i) * 8;          // output index == loop index (same decomposition)
     store8(y + o, m);
     if (idx) {
       uint2 pk;
@@ -116,45 +133,78 @@ __global__ void bn_relu_maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, 
 }
 
 // dx[n,h,w,c] = scale[c] * sum over windows whose recorded arg-max is (h,w) of dy.
-__global__ void bn_relu_maxpool_bwd_kernel(const uint8_t* __restrict__ idx, const float* __restrict__ scale,
-                                           const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N,
-                                           int H, int W, int C, int OH, int OW, int pad_h, int pad_w) {
-  const int cg = C >> 3;
-  const long long total = static_cast<long long>(N) * H * W * cg;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+// An input position lies in at most 2 x 2 windows (3x3 / stride 2).  The four index words are loaded together, then the
+// dy vectors of the windows that match, so a thread waits for two memory round trips instead of up to eight.
+__global__ void __launch_bounds__(256) bn_relu_maxpool_bwd_kernel(const uint8_t* __restrict__ idx,
+                                                                  const float* __restrict__ scale,
+                                                                  const __nv_bfloat16* __restrict__ dy,
+                                                                  __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C,
+                                                                  int OH, int OW, int pad_h, int pad_w) {
+  const unsigned cg = static_cast<unsigned>(C) >> 3;
+  const unsigned total = static_cast<unsigned>(N) * H * W * cg;
+  float sc[8];
+  int c_have = -1;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int c = static_cast<int>(i % cg) * 8;
-    long long t = i / cg;
-    const int w = static_cast<int>(t % W);
-    t /= W;
-    const int h = static_cast<int>(t % H);
-    const int n = static_cast<int>(t / H);
+    unsigned t = i / cg;
+    const int w = static_cast<int>(t % static_cast<unsigned>(W));
+    t /= static_cast<unsigned>(W);
+    const int h = static_cast<int>(t % static_cast<unsigned>(H));
+    const int n = static_cast<int>(t / static_cast<unsigned>(H));
+    if (c != c_have) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) sc[e] = scale[c + e];
+      c_have = c;
+    }
+    // candidate windows: oh = (h + pad_h) >> 1 always, and the one above it when h + pad_h is even (same along w)
+    const int th = h + pad_h, tw = w + pad_w;
+    int ohs[2], ows[2];
+    bool vh[2], vw[2];
+    ohs[1] = th >> 1;
+    ohs[0] = ohs[1] - 1;
+    vh[1] = ohs[1] < OH;
+    vh[0] = !(th & 1) && ohs[0] >= 0 && ohs[0] < OH;
+    ows[1] = tw >> 1;
+    ows[0] = ows[1] - 1;
+    vw[1] = ows[1] < OW;
+    vw[0] = !(tw & 1) && ows[0] >= 0 && ows[0] < OW;
+    uint2 pk[4];
+    size_t off[4];
+    uint32_t me[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int a = k >> 1, b = k & 1;
+      const bool ok = vh[a] && vw[b];
+      off[k] = ((static_cast<size_t>(n) * OH + (ok ? ohs[a] : 0)) * OW + (ok ? ows[b] : 0)) * C + c;
+      me[k] = static_cast<uint32_t>((th - 2 * ohs[a]) * 3 + (tw - 2 * ows[b]));
+      pk[k] = ok ? *reinterpret_cast<const uint2*>(idx + off[k]) : make_uint2(0xffffffffu, 0xffffffffu);
+    }
+    uint4 gy[4];
+    bool hit[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t me4 = me[k] * 0x01010101u;
+      const uint32_t x0 = pk[k].x ^ me4, x1 = pk[k].y ^ me4;          // byte-wise equality test
+      hit[k] = (((x0 - 0x01010101u) & ~x0 & 0x80808080u) | ((x1 - 0x01010101u) & ~x1 & 0x80808080u)) != 0u;
+      gy[k] = hit[k] ? *reinterpret_cast<const uint4*>(dy + off[k]) : make_uint4(0u, 0u, 0u, 0u);
+    }
     float g[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) g[e] = 0.f;
-    const int oh_lo = max(0, (h + pad_h - 1) >> 1), oh_hi = min(OH - 1, (h + pad_h) >> 1);
-    const int ow_lo = max(0, (w + pad_w - 1) >> 1), ow_hi = min(OW - 1, (w + pad_w) >> 1);
-    for (int oh = oh_lo; oh <= oh_hi; ++oh)
-      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
-        const uint32_t me = static_cast<uint32_t>((h - (oh * 2 - pad_h)) * 3 + (w - (ow * 2 - pad_w)));
-        const long long o = ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + c;
-        const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
-        const uint32_t me4 = me * 0x01010101u;
-        // byte-wise equality test
-        const uint32_t x0 = pk.x ^ me4, x1 = pk.y ^ me4;
-        if (((x0 - 0x01010101u) & ~x0 & 0x80808080u) | ((x1 - 0x01010101u) & ~x1 & 0x80808080u)) {
-          float gy[8];
-          load8(dy + o, gy);
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            if (((pk.x >> (8 * e)) & 0xffu) == me) g[e] += gy[e];
-            if (((pk.y >> (8 * e)) & 0xffu) == me) g[4 + e] += gy[4 + e];
-          }
-        }
+    for (int k = 0; k < 4; ++k) {
+      if (!hit[k]) continue;
+      const float f[8] = {bf16_lo(gy[k].x), bf16_hi(gy[k].x), bf16_lo(gy[k].y), bf16_hi(gy[k].y),
+                          bf16_lo(gy[k].z), bf16_hi(gy[k].z), bf16_lo(gy[k].w), bf16_hi(gy[k].w)};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        if (((pk[k].x >> (8 * e)) & 0xffu) == me[k]) g[e] += f[e];
+        if (((pk[k].y >> (8 * e)) & 0xffu) == me[k]) g[4 + e] += f[4 + e];
       }
+    }
 #pragma unroll
-    for (int e = 0; e < 8; ++e) g[e] *= scale[c + e];
-    store8(dx + ((static_cast<long long>(n) * H + h) * W + w) * C + c, g);
+    for (int e = 0; e < 8; ++e) g[e] *= sc[e];
+    store8(dx + static_cast<size_t>(i) * 8, g);
   }
 }
 
@@ -455,6 +505,7 @@ int b200_bn_relu_maxpool_fwd(const void* x, const float* scale, const float* shi
                              int H, int W, int C, int OH, int OW, int pad_h, int pad_w, void* stream) {
   if (C % 8) return set_error(-1, "maxpool: C must be a multiple of 8");
   const long long total = static_cast<long long>(N) * OH * OW * (C / 8);
+  if (static_cast<long long>(N) * H * W * (C / 8) >= (1LL << 31)) return set_error(-1, "maxpool: tensor too large for 32-bit indexing");
   bn_relu_maxpool_fwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), scale, shift, static_cast<__nv_bfloat16*>(y), idx, N, H, W, C, OH, OW,
       pad_h, pad_w);
@@ -465,6 +516,7 @@ int b200_bn_relu_maxpool_bwd(const uint8_t* idx, const float* scale, const void*
                              int C, int OH, int OW, int pad_h, int pad_w, void* stream) {
   if (C % 8) return set_error(-1, "maxpool: C must be a multiple of 8");
   const long long total = static_cast<long long>(N) * H * W * (C / 8);
+  if (total >= (1LL << 31)) return set_error(-1, "maxpool: tensor too large for 32-bit indexing");
   bn_relu_maxpool_bwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       idx, scale, static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), N, H, W, C, OH, OW, pad_h,
       pad_w);
