@@ -113,6 +113,67 @@ __global__ void focal_kernel(const __nv_bfloat16* __restrict__ logits, __nv_bflo
   const float inv_norm = 1.f / fmaxf(1.f, static_cast<float>(*num_pos));
   const float gscale = loss_scale * inv_norm;
   float lsum = 0.f;
+  if ((K & 7) == 0 && total < (1LL << 31)) {
+    // Fast path (K a multiple of 8, e.g. COCO's 80): the 8 logits of a thread belong to ONE anchor, so its state and
+    // class are read once, ignored anchors cost one store, and there is no per-element anchor / class bookkeeping.
+    const unsigned ugroups = static_cast<unsigned>(groups), gpa = static_cast<unsigned>(K) >> 3;   // groups per anchor
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < static_cast<unsigned>(total); i += gridDim.x * blockDim.x) {
+      const unsigned g = i % ugroups, pix = i / ugroups;
+      const unsigned b = pix / static_cast<unsigned>(HW), p = pix - b * static_cast<unsigned>(HW);
+      const unsigned j = g / gpa;
+      const int k0 = static_cast<int>(g - j * gpa) * 8;
+      const size_t off = static_cast<size_t>(pix) * ld + g * 8;
+      const size_t t = static_cast<size_t>(b) * A_total + a_off + p * 9 + j;
+      const int st = state[t];
+      uint4 o = make_uint4(0u, 0u, 0u, 0u);
+      if (st >= 0) {
+        const int kpos = (st == 1) ? static_cast<int>(cls[t]) - k0 : -1;     // index of the positive class in this vector
+        const uint4 u = *reinterpret_cast<const uint4*>(logits + off);
+        const float x[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
+                            bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
+        float gr[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float xv = x[e];
+          const float ex = __expf(-fabsf(xv));
+          const float inv = __frcp_rn(1.f + ex);
+          const float pr = xv >= 0.f ? inv : ex * inv;
+          const float sp_pos = fmaxf(xv, 0.f) + __logf(1.f + ex);   // -log(1-p)
+          const float sp_neg = sp_pos - xv;                          // -log(p)
+          const bool pos = e == kpos;
+          float l, d;
+          if (gamma == 2.f) {
+            if (pos) {
+              const float q = 1.f - pr;
+              l = alpha * q * q * sp_neg;
+              d = alpha * q * q * (-2.f * pr * sp_neg - q);
+            } else {
+              l = (1.f - alpha) * pr * pr * sp_pos;
+              d = (1.f - alpha) * pr * pr * (pr + 2.f * (1.f - pr) * sp_pos);
+            }
+          } else {
+            if (pos) {
+              const float q = 1.f - pr;
+              const float m = __powf(fmaxf(q, 1e-12f), gamma);
+              l = alpha * m * sp_neg;
+              d = alpha * m * (-gamma * pr * sp_neg - q);
+            } else {
+              const float m = __powf(fmaxf(pr, 1e-12f), gamma);
+              l = (1.f - alpha) * m * sp_pos;
+              d = (1.f - alpha) * m * (pr + gamma * (1.f - pr) * sp_pos);
+            }
+          }
+          lsum += l;
+          gr[e] = d * gscale;
+        }
+        o.x = pack_bf16x2(gr[0], gr[1]);
+        o.y = pack_bf16x2(gr[2], gr[3]);
+        o.z = pack_bf16x2(gr[4], gr[5]);
+        o.w = pack_bf16x2(gr[6], gr[7]);
+      }
+      *reinterpret_cast<uint4*>(dlogits + off) = o;
+    }
+  } else
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int g = static_cast<int>(i % groups);
