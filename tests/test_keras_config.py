@@ -88,7 +88,8 @@ def interpret(cfg, input_shape, weights):
     return [get(r) for r in cfg["output_layers"]]
 
 
-@pytest.mark.parametrize("backbone", ["resnet50", "resnet101", "vgg16", "mobilenet224_1.0", "densenet121"])
+@pytest.mark.parametrize("backbone", ["resnet50", "resnet101", "resnet152", "vgg16", "vgg19", "mobilenet224_1.0",
+                                      "mobilenet128_0.25", "densenet121", "densenet169"])
 def test_model_config_is_a_consistent_keras_graph(backbone):
     m = RetinaNet(7, backbone)
     cfg = json.loads(json.dumps(keras_h5.model_config(m)))          # through JSON, as it is stored
