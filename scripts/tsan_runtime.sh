@@ -15,8 +15,11 @@ export TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 exitcode=0 log_path=
 rm -f build/tsan/report.*
 LD_PRELOAD=$TSAN python -m batchai_retinanet_horovod_coco_b200.parallel.launcher -np $NP python tests/workers/rt_collectives.py basic $TL > build/tsan/run.log 2>&1
 RC=$?
+# allreduce and broadcast released in one response with a delayed non-root rank (the result-buffer race of round 1)
+B200RT_FAULT=delay:1:3 LD_PRELOAD=$TSAN python -m batchai_retinanet_horovod_coco_b200.parallel.launcher -np $NP python tests/workers/rt_collectives.py ar_then_bcast >> build/tsan/run.log 2>&1
+RC2=$?
 {
-  echo "# ThreadSanitizer run of libb200rt.so: $NP ranks, tests/workers/rt_collectives.py basic (exit $RC)"
+  echo "# ThreadSanitizer run of libb200rt.so: $NP ranks, tests/workers/rt_collectives.py basic (exit $RC) + ar_then_bcast with B200RT_FAULT=delay:1:3 (exit $RC2)"
   echo "# $(g++ --version | head -1)"
   grep -o WORKER_OK build/tsan/run.log | wc -l | sed 's/^/workers finished: /'
   N=$(cat build/tsan/report.* 2>/dev/null | grep -c "WARNING: ThreadSanitizer")
