@@ -218,11 +218,9 @@ __global__ void nms_scan_kernel(const unsigned long long* __restrict__ mask, con
                                 float* __restrict__ out_scores, int* __restrict__ out_labels,
                                 int* __restrict__ keep_flags) {
   extern __shared__ unsigned long long removed[];
-  __shared__ int s_keep;
   const int b = blockIdx.x;
   const int n = count ? min(min(count[b], max_cand), kNmsCap) : fixed_n;
   for (int w = threadIdx.x; w < words; w += blockDim.x) removed[w] = 0ull;
-  if (threadIdx.x == 0) s_keep = 0;
   __syncthreads();
   int kept = 0;
   for (int i = 0; i < n && kept < max_keep; ++i) {
