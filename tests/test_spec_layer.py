@@ -182,3 +182,20 @@ def test_prediction_model_runs(r50):
     pm = retinanet_bbox(r50)
     b, s, l = pm(torch.randn(1, 3, 128, 160))
     assert b.shape == (1, 300, 4) and s.shape == (1, 300) and l.shape == (1, 300)
+
+
+def test_affine_inversion_matches_opencv():
+    """``ops.native.invert_affine_like_cv2`` (host side of the GPU warp: the dst -> src map) against OpenCV's own
+    inversion, for the transforms the augmentation generates and for a singular matrix."""
+    import cv2
+    import numpy as np
+    from batchai_retinanet_horovod_coco_b200.ops.native import invert_affine_like_cv2
+    from batchai_retinanet_horovod_coco_b200.utils.transform import random_transform_generator
+    gen = random_transform_generator(min_rotation=-0.1, max_rotation=0.1, min_translation=(-0.1, -0.1),
+                                     max_translation=(0.1, 0.1), min_shear=-0.1, max_shear=0.1, min_scaling=(0.9, 0.9),
+                                     max_scaling=(1.1, 1.1), flip_x_chance=0.5, flip_y_chance=0.5,
+                                     prng=np.random.RandomState(3))
+    for _ in range(50):
+        m = np.asarray(next(gen), dtype=np.float64)[:2, :]
+        assert np.allclose(invert_affine_like_cv2(m), cv2.invertAffineTransform(m), rtol=1e-12, atol=1e-12)
+    assert np.array_equal(invert_affine_like_cv2([[1, 2, 3], [2, 4, 5]])[:, :2], np.zeros((2, 2)))     # singular: D = 0
