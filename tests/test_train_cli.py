@@ -212,3 +212,46 @@ def test_latest_snapshot_picks_highest_epoch(tmp_path):
     for n in ("checkpoint-02.h5", "checkpoint-10.h5", "checkpoint-9.h5", "checkpoint-xx.h5", "other.h5"):
         (tmp_path / n).write_text("")
     assert T.latest_snapshot(str(tmp_path)) == str(tmp_path / "checkpoint-10.h5")
+
+
+def test_next_raw_describes_the_same_batch_as_the_host_pipeline(tmp_path):
+    """``Generator.next_raw()`` (what the GPU batch assembler consumes: decoded images + augmentation matrices + resize
+    scales + transformed boxes) against ``next_compact()`` (pixels produced on the host): replaying the raw description
+    with OpenCV on the CPU must give the identical batch, so the two data paths differ only in WHERE the warp and the
+    resize run.  (The GPU kernels themselves are compared with OpenCV in tests/test_gpu_ops.py.)"""
+    import cv2
+    import numpy as np
+    from batchai_retinanet_horovod_coco_b200.preprocessing.csv_generator import CSVGenerator
+    from batchai_retinanet_horovod_coco_b200.utils.transform import random_transform_generator
+    rng = np.random.default_rng(1)
+    rows = []
+    for i, (h, w) in enumerate([(120, 160), (150, 110), (96, 200), (130, 130)]):
+        img = cv2.GaussianBlur(rng.integers(0, 256, (h, w, 3), dtype=np.uint8), (7, 7), 2.0)
+        path = str(tmp_path / f"im{i}.png")
+        cv2.imwrite(path, img)
+        rows.append(f"{path},10,12,{w - 20},{h - 15},thing")
+    (tmp_path / "ann.csv").write_text("\n".join(rows) + "\n")
+    (tmp_path / "cls.csv").write_text("thing,0\n")
+
+    def make():
+        tg = random_transform_generator(min_rotation=-0.1, max_rotation=0.1, min_translation=(-0.1, -0.1),
+                                        max_translation=(0.1, 0.1), min_shear=-0.1, max_shear=0.1, min_scaling=(0.9, 0.9),
+                                        max_scaling=(1.1, 1.1), flip_x_chance=0.5, flip_y_chance=0.5,
+                                        prng=np.random.RandomState(5))
+        return CSVGenerator(str(tmp_path / "ann.csv"), str(tmp_path / "cls.csv"), transform_generator=tg, batch_size=2,
+                            image_min_side=200, image_max_side=300, shuffle_groups=False, seed=3)
+
+    ga, gb = make(), make()
+    for _ in range(2):
+        himg, hgt, hcnt, hhw = ga.next_compact()
+        raw = gb.next_raw()
+        assert torch.equal(hcnt, raw["count"]) and torch.allclose(hgt, raw["gt"], atol=1e-3)
+        assert [tuple(x) for x in hhw.tolist()] == [tuple(x) for x in raw["out_hw"]]
+        border = cv2.BORDER_REPLICATE if raw["border_replicate"] else cv2.BORDER_CONSTANT
+        for i, (img, m, (h, w), (sx, sy)) in enumerate(zip(raw["images"], raw["matrices"], raw["out_hw"], raw["scales"])):
+            if m is not None:
+                img = cv2.warpAffine(img, np.asarray(m)[:2, :], dsize=(img.shape[1], img.shape[0]), flags=cv2.INTER_LINEAR,
+                                     borderMode=border, borderValue=raw["cval"])
+            out = cv2.resize(img, None, fx=1.0 / sx, fy=1.0 / sy)
+            assert out.shape[:2] == (h, w)
+            assert np.array_equal(himg[i, :h, :w].numpy(), out)
