@@ -299,6 +299,28 @@ def test_gpu_resize_and_warp_match_opencv():
         assert np.abs(d).max() <= 1, (rep, np.abs(d).max())
 
 
+def test_gpu_geometry_kernels_equal_their_numpy_restatement():
+    """The kernels against ``ops.image_ref`` (the same integer arithmetic in NumPy, itself compared with OpenCV over
+    many random cases on the CPU): identical bytes, odd sizes, up- and down-scaling, shear + flip, both border modes."""
+    import numpy as np
+    from batchai_retinanet_horovod_coco_b200.ops import image_ref
+    rng = np.random.default_rng(4)
+    for (h, w) in ((197, 263), (64, 31), (33, 250)):
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        src = torch.from_numpy(img).to(DEV)
+        for f in (1.37, 0.61, 2.5):
+            dh, dw = int(round(h * f)), int(round(w * f))
+            out = torch.zeros(dh, dw, 3, dtype=torch.uint8, device=DEV)
+            native.resize_linear_u8(src, out, 1.0 / f, 1.0 / f)
+            assert np.array_equal(out.cpu().numpy(), image_ref.resize_linear_u8(img, dh, dw, 1.0 / f, 1.0 / f)), (h, w, f)
+        M = np.array([[-1.04 * np.cos(0.1), 1.04 * np.sin(0.15), w - 3.7], [0.97 * np.sin(0.1), 0.97 * np.cos(0.15), 2.2]])
+        for rep in (True, False):
+            out = torch.zeros_like(src)
+            native.warp_affine_u8(src, out, M, border_replicate=rep, cval=9)
+            want = image_ref.warp_affine_u8(img, native.invert_affine_like_cv2(M), rep, 9)
+            assert np.array_equal(out.cpu().numpy(), want), (h, w, rep)
+
+
 def test_gpu_batch_assembly_matches_the_host_pipeline(tmp_path):
     """Generator.next_raw() + GpuBatchAssembler == Generator.next_compact() (decode, random transform, resize, pad)."""
     import cv2
